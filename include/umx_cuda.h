@@ -1,0 +1,120 @@
+/* umx_cuda.h — C ABI of the B200-native (sm_100a) UMX-L demixing hot path.
+ *
+ * Drop-in boundary for sevagh/umx.cpp's CPU path.  Every entry point cites the reference interface it
+ * replaces (paths relative to the reference tree).  Plain pointers and sizes only; no C++ or torch
+ * types.  All calls return 0 on success and a negative status on failure (never throw, never exit);
+ * umx_cuda_last_error() then describes the failure.  There is NO CPU fallback: without a CUDA device
+ * every compute call fails with a clear error.
+ *
+ * Memory orders at the boundary are the reference's own (Eigen column-major), so a reference-side
+ * binding passes Eigen's .data() pointers straight through:
+ *   waveform  Eigen::MatrixXf(2, N)              -> float[N][2]          interleaved L,R
+ *   spec      Eigen::Tensor3dXcf(2, F, 2049)     -> float[2049][F][2][2] (re,im)
+ *   mags      Eigen::Tensor3dXf(2, F, 2049)      -> float[2049][F][2]
+ *   matrices  Eigen::MatrixXf(r, c)              -> float[c][r]
+ * Host pointers unless a parameter is named d_* (device pointer).
+ */
+#ifndef UMX_CUDA_H
+#define UMX_CUDA_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct umx_cuda_model umx_cuda_model;     /* weights resident on one GPU       (struct umx_model, src/model.hpp:12-56) */
+typedef struct umx_cuda_session umx_cuda_session; /* per-track streaming state + work buffers (lstm_data src/lstm.hpp:10-16, stft_buffers src/dsp.hpp:21-59) */
+
+/* reference constants (src/dsp.hpp:16-19, src/inference.hpp:13-16, umx.cpp:112-113,156-157,180) */
+#define UMX_SAMPLE_RATE 44100
+#define UMX_NFFT 4096
+#define UMX_HOP 1024
+#define UMX_BINS 2049
+#define UMX_SEGMENT_SAMPLES 2646000
+#define UMX_STRIDE_SAMPLES 1984500
+#define UMX_MAX_SHIFT 22050
+#define UMX_DEFAULT_SHIFT_OFFSET 4033 /* rand() % 22050 of an unseeded glibc process, umx.cpp:115 */
+
+/* ---- errors / device ------------------------------------------------------------------------- */
+const char *umx_cuda_last_error(void);
+int umx_cuda_device_count(void);
+/* frames of an STFT over a buffer of n_buf samples: n_buf/1024 + 1 (src/dsp.hpp:46) */
+int umx_cuda_nb_frames(int n_buf);
+
+/* ---- model: replaces load_umx_model (src/model.hpp:58, src/model.cpp:42-665) ----------------- */
+/* ggml stream (magic 0x756d7867), gzip-compressed or raw, parsed on the host, dequantised on the GPU
+ * with one fmaf per element (bit-exact with src/model.cpp:614,660). */
+int umx_cuda_model_create(const void *ggml_bytes, size_t n_bytes, int device, umx_cuda_model **out);
+int umx_cuda_model_create_from_file(const char *path, int device, umx_cuda_model **out);
+void umx_cuda_model_destroy(umx_cuda_model *m);
+int umx_cuda_model_hidden_size(const umx_cuda_model *m); /* umx_model::hidden_size */
+int umx_cuda_model_device(const umx_cuda_model *m);
+/* Dequantised fp32 tensor as the reference holds it (same member names as struct umx_model, e.g.
+ * "fc1_w", "bn1_rv", "lstm_hh_w", "input_mean"; layer/dir only for lstm_*).  Column-major (rows, cols).
+ * out may be NULL to query the shape.  Returns the element count, or <0. */
+long umx_cuda_model_tensor(const umx_cuda_model *m, const char *name, int target, int layer, int dir,
+                           float *out, long capacity, int *rows, int *cols);
+
+/* ---- session: streaming state for up to max_tracks tracks processed in lockstep ------------- */
+/* n_buf = samples per segment buffer (UMX_SEGMENT_SAMPLES in the CLI, umx.cpp:161-171).
+ * Creating a session zeroes the LSTM h/c carry (create_lstm_data, src/lstm.cpp:41-84). */
+int umx_cuda_session_create(umx_cuda_model *m, int max_tracks, int n_buf, umx_cuda_session **out);
+void umx_cuda_session_destroy(umx_cuda_session *s);
+int umx_cuda_session_reset(umx_cuda_session *s); /* umx_lstm_set_zero, src/lstm.cpp:86-99 */
+/* h / c carry of (track, target, layer, dir): lstm_hidden floats each (lstm_data::h/c, src/lstm.hpp:14-15) */
+int umx_cuda_session_get_state(umx_cuda_session *s, int track, int target, int layer, int dir, float *h, float *c);
+
+/* ---- umx_inference (src/inference.hpp:20-23, src/inference.cpp:12-207) ----------------------- */
+/* One chunk of n <= n_buf samples, processed as a full n_buf-sample window (always nb_frames(n_buf)
+ * frames, zero-extended: SURVEY F4), LSTM state carried in the session (track slot 0).
+ * audio: float[n][2]; out: 4 stems x float[n][2] (bass, drums, other, vocals). */
+int umx_cuda_infer_segment(umx_cuda_session *s, const float *audio, int n, float *out);
+
+/* ---- whole tracks: shift_inference + split_inference (umx.cpp:99-295) ------------------------ */
+/* n_tracks <= max_tracks independent tracks, each shifted by shift_offset (umx.cpp:112-122), cut into
+ * n_buf-sample segments at 0.75*n_buf stride, demixed with streaming LSTM state, recombined with the
+ * triangular weights and sum_weight normalisation (umx.cpp:197-273), trimmed (umx.cpp:136-147).
+ * Session state is reset first (a fresh process per track in the reference).
+ * audio[i]: float[n_samples[i]][2]; out[i]: 4 x float[n_samples[i]][2]. Host memory (pinned is faster). */
+int umx_cuda_demix(umx_cuda_session *s, const float *const *audio, const int64_t *n_samples, int n_tracks,
+                   int shift_offset, float *const *out);
+/* Same with inputs/outputs already resident in device memory (no host<->device copies). */
+int umx_cuda_demix_device(umx_cuda_session *s, const float *const *d_audio, const int64_t *n_samples,
+                          int n_tracks, int shift_offset, float *const *d_out);
+/* Segment table of split_inference for a track of n samples shifted by shift_offset (umx.cpp:214-218):
+ * writes up to cap (offset, chunk_length) pairs, returns the segment count. */
+int umx_cuda_segment_plan(int64_t n_samples, int shift_offset, int n_buf, int64_t *offsets, int *lengths, int cap);
+
+/* ---- kernel-level entry points (parity tests, microbenchmarks, the Eigen-typed shim) --------- */
+/* stft (src/dsp.hpp:114, src/dsp.cpp:141-176): audio float[n][2] zero-extended to n_buf;
+ * spec: complex float[2049][F][2], F = nb_frames(n_buf). */
+int umx_cuda_stft(const float *audio, int n, int n_buf, float *spec);
+/* istft (src/dsp.hpp:115, src/dsp.cpp:178-207): spec complex float[2049][F][2] -> wave float[n_wave][2] */
+int umx_cuda_istft(const float *spec, int n_buf, int n_wave, float *wave);
+/* umx_lstm_forward (src/lstm.hpp:22-24, src/lstm.cpp:101-179) for `target`, state of track slot 0:
+ * input column-major (F, hidden) -> out column-major (F, hidden); F <= nb_frames(n_buf). */
+int umx_cuda_lstm_forward(umx_cuda_session *s, int target, const float *input, int F, float *out);
+/* wiener_filter (src/wiener.hpp:19-21, src/wiener.cpp:92-425): mix complex float[2049][F][2] (IN/OUT:
+ * left divided by max_abs like the reference), mags 4 x float[2049][F][2] -> out 4 x complex [2049][F][2] */
+int umx_cuda_wiener(float *mix, const float *mags, int F, float *out);
+/* The network only (src/inference.cpp:29-186): spec complex [2049][F][2] -> target magnitudes
+ * 4 x float[2049][F][2]; LSTM state of track slot 0 advances. F == nb_frames(n_buf) of the session. */
+int umx_cuda_target_mags(umx_cuda_session *s, const float *spec, float *mags);
+
+/* ---- measurement ------------------------------------------------------------------------------ */
+/* Per-stage device time of the most recent demix / infer_segment call, from CUDA events recorded on
+ * the session's own stream.  Stage names: "stft", "gemm", "lstm", "wiener", "istft", "finalize",
+ * "h2d", "d2h", "total".  Returns milliseconds, or <0 if unknown.  launches: kernels launched. */
+int umx_cuda_session_set_profiling(umx_cuda_session *s, int enabled);
+double umx_cuda_session_stage_ms(umx_cuda_session *s, const char *stage);
+long umx_cuda_session_launches(umx_cuda_session *s);
+/* Tuning knobs (documented in DESIGN.md): "gemm_terms" 1..3 fp16 split terms per tensor-core GEMM,
+ * "gemm_impl" 0 = tcgen05, 1 = SIMT fp32 validation kernel, "lstm_impl" 0 = cluster kernel, 1 = simple. */
+int umx_cuda_session_set_option(umx_cuda_session *s, const char *name, int value);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* UMX_CUDA_H */

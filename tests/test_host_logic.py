@@ -1,0 +1,71 @@
+"""CPU: host-side logic and the C-ABI surface (no compute calls)."""
+import ctypes
+import os
+import re
+import subprocess
+
+import numpy as np
+import pytest
+
+from oracle import umx_oracle as O
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def test_fft_core_and_padding_on_host(tmp_path):
+    """The exact radix-16 FFT code of the kernels (csrc/fft4096.cuh), emulated thread by thread."""
+    exe = tmp_path / "host_fft_check"
+    subprocess.run(["/usr/bin/g++", "-O2", "-std=c++17", "-o", str(exe),
+                    os.path.join(ROOT, "tests", "host", "host_fft_check.cpp")], check=True)
+    out = subprocess.run([str(exe)], capture_output=True, text=True)
+    assert out.returncode == 0, out.stdout + out.stderr
+
+
+def test_library_exports_every_declared_symbol(umx):
+    hdr = open(os.path.join(ROOT, "include", "umx_cuda.h")).read()
+    declared = sorted(set(re.findall(r"\b(umx_cuda_[a-z0-9_]+)\s*\(", hdr)))
+    assert len(declared) >= 20
+    lib = ctypes.CDLL(umx.LIB_PATH)
+    missing = [s for s in declared if not hasattr(lib, s)]
+    assert not missing, f"not exported: {missing}"
+    assert sorted(umx.EXPORTS) == declared
+
+
+@pytest.mark.parametrize("n,shift", [(441000, 4033), (7938000, 4033), (18522000, 4033), (1, 0), (1984500, 22049),
+                                     (2646000 - 22050 + 4033, 4033), (5 * 1984500, 0)])
+def test_segment_plan_bit_exact(umx, n, shift):
+    """umx.cpp:214-218 through the C ABI vs the oracle's integer math."""
+    assert umx.segment_plan(n, shift) == O.segment_plan(O.shifted_length(n, shift))
+
+
+def test_segment_plan_small_buffers(umx):
+    n_buf = 16384
+    stride = int(np.float32(0.75) * np.float32(n_buf))
+    for n in (100, 30000, 16384 * 3):
+        L = n + 22050 - 4033
+        want = [(off, min(n_buf, L - off)) for off in range(0, L, stride)]
+        assert umx.segment_plan(n, 4033, n_buf) == want
+
+
+def test_nb_frames(umx):
+    assert umx.lib().umx_cuda_nb_frames(2646000) == 2584 == O.nb_frames(2646000)
+    assert umx.lib().umx_cuda_nb_frames(4096) == 5
+
+
+def test_no_cpu_fallback(umx, have_gpu):
+    """Without a device every compute entry point must fail loudly."""
+    if have_gpu:
+        pytest.skip("GPU present")
+    from oracle import synth
+
+    with pytest.raises(umx.UmxCudaError):
+        umx.load_umx_model(synth.make_ggml(hidden=8))
+    with pytest.raises(umx.UmxCudaError):
+        umx.stft(np.zeros((2, 4096), np.float32))
+
+
+def test_product_does_not_import_oracle():
+    src = open(os.path.join(ROOT, "umx.cpp_b200", "__init__.py")).read()
+    assert "import oracle" not in src and "from oracle" not in src
+    for f in os.listdir(os.path.join(ROOT, "umx.cpp_b200", "csrc")):
+        assert "oracle" not in open(os.path.join(ROOT, "umx.cpp_b200", "csrc", f)).read().lower()

@@ -1,0 +1,364 @@
+// Tensor-core GEMM for the dense layers of the network (reference: the Eigen GEMMs at
+// src/inference.cpp:86,127,143 and the W_ih x_t half of src/lstm.cpp:132-136, for ALL frames at once).
+//
+//   C[m,n] = act(alpha[n] * sum_k A[m,k] B[n,k] + beta[n])
+//
+// sm_100a design: persistent CTAs (one per SM), 128x256 output tiles, fp16 operands staged by TMA
+// (cp.async.bulk.tensor, 128-byte swizzle) through a 4-stage mbarrier ring, tcgen05.mma (M128 N256 K16,
+// one issuing thread) accumulating in fp32 in TMEM, two accumulator buffers (2 x 256 TMEM columns) so
+// the epilogue of tile i overlaps the MMAs of tile i+1.  Warp roles: 0 = TMA producer, 1 = MMA issuer
+// (+ TMEM alloc), 2..5 = epilogue (tcgen05.ld -> BN/bias/activation -> fp32 or fp16 hi/lo stores).
+// Precision: every operand is a (hi, lo) fp16 pair; `terms` selects hi*hi [+ lo*hi [+ hi*lo]] into the
+// same accumulator, i.e. 1, 2 or 3 MMA passes per k-block ("GEMM precision").
+#include "common.cuh"
+#include "kernels.cuh"
+#include "tc_common.cuh"
+
+#include <cstring>
+#include <mutex>
+
+namespace umx
+{
+using namespace tc;
+
+namespace
+{
+constexpr int BM = 128, BN = 256, BK = 64; // BK fp16 = 128 bytes = one swizzle row
+constexpr int kStages = 4;
+constexpr int kABytes = BM * BK * 2;       // 16 KB
+constexpr int kBBytes = BN * BK * 2;       // 32 KB
+constexpr int kStageBytes = kABytes + kBBytes;
+constexpr int kEpiWarps = 4;
+constexpr int kEpiBytesPerWarp = 32 * 33 * 4;
+constexpr int kSmemBytes = kStages * kStageBytes + kEpiWarps * kEpiBytesPerWarp + 256 + 1024; // + barriers + align slack
+constexpr int kThreads = 32 * (2 + kEpiWarps);
+constexpr uint32_t kTmemCols = 512;
+
+struct TcProblem
+{
+    int M, N, K;
+    int act;
+    const float *alpha;
+    const float *beta;
+    float *out_f32;
+    __half *out_hi;
+    __half *out_lo;
+    int ldo;
+    int n_group;
+    long group_stride;
+    int m_tiles, n_tiles, tile_begin; // tiles [tile_begin, tile_begin + m_tiles*n_tiles)
+    int pad_;
+};
+
+struct alignas(64) TcParams
+{
+    CUtensorMap a_hi[kMaxGemmProblems], a_lo[kMaxGemmProblems], b_hi[kMaxGemmProblems], b_lo[kMaxGemmProblems];
+    TcProblem p[kMaxGemmProblems];
+    int count, total_tiles, terms, pad_;
+};
+
+__device__ __forceinline__ float act_apply(float v, int act)
+{
+    if (act == kActTanh)
+        return tanhf(v);
+    if (act == kActRelu)
+        return fmaxf(v, 0.f);
+    return v;
+}
+
+__global__ void __launch_bounds__(kThreads, 1) gemm_tc_kernel(const __grid_constant__ TcParams P)
+{
+    extern __shared__ uint8_t smem_raw[];
+    // 1024-byte alignment for the 128-byte swizzle atoms
+    uint8_t *smem = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    uint8_t *epi_base = smem + kStages * kStageBytes;
+    uint64_t *bars = reinterpret_cast<uint64_t *>(epi_base + kEpiWarps * kEpiBytesPerWarp);
+    // bars: full[kStages], empty[kStages], tmem_full[2], tmem_empty[2], then the TMEM base address
+    const uint32_t full0 = smem_u32(bars), empty0 = smem_u32(bars + kStages);
+    const uint32_t tfull0 = smem_u32(bars + 2 * kStages), tempty0 = smem_u32(bars + 2 * kStages + 2);
+    uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + 2 * kStages + 4);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+    if (warp == 0 && lane == 0)
+    {
+        for (int i = 0; i < kStages; ++i)
+        {
+            mbar_init(full0 + 8 * i, 1);
+            mbar_init(empty0 + 8 * i, 1);
+        }
+        for (int i = 0; i < 2; ++i)
+        {
+            mbar_init(tfull0 + 8 * i, 1);
+            mbar_init(tempty0 + 8 * i, kEpiWarps);
+        }
+        fence_barrier_init();
+    }
+    if (warp == 1)
+        tmem_alloc(smem_u32(tmem_slot), kTmemCols);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    auto locate = [&](int tile, int &pi, int &m0, int &n0) {
+        pi = 0;
+        while (pi + 1 < P.count && tile >= P.p[pi + 1].tile_begin)
+            ++pi;
+        const int local = tile - P.p[pi].tile_begin;
+        m0 = (local % P.p[pi].m_tiles) * BM; // m fastest: CTAs running together share one B tile
+        n0 = (local / P.p[pi].m_tiles) * BN;
+    };
+
+    if (warp == 0)
+    {
+        // ================= TMA producer =================
+        if (lane == 0)
+        {
+            int stage = 0;
+            uint32_t phase = 0;
+            for (int tile = blockIdx.x; tile < P.total_tiles; tile += gridDim.x)
+            {
+                int pi, m0, n0;
+                locate(tile, pi, m0, n0);
+                const int kblocks = (P.p[pi].K + BK - 1) / BK;
+                for (int kb = 0; kb < kblocks; ++kb)
+                    for (int term = 0; term < P.terms; ++term)
+                    {
+                        mbar_wait(empty0 + 8 * stage, phase ^ 1);
+                        const uint32_t bar = full0 + 8 * stage;
+                        mbar_arrive_expect_tx(bar, kStageBytes);
+                        const CUtensorMap *ma = (term == 1) ? &P.a_lo[pi] : &P.a_hi[pi];
+                        const CUtensorMap *mb = (term == 2) ? &P.b_lo[pi] : &P.b_hi[pi];
+                        const uint32_t sa = smem_u32(smem + stage * kStageBytes);
+                        tma_load_2d(sa, ma, kb * BK, m0, bar);
+                        tma_load_2d(sa + kABytes, mb, kb * BK, n0, bar);
+                        if (++stage == kStages)
+                        {
+                            stage = 0;
+                            phase ^= 1;
+                        }
+                    }
+            }
+        }
+    }
+    else if (warp == 1)
+    {
+        // ================= MMA issuer =================
+        if (lane == 0)
+        {
+            constexpr uint32_t idesc = idesc_f16_f32acc(BM, BN);
+            int stage = 0;
+            uint32_t phase = 0;
+            int acc = 0;
+            uint32_t acc_phase = 0;
+            for (int tile = blockIdx.x; tile < P.total_tiles; tile += gridDim.x)
+            {
+                int pi, m0, n0;
+                locate(tile, pi, m0, n0);
+                const int kiters = ((P.p[pi].K + BK - 1) / BK) * P.terms;
+                mbar_wait(tempty0 + 8 * acc, acc_phase ^ 1); // epilogue has drained this accumulator
+                tc_fence_after();
+                const uint32_t d_tmem = tmem_base + acc * BN;
+                for (int it = 0; it < kiters; ++it)
+                {
+                    mbar_wait(full0 + 8 * stage, phase);
+                    tc_fence_after();
+                    const uint32_t sa = smem_u32(smem + stage * kStageBytes);
+                    const uint64_t da = smem_desc_sw128(sa), db = smem_desc_sw128(sa + kABytes);
+#pragma unroll
+                    for (int k = 0; k < BK / 16; ++k) // +32 bytes per K=16 step inside the swizzle row
+                        mma_f16(d_tmem, da + 2 * k, db + 2 * k, idesc, (it > 0 || k > 0) ? 1u : 0u);
+                    tc_commit(empty0 + 8 * stage); // frees the smem slot when these MMAs retire
+                    if (++stage == kStages)
+                    {
+                        stage = 0;
+                        phase ^= 1;
+                    }
+                }
+                tc_commit(tfull0 + 8 * acc); // accumulator complete
+                if (++acc == 2)
+                {
+                    acc = 0;
+                    acc_phase ^= 1;
+                }
+            }
+        }
+    }
+    else
+    {
+        // ================= epilogue =================
+        const int q = warp & 3; // TMEM lane quadrant this warp may read
+        float *stage_buf = reinterpret_cast<float *>(epi_base + (warp - 2) * kEpiBytesPerWarp);
+        int acc = 0;
+        uint32_t acc_phase = 0;
+        for (int tile = blockIdx.x; tile < P.total_tiles; tile += gridDim.x)
+        {
+            int pi, m0, n0;
+            locate(tile, pi, m0, n0);
+            const TcProblem &pb = P.p[pi];
+            mbar_wait(tfull0 + 8 * acc, acc_phase);
+            tc_fence_after();
+            const uint32_t taddr = tmem_base + acc * BN + ((uint32_t)(32 * q) << 16);
+            const int row0 = m0 + 32 * q;
+#pragma unroll 1
+            for (int ch = 0; ch < BN / 32; ++ch)
+            {
+                uint32_t r[32];
+                tmem_ld32(taddr + ch * 32, r);
+                tc_wait_ld();
+                if (ch == BN / 32 - 1)
+                { // everything this warp needs has left TMEM
+                    tc_fence_before();
+                    __syncwarp();
+                    if (lane == 0)
+                        mbar_arrive(tempty0 + 8 * acc);
+                }
+                const int n = n0 + ch * 32 + lane;
+                if (n0 + ch * 32 >= pb.N)
+                    continue;
+                // transpose 32x32 through smem: lane = row -> lane = column
+#pragma unroll
+                for (int c = 0; c < 32; ++c)
+                    stage_buf[lane * 33 + c] = __uint_as_float(r[c]);
+                __syncwarp();
+                const bool col_ok = n < pb.N;
+                const float al = (col_ok && pb.alpha) ? pb.alpha[n] : 1.f;
+                const float be = (col_ok && pb.beta) ? pb.beta[n] : 0.f;
+                const long obase = col_ok ? (long)(n / pb.n_group) * pb.group_stride + (n % pb.n_group) : 0;
+#pragma unroll 4
+                for (int rr = 0; rr < 32; ++rr)
+                {
+                    const int m = row0 + rr;
+                    if (m >= pb.M)
+                        break;
+                    if (col_ok)
+                    {
+                        const float v = act_apply(fmaf(stage_buf[rr * 33 + lane], al, be), pb.act);
+                        const long o = obase + (long)m * pb.ldo;
+                        if (pb.out_f32)
+                            pb.out_f32[o] = v;
+                        if (pb.out_hi)
+                        {
+                            __half h, l;
+                            split_half(v, h, l);
+                            pb.out_hi[o] = h;
+                            pb.out_lo[o] = l;
+                        }
+                    }
+                }
+                __syncwarp();
+            }
+            if (++acc == 2)
+            {
+                acc = 0;
+                acc_phase ^= 1;
+            }
+        }
+    }
+
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1)
+    {
+        tc_fence_after();
+        tmem_dealloc(tmem_base, kTmemCols);
+    }
+}
+
+// ---- host side -----------------------------------------------------------------------------------------
+typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *,
+                                  const cuuint64_t *, const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+EncodeTiledFn get_encode_fn()
+{
+    static EncodeTiledFn fn = nullptr;
+    static std::once_flag once;
+    std::call_once(once, [] {
+        void *p = nullptr;
+        cudaDriverEntryPointQueryResult qres;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qres) == cudaSuccess &&
+            qres == cudaDriverEntryPointSuccess)
+            fn = reinterpret_cast<EncodeTiledFn>(p);
+    });
+    return fn;
+}
+
+// 2-D fp16 K-major operand: dims (K, rows), row pitch ld elements, box (64, box_rows), 128-byte swizzle
+int make_map(CUtensorMap *map, const __half *ptr, int K, int rows, int ld, int box_rows)
+{
+    EncodeTiledFn fn = get_encode_fn();
+    UMX_CHECK(fn != nullptr, "cuTensorMapEncodeTiled is not available from the CUDA driver");
+    UMX_CHECK((reinterpret_cast<uintptr_t>(ptr) & 15) == 0 && (ld % 8) == 0, "GEMM operand must be 16-byte aligned with a 16-byte row pitch");
+    const cuuint64_t dims[2] = {(cuuint64_t)K, (cuuint64_t)rows};
+    const cuuint64_t strides[1] = {(cuuint64_t)ld * 2};
+    const cuuint32_t box[2] = {(cuuint32_t)BK, (cuuint32_t)box_rows};
+    const cuuint32_t estr[2] = {1, 1};
+    const CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, const_cast<__half *>(ptr), dims, strides, box, estr,
+                          CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                          CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS)
+    {
+        set_error("cuTensorMapEncodeTiled failed with CUresult " + std::to_string((int)r));
+        return -1;
+    }
+    return 0;
+}
+} // namespace
+
+int launch_gemm_tc(const GemmBatch &batch, int terms, cudaStream_t st)
+{
+    UMX_CHECK(batch.count >= 1 && batch.count <= kMaxGemmProblems, "gemm_tc: bad problem count");
+    UMX_CHECK(terms >= 1 && terms <= 3, "gemm_tc: terms must be 1..3");
+    TcParams P;
+    std::memset(&P, 0, sizeof P);
+    P.count = batch.count;
+    P.terms = terms;
+    int tiles = 0;
+    for (int i = 0; i < batch.count; ++i)
+    {
+        const GemmProblem &g = batch.p[i];
+        UMX_CHECK(g.M > 0 && g.N > 0 && g.K > 0, "gemm_tc: empty problem");
+        UMX_CHECK(g.A.lo != nullptr && g.B.lo != nullptr, "gemm_tc: operands need hi and lo planes");
+        if (make_map(&P.a_hi[i], g.A.hi, g.K, g.M, g.A.ld, BM) || make_map(&P.a_lo[i], g.A.lo, g.K, g.M, g.A.ld, BM) ||
+            make_map(&P.b_hi[i], g.B.hi, g.K, g.N, g.B.ld, BN) || make_map(&P.b_lo[i], g.B.lo, g.K, g.N, g.B.ld, BN))
+            return -1;
+        TcProblem &p = P.p[i];
+        p.M = g.M;
+        p.N = g.N;
+        p.K = g.K;
+        p.act = g.act;
+        p.alpha = g.alpha;
+        p.beta = g.beta;
+        p.out_f32 = g.out_f32;
+        p.out_hi = g.out_hi;
+        p.out_lo = g.out_lo;
+        p.ldo = g.ldo;
+        p.n_group = g.n_group;
+        p.group_stride = g.group_stride;
+        p.m_tiles = ceil_div(g.M, BM);
+        p.n_tiles = ceil_div(g.N, BN);
+        p.tile_begin = tiles;
+        tiles += p.m_tiles * p.n_tiles;
+    }
+    P.total_tiles = tiles;
+
+    static int sm_count[64] = {};
+    static bool attr_set[64] = {};
+    int dev = 0;
+    UMX_CUDA_OK(cudaGetDevice(&dev));
+    dev &= 63;
+    if (!attr_set[dev])
+    {
+        UMX_CUDA_OK(cudaFuncSetAttribute(gemm_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
+        UMX_CUDA_OK(cudaDeviceGetAttribute(&sm_count[dev], cudaDevAttrMultiProcessorCount, dev));
+        attr_set[dev] = true;
+    }
+    const int grid = std::min(tiles, sm_count[dev]);
+    gemm_tc_kernel<<<grid, kThreads, kSmemBytes, st>>>(P);
+    UMX_CUDA_OK(cudaGetLastError());
+    return 0;
+}
+
+} // namespace umx

@@ -1,0 +1,149 @@
+// Internal kernel interfaces of the demixing path (device pointers, explicit stream).
+#pragma once
+#include "common.cuh"
+
+namespace umx
+{
+
+// ---- stft.cu -------------------------------------------------------------------------------------
+struct StftTrack
+{
+    const float2 *audio; // interleaved stereo source track (device)
+    long n_src;          // samples in the source track
+    long src_shift;      // source index of chunk sample 0 (segment offset - shift offset; may be < 0)
+    int n_valid;         // chunk length; samples >= n_valid of the n_buf window are zero
+    int pad_;
+};
+
+struct IstftTrack
+{
+    float2 *out;          // chunk output, or the track accumulator when accumulate != 0
+    long out_stem_stride; // float2 elements between stems
+    long out_offset;      // segment offset inside the accumulator
+    int n_wave;           // samples to emit (chunk length)
+    int accumulate;       // 1: out[off+k] += w[k]*y[k] (umx.cpp:234-249), 0: plain store
+};
+
+constexpr int kIstftFramesPerCta = 16;
+
+int init_fft_tables(int device);
+int launch_stft(const StftTrack *d_tracks, int n_tracks, int n_buf, float2 *spec, __half *xh, __half *xl,
+                float *maxabs, cudaStream_t st);
+int launch_istft(const float2 *stems, long stem_stride, int n_stems, const IstftTrack *d_tracks, int n_tracks,
+                 int n_buf, cudaStream_t st);
+int launch_finalize(const float2 *acc, long L, float2 *out, long n, int shift, int n_buf, int stride, int n_stems,
+                    cudaStream_t st);
+int launch_to_ref_layout_c64(const float2 *in, float2 *out, int F, cudaStream_t st);
+int launch_from_ref_layout_c64(const float2 *in, float2 *out, int F, cudaStream_t st);
+int launch_to_ref_layout_f32(const float *in, float *out, int F, cudaStream_t st);
+int launch_from_ref_layout_f32(const float *in, float *out, int F, cudaStream_t st);
+
+// ---- gemm ----------------------------------------------------------------------------------------
+// C[m, n] = act(alpha[n] * sum_k A[m,k] * B[n,k] + beta[n]);  A, B are fp16 (hi, lo) plane pairs, K-major.
+enum GemmAct
+{
+    kActNone = 0,
+    kActTanh = 1,
+    kActRelu = 2
+};
+
+struct GemmOperand
+{
+    const __half *hi;
+    const __half *lo;
+    int ld; // elements between rows
+    int pad_;
+};
+
+struct GemmProblem
+{
+    GemmOperand A; // (M, K)
+    GemmOperand B; // (N, K)
+    int M, N, K;
+    int act;
+    const float *alpha; // per output column (may be null = 1)
+    const float *beta;  // per output column (may be null = 0)
+    // output: column n goes to group g = n / n_group at  base + g*group_stride + m*ldo + n % n_group
+    float *out_f32;  // fp32 output (or null)
+    __half *out_hi;  // fp16 plane pair output (or null)
+    __half *out_lo;
+    int ldo;
+    int n_group;
+    long group_stride;
+};
+
+constexpr int kMaxGemmProblems = 4;
+struct GemmBatch
+{
+    GemmProblem p[kMaxGemmProblems];
+    int count;
+};
+
+int launch_gemm_simt(const GemmBatch &batch, cudaStream_t st);
+// terms: 1 = A_hi*B_hi ; 2 = + A_lo*B_hi ; 3 = + A_hi*B_lo
+int launch_gemm_tc(const GemmBatch &batch, int terms, cudaStream_t st);
+
+// ---- lstm ----------------------------------------------------------------------------------------
+struct LstmLayerArgs
+{
+    // per target: W_hh as [k][unit][gate] uint8 + its (scale, offset)
+    const uint8_t *whh_q[kTargets][2];
+    float whh_scale[kTargets][2];
+    float whh_offset[kTargets][2];
+    const float *xproj;    // [target][M][2*4*Hh] : W_ih x + b_ih + b_hh, gate order i,f,g,o per direction
+    long xproj_target_stride;
+    float *h_state;        // [track][target][dir][Hh] for this layer
+    float *c_state;
+    long state_track_stride; // floats between tracks
+    __half *out_hi;        // [target][M][ldo] + col_offset + dir*Hh + unit
+    __half *out_lo;
+    long out_target_stride;
+    int ldo;
+    int col_offset;
+    float *out_f32;        // optional [target][M][2*Hh]
+    long out_f32_target_stride;
+    int F;                 // frames per track
+    int Hh;                // hidden units per direction
+    int n_tracks;
+    int target_begin, target_count;
+};
+int launch_lstm_simple(const LstmLayerArgs &a, cudaStream_t st);
+
+// ---- wiener --------------------------------------------------------------------------------------
+struct WienerArgs
+{
+    const float2 *spec;   // [M][2][2049]
+    const float *mask;    // [4][M][ld] (ld = kMaskLd), or target magnitudes when mask_is_mag
+    long mask_target_stride;
+    int mask_ld;
+    int mask_is_mag;      // 1: inputs are |Y_j| (kernel-level API), 0: inputs are the masks
+    const float *maxabs;  // [track] max |X|
+    float *partials;      // [track][chunks][2049][20]
+    float *stats;         // [track][2049][16]
+    float2 *out;          // [4][M][2][2049]
+    long out_stem_stride;
+    float2 *mix_out;      // optional: mix / max_abs (the reference mutates its argument)
+    int F;
+    int n_tracks;
+};
+constexpr int kWienerChunks = 19;
+int launch_wiener(const WienerArgs &a, cudaStream_t st);
+
+// ---- model prep ----------------------------------------------------------------------------------
+int launch_dequant_u8(const uint8_t *q, float scale, float offset, float *out, long n, cudaStream_t st);
+int launch_dequant_u16(const uint16_t *q, float scale, float offset, float *out, long n, cudaStream_t st);
+// planes[n][k] = split(W[n][k] * (kscale ? kscale[k % kscale_mod] : 1)), zero padded to (n_pad, ld)
+int launch_make_planes(const float *w, int N, int K, const float *kscale, int kscale_mod, __half *hi, __half *lo,
+                       int n_pad, int ld, cudaStream_t st);
+// out[n] = sum_k v[k % vmod] * W[n][k]
+int launch_row_dot(const float *w, int N, int K, const float *v, int vmod, float *out, cudaStream_t st);
+// whh_q [4*Hh][Hh] (PyTorch rows = gates i,f,g,o) -> [k][unit][gate]
+int launch_pack_whh(const uint8_t *q, int Hh, uint8_t *out, cudaStream_t st);
+// fp32 (F, H) column-major <-> fp16 plane pair row-major with pitch ld
+int launch_colmajor_to_planes(const float *in, int F, int H, __half *hi, __half *lo, int ld, cudaStream_t st);
+int launch_rowmajor_to_colmajor(const float *in, int F, int H, int ld, float *out, cudaStream_t st);
+// mags[c][f][b] = mask[f][c*2049+b] * |spec[f][c][b]|  (src/inference.cpp:173-185), internal layouts
+int launch_spec_to_x(const float2 *spec, long M, __half *xh, __half *xl, cudaStream_t st);
+int launch_mask_to_mag(const float *mask, int ld, const float2 *spec, float *mag, long M, cudaStream_t st);
+
+} // namespace umx

@@ -1,0 +1,520 @@
+// Host orchestration of the demixing path: umx_inference (src/inference.cpp:12-207) and
+// shift_inference / split_inference (umx.cpp:99-295) as stream-ordered kernel launches.
+#include "session.h"
+
+#include <algorithm>
+#include <cstring>
+
+namespace umx
+{
+
+namespace
+{
+template <typename T>
+int salloc(Session *s, T **p, size_t count, bool zero = false)
+{
+    void *q = nullptr;
+    UMX_CUDA_OK(cudaMalloc(&q, std::max<size_t>(count, 1) * sizeof(T)));
+    s->allocs.push_back(q);
+    if (zero)
+        UMX_CUDA_OK(cudaMemset(q, 0, std::max<size_t>(count, 1) * sizeof(T)));
+    *p = static_cast<T *>(q);
+    return 0;
+}
+} // namespace
+
+// ---- measurement -----------------------------------------------------------------------------------
+StageScope::StageScope(Session *s_, const char *stage) : s(s_)
+{
+    if (!s->profiling)
+        return;
+    StageTimer t;
+    t.stage = stage;
+    cudaEventCreate(&t.a);
+    cudaEventCreate(&t.b);
+    cudaEventRecord(t.a, s->st);
+    s->timers.push_back(t);
+    idx = (int)s->timers.size() - 1;
+}
+StageScope::~StageScope()
+{
+    if (idx >= 0)
+        cudaEventRecord(s->timers[idx].b, s->st);
+}
+
+void session_begin_profile(Session *s)
+{
+    s->launches = 0;
+    s->stage_ms.clear();
+    for (auto &t : s->timers)
+    {
+        cudaEventDestroy(t.a);
+        cudaEventDestroy(t.b);
+    }
+    s->timers.clear();
+}
+
+int session_end_profile(Session *s)
+{
+    if (!s->profiling)
+        return 0;
+    UMX_CUDA_OK(cudaStreamSynchronize(s->st));
+    for (auto &t : s->timers)
+    {
+        float ms = 0.f;
+        UMX_CUDA_OK(cudaEventElapsedTime(&ms, t.a, t.b));
+        s->stage_ms[t.stage] += ms;
+    }
+    return 0;
+}
+
+// ---- lifetime ----------------------------------------------------------------------------------------
+int session_create(Model *m, int max_tracks, int n_buf, Session **out)
+{
+    UMX_CHECK(m != nullptr && out != nullptr, "session_create: null argument");
+    UMX_CHECK(max_tracks >= 1 && max_tracks <= 1024, "session_create: max_tracks must be in [1,1024]");
+    UMX_CHECK(n_buf >= kNfft && n_buf % 2 == 0, "session_create: n_buf must be even and >= 4096");
+    UMX_CUDA_OK(cudaSetDevice(m->device));
+    if (int rc = init_fft_tables(m->device))
+        return rc;
+    Session *s = new Session();
+    s->m = m;
+    s->device = m->device;
+    s->T = max_tracks;
+    s->n_buf = n_buf;
+    s->F = n_buf / kHop + 1;
+    s->H = m->hidden;
+    s->Hh = m->hidden / 2;
+    s->Mcap = (long)s->T * s->F;
+    const size_t M = (size_t)s->Mcap, H = (size_t)s->H;
+    auto fail = [&](int rc) {
+        session_destroy(s);
+        return rc;
+    };
+    if (cudaStreamCreateWithFlags(&s->st, cudaStreamNonBlocking) != cudaSuccess)
+    {
+        set_error("session_create: cudaStreamCreate failed");
+        return fail(-1);
+    }
+    int rc = 0;
+    rc |= salloc(s, &s->spec, M * 2 * kBins);
+    rc |= salloc(s, &s->xh, M * kFc1InPad, true); // pad columns stay zero
+    rc |= salloc(s, &s->xl, M * kFc1InPad, true);
+    rc |= salloc(s, &s->act_h, 4 * M * 2 * H);
+    rc |= salloc(s, &s->act_l, 4 * M * 2 * H);
+    for (int i = 0; i < 2; ++i)
+    {
+        rc |= salloc(s, &s->lb_h[i], 4 * M * H);
+        rc |= salloc(s, &s->lb_l[i], 4 * M * H);
+    }
+    rc |= salloc(s, &s->xproj, 4 * M * 4 * H);
+    rc |= salloc(s, &s->fc2_h, 4 * M * H);
+    rc |= salloc(s, &s->fc2_l, 4 * M * H);
+    rc |= salloc(s, &s->mask, 4 * M * kMaskLd);
+    rc |= salloc(s, &s->stems, 4 * M * 2 * kBins);
+    rc |= salloc(s, &s->maxabs, (size_t)s->T, true);
+    rc |= salloc(s, &s->partials, (size_t)s->T * kWienerChunks * 20 * kBins);
+    rc |= salloc(s, &s->stats, (size_t)s->T * 16 * kBins);
+    rc |= salloc(s, &s->h_state, (size_t)s->T * 3 * 8 * s->Hh, true);
+    rc |= salloc(s, &s->c_state, (size_t)s->T * 3 * 8 * s->Hh, true);
+    if (rc)
+        return fail(-1);
+    s->acc_pool.assign(s->T, nullptr);
+    s->in_pool.assign(s->T, nullptr);
+    s->out_pool.assign(s->T, nullptr);
+    s->acc_cap.assign(s->T, 0);
+    s->in_cap.assign(s->T, 0);
+    s->out_cap.assign(s->T, 0);
+    if (ensure_desc_capacity(s, 16))
+        return fail(-1);
+    *out = s;
+    return 0;
+}
+
+int ensure_desc_capacity(Session *s, int segs)
+{
+    if (segs <= s->seg_cap)
+        return 0;
+    if (s->d_stft)
+        cudaFree(s->d_stft);
+    if (s->d_istft)
+        cudaFree(s->d_istft);
+    s->d_stft = nullptr;
+    s->d_istft = nullptr;
+    s->seg_cap = 0;
+    UMX_CUDA_OK(cudaMalloc(&s->d_stft, sizeof(StftTrack) * (size_t)segs * s->T));
+    UMX_CUDA_OK(cudaMalloc(&s->d_istft, sizeof(IstftTrack) * (size_t)segs * s->T));
+    s->seg_cap = segs;
+    return 0;
+}
+
+void session_destroy(Session *s)
+{
+    if (!s)
+        return;
+    cudaSetDevice(s->device);
+    if (s->st)
+        cudaStreamSynchronize(s->st);
+    session_begin_profile(s);
+    for (void *p : s->allocs)
+        cudaFree(p);
+    for (auto *p : s->acc_pool)
+        cudaFree(p);
+    for (auto *p : s->in_pool)
+        cudaFree(p);
+    for (auto *p : s->out_pool)
+        cudaFree(p);
+    cudaFree(s->d_stft);
+    cudaFree(s->d_istft);
+    if (s->st)
+        cudaStreamDestroy(s->st);
+    delete s;
+}
+
+int session_reset(Session *s)
+{
+    UMX_CUDA_OK(cudaSetDevice(s->device));
+    const size_t n = sizeof(float) * (size_t)s->T * 3 * 8 * s->Hh;
+    UMX_CUDA_OK(cudaMemsetAsync(s->h_state, 0, n, s->st));
+    UMX_CUDA_OK(cudaMemsetAsync(s->c_state, 0, n, s->st));
+    return 0;
+}
+
+// ---- the network (src/inference.cpp:58-186) ------------------------------------------------------------
+static int run_gemm(Session *s, const GemmBatch &b)
+{
+    s->launches++;
+    if (s->gemm_impl == 1)
+        return launch_gemm_simt(b, s->st);
+    return launch_gemm_tc(b, s->gemm_terms, s->st);
+}
+
+int session_lstm(Session *s, int n_tracks, int target_begin, int target_count, bool want_f32)
+{
+    const int H = s->H, Hh = s->Hh;
+    const long M = (long)n_tracks * s->F, Mc = s->Mcap;
+    Model *m = s->m;
+    for (int l = 0; l < 3; ++l)
+    {
+        {
+            StageScope sc(s, "gemm");
+            GemmBatch b{};
+            b.count = target_count;
+            for (int i = 0; i < target_count; ++i)
+            {
+                const int t = target_begin + i;
+                GemmProblem &p = b.p[i];
+                if (l == 0)
+                    p.A = {s->act_h + (size_t)t * Mc * 2 * H, s->act_l + (size_t)t * Mc * 2 * H, 2 * H, 0};
+                else
+                    p.A = {s->lb_h[(l - 1) & 1] + (size_t)t * Mc * H, s->lb_l[(l - 1) & 1] + (size_t)t * Mc * H, H, 0};
+                p.B = {m->t[t].wih_hi[l], m->t[t].wih_lo[l], H, 0};
+                p.M = (int)M;
+                p.N = 4 * H;
+                p.K = H;
+                p.act = kActNone;
+                p.alpha = nullptr;
+                p.beta = m->t[t].wih_beta[l];
+                p.out_f32 = s->xproj + (size_t)t * Mc * 4 * H;
+                p.ldo = 4 * H;
+                p.n_group = 4 * H;
+                p.group_stride = 0;
+            }
+            if (int rc = run_gemm(s, b))
+                return rc;
+        }
+        StageScope sc(s, "lstm");
+        LstmLayerArgs a{};
+        for (int t = 0; t < kTargets; ++t)
+            for (int d = 0; d < 2; ++d)
+            {
+                a.whh_q[t][d] = m->t[t].whh_q[l][d];
+                a.whh_scale[t][d] = m->t[t].whh_scale[l][d];
+                a.whh_offset[t][d] = m->t[t].whh_offset[l][d];
+            }
+        a.xproj = s->xproj;
+        a.xproj_target_stride = Mc * 4 * H;
+        a.h_state = s->h_state + (size_t)l * 8 * Hh;
+        a.c_state = s->c_state + (size_t)l * 8 * Hh;
+        a.state_track_stride = 3 * 8 * Hh;
+        if (l < 2)
+        {
+            a.out_hi = s->lb_h[l & 1];
+            a.out_lo = s->lb_l[l & 1];
+            a.out_target_stride = Mc * H;
+            a.ldo = H;
+            a.col_offset = 0;
+        }
+        else
+        {
+            a.out_hi = s->act_h;
+            a.out_lo = s->act_l;
+            a.out_target_stride = Mc * 2 * H;
+            a.ldo = 2 * H;
+            a.col_offset = H;
+        }
+        a.out_f32 = (want_f32 && l == 2) ? s->lstm_f32 : nullptr;
+        a.out_f32_target_stride = Mc * H;
+        a.F = s->F;
+        a.Hh = Hh;
+        a.n_tracks = n_tracks;
+        a.target_begin = target_begin;
+        a.target_count = target_count;
+        s->launches++;
+        if (int rc = launch_lstm_simple(a, s->st))
+            return rc;
+    }
+    return 0;
+}
+
+int session_network(Session *s, int n_tracks)
+{
+    const int H = s->H;
+    const long M = (long)n_tracks * s->F, Mc = s->Mcap;
+    Model *m = s->m;
+    { // fc1 + BN1 + tanh for all four targets in one GEMM (inference.cpp:75-99)
+        StageScope sc(s, "gemm");
+        GemmBatch b{};
+        b.count = 1;
+        GemmProblem &p = b.p[0];
+        p.A = {s->xh, s->xl, kFc1InPad, 0};
+        p.B = {m->fc1_hi, m->fc1_lo, kFc1InPad, 0};
+        p.M = (int)M;
+        p.N = 4 * H;
+        p.K = kFc1InPad;
+        p.act = kActTanh;
+        p.alpha = m->fc1_alpha;
+        p.beta = m->fc1_beta;
+        p.out_hi = s->act_h;
+        p.out_lo = s->act_l;
+        p.ldo = 2 * H;
+        p.n_group = H;
+        p.group_stride = Mc * 2 * H;
+        if (int rc = run_gemm(s, b))
+            return rc;
+    }
+    if (int rc = session_lstm(s, n_tracks, 0, kTargets, false))
+        return rc;
+    StageScope sc(s, "gemm");
+    { // skip concat + fc2 + BN2 + ReLU (inference.cpp:118-140)
+        GemmBatch b{};
+        b.count = kTargets;
+        for (int t = 0; t < kTargets; ++t)
+        {
+            GemmProblem &p = b.p[t];
+            p.A = {s->act_h + (size_t)t * Mc * 2 * H, s->act_l + (size_t)t * Mc * 2 * H, 2 * H, 0};
+            p.B = {m->t[t].fc2_hi, m->t[t].fc2_lo, 2 * H, 0};
+            p.M = (int)M;
+            p.N = H;
+            p.K = 2 * H;
+            p.act = kActRelu;
+            p.alpha = m->t[t].fc2_alpha;
+            p.beta = m->t[t].fc2_beta;
+            p.out_hi = s->fc2_h + (size_t)t * Mc * H;
+            p.out_lo = s->fc2_l + (size_t)t * Mc * H;
+            p.ldo = H;
+            p.n_group = H;
+            p.group_stride = 0;
+        }
+        if (int rc = run_gemm(s, b))
+            return rc;
+    }
+    { // fc3 + BN3 + output affine + ReLU -> mask (inference.cpp:143-166)
+        GemmBatch b{};
+        b.count = kTargets;
+        for (int t = 0; t < kTargets; ++t)
+        {
+            GemmProblem &p = b.p[t];
+            p.A = {s->fc2_h + (size_t)t * Mc * H, s->fc2_l + (size_t)t * Mc * H, H, 0};
+            p.B = {m->t[t].fc3_hi, m->t[t].fc3_lo, H, 0};
+            p.M = (int)M;
+            p.N = kFc3Out;
+            p.K = H;
+            p.act = kActRelu;
+            p.alpha = m->t[t].fc3_alpha;
+            p.beta = m->t[t].fc3_beta;
+            p.out_f32 = s->mask + (size_t)t * Mc * kMaskLd;
+            p.ldo = kMaskLd;
+            p.n_group = kMaskLd;
+            p.group_stride = 0;
+        }
+        if (int rc = run_gemm(s, b))
+            return rc;
+    }
+    return 0;
+}
+
+int session_run_segment(Session *s, int seg, int n_tracks)
+{
+    const StftTrack *dst = s->d_stft + (size_t)seg * s->T;
+    const IstftTrack *dis = s->d_istft + (size_t)seg * s->T;
+    {
+        StageScope sc(s, "stft");
+        UMX_CUDA_OK(cudaMemsetAsync(s->maxabs, 0, sizeof(float) * s->T, s->st));
+        s->launches++;
+        if (int rc = launch_stft(dst, n_tracks, s->n_buf, s->spec, s->xh, s->xl, s->maxabs, s->st))
+            return rc;
+    }
+    if (int rc = session_network(s, n_tracks))
+        return rc;
+    {
+        StageScope sc(s, "wiener");
+        WienerArgs w{};
+        w.spec = s->spec;
+        w.mask = s->mask;
+        w.mask_target_stride = s->Mcap * kMaskLd;
+        w.mask_ld = kMaskLd;
+        w.mask_is_mag = 0;
+        w.maxabs = s->maxabs;
+        w.partials = s->partials;
+        w.stats = s->stats;
+        w.out = s->stems;
+        w.out_stem_stride = s->Mcap * 2 * kBins;
+        w.mix_out = nullptr;
+        w.F = s->F;
+        w.n_tracks = n_tracks;
+        s->launches += 3;
+        if (int rc = launch_wiener(w, s->st))
+            return rc;
+    }
+    {
+        StageScope sc(s, "istft");
+        s->launches++;
+        if (int rc = launch_istft(s->stems, s->Mcap * 2 * kBins, 4, dis, n_tracks, s->n_buf, s->st))
+            return rc;
+    }
+    return 0;
+}
+
+// ---- umx_inference on host buffers (src/inference.cpp:12-207) ------------------------------------------
+static int grow(float2 **p, long *cap, long need)
+{
+    if (need <= *cap)
+        return 0;
+    if (*p)
+        cudaFree(*p);
+    *p = nullptr;
+    *cap = 0;
+    UMX_CUDA_OK(cudaMalloc(p, sizeof(float2) * (size_t)need));
+    *cap = need;
+    return 0;
+}
+
+int session_infer_segment(Session *s, const float *audio, int n, float *out)
+{
+    UMX_CHECK(n >= 0 && n <= s->n_buf, "umx_cuda_infer_segment: n must be in [0, n_buf]");
+    UMX_CUDA_OK(cudaSetDevice(s->device));
+    session_begin_profile(s);
+    if (grow(&s->in_pool[0], &s->in_cap[0], std::max(n, 1)) || grow(&s->out_pool[0], &s->out_cap[0], 4L * std::max(n, 1)))
+        return -1;
+    {
+        StageScope sc(s, "h2d");
+        UMX_CUDA_OK(cudaMemcpyAsync(s->in_pool[0], audio, sizeof(float2) * (size_t)n, cudaMemcpyHostToDevice, s->st));
+    }
+    StftTrack a{s->in_pool[0], n, 0, n, 0};
+    IstftTrack b{s->out_pool[0], n, 0, n, 0};
+    UMX_CUDA_OK(cudaMemcpyAsync(s->d_stft, &a, sizeof a, cudaMemcpyHostToDevice, s->st));
+    UMX_CUDA_OK(cudaMemcpyAsync(s->d_istft, &b, sizeof b, cudaMemcpyHostToDevice, s->st));
+    UMX_CUDA_OK(cudaStreamSynchronize(s->st)); // descriptors live on this stack frame
+    if (int rc = session_run_segment(s, 0, 1))
+        return rc;
+    {
+        StageScope sc(s, "d2h");
+        UMX_CUDA_OK(cudaMemcpyAsync(out, s->out_pool[0], sizeof(float2) * 4 * (size_t)n, cudaMemcpyDeviceToHost, s->st));
+    }
+    UMX_CUDA_OK(cudaStreamSynchronize(s->st));
+    return session_end_profile(s);
+}
+
+// ---- shift_inference + split_inference (umx.cpp:99-295) ------------------------------------------------
+static int stride_of(int n_buf) { return (int)((1 - 0.25f) * n_buf); } // umx.cpp:180
+
+int session_demix_device(Session *s, const float *const *d_audio, const int64_t *n_samples, int n_tracks,
+                         int shift_offset, float *const *d_out)
+{
+    UMX_CHECK(n_tracks >= 1 && n_tracks <= s->T, "umx_cuda_demix: n_tracks must be in [1, max_tracks]");
+    UMX_CHECK(shift_offset >= 0 && shift_offset < kMaxShift, "umx_cuda_demix: shift_offset must be in [0, 22050)");
+    UMX_CUDA_OK(cudaSetDevice(s->device));
+    const int stride = stride_of(s->n_buf);
+    std::vector<long> L(n_tracks);
+    int max_segs = 0;
+    for (int i = 0; i < n_tracks; ++i)
+    {
+        UMX_CHECK(n_samples[i] >= 0 && n_samples[i] < (1LL << 40), "umx_cuda_demix: bad track length");
+        L[i] = (long)n_samples[i] + kMaxShift - shift_offset; // umx.cpp:120-121
+        max_segs = std::max(max_segs, (int)((L[i] + stride - 1) / stride)); // offsets 0, stride, ... < L
+    }
+    if (ensure_desc_capacity(s, max_segs))
+        return -1;
+    if (int rc = session_reset(s)) // a fresh create_lstm_data per track (umx.cpp:167-171)
+        return rc;
+    // descriptors for every (segment, track); tracks that have ended run an empty chunk
+    std::vector<StftTrack> hs((size_t)max_segs * s->T);
+    std::vector<IstftTrack> hi((size_t)max_segs * s->T);
+    for (int i = 0; i < n_tracks; ++i)
+    {
+        if (grow(&s->acc_pool[i], &s->acc_cap[i], 4 * L[i]))
+            return -1;
+        UMX_CUDA_OK(cudaMemsetAsync(s->acc_pool[i], 0, sizeof(float2) * 4 * (size_t)L[i], s->st));
+        for (int sg = 0; sg < max_segs; ++sg)
+        {
+            const long off = (long)sg * stride;
+            const int clen = off < L[i] ? (int)std::min<long>(s->n_buf, L[i] - off) : 0; // umx.cpp:217-218
+            hs[(size_t)sg * s->T + i] = {reinterpret_cast<const float2 *>(d_audio[i]), (long)n_samples[i],
+                                         off - shift_offset, clen, 0};
+            hi[(size_t)sg * s->T + i] = {s->acc_pool[i], L[i], off, clen, 1};
+        }
+    }
+    UMX_CUDA_OK(cudaMemcpyAsync(s->d_stft, hs.data(), sizeof(StftTrack) * hs.size(), cudaMemcpyHostToDevice, s->st));
+    UMX_CUDA_OK(cudaMemcpyAsync(s->d_istft, hi.data(), sizeof(IstftTrack) * hi.size(), cudaMemcpyHostToDevice, s->st));
+    UMX_CUDA_OK(cudaStreamSynchronize(s->st)); // hs/hi are pageable host vectors
+    for (int sg = 0; sg < max_segs; ++sg) // sequential: h/c stream from segment to segment
+        if (int rc = session_run_segment(s, sg, n_tracks))
+            return rc;
+    {
+        StageScope sc(s, "finalize");
+        for (int i = 0; i < n_tracks; ++i)
+        {
+            s->launches++;
+            if (int rc = launch_finalize(s->acc_pool[i], L[i], reinterpret_cast<float2 *>(d_out[i]), (long)n_samples[i],
+                                         shift_offset, s->n_buf, stride, 4, s->st))
+                return rc;
+        }
+    }
+    return 0;
+}
+
+int session_demix_host(Session *s, const float *const *audio, const int64_t *n_samples, int n_tracks, int shift_offset,
+                       float *const *out)
+{
+    UMX_CHECK(n_tracks >= 1 && n_tracks <= s->T, "umx_cuda_demix: n_tracks must be in [1, max_tracks]");
+    UMX_CUDA_OK(cudaSetDevice(s->device));
+    session_begin_profile(s);
+    std::vector<const float *> din(n_tracks);
+    std::vector<float *> dout(n_tracks);
+    {
+        StageScope sc(s, "h2d");
+        for (int i = 0; i < n_tracks; ++i)
+        {
+            const long n = std::max<long>((long)n_samples[i], 1);
+            if (grow(&s->in_pool[i], &s->in_cap[i], n) || grow(&s->out_pool[i], &s->out_cap[i], 4 * n))
+                return -1;
+            UMX_CUDA_OK(cudaMemcpyAsync(s->in_pool[i], audio[i], sizeof(float2) * (size_t)n_samples[i],
+                                        cudaMemcpyHostToDevice, s->st));
+            din[i] = reinterpret_cast<const float *>(s->in_pool[i]);
+            dout[i] = reinterpret_cast<float *>(s->out_pool[i]);
+        }
+    }
+    if (int rc = session_demix_device(s, din.data(), n_samples, n_tracks, shift_offset, dout.data()))
+        return rc;
+    {
+        StageScope sc(s, "d2h");
+        for (int i = 0; i < n_tracks; ++i)
+            UMX_CUDA_OK(cudaMemcpyAsync(out[i], s->out_pool[i], sizeof(float2) * 4 * (size_t)n_samples[i],
+                                        cudaMemcpyDeviceToHost, s->st));
+    }
+    UMX_CUDA_OK(cudaStreamSynchronize(s->st));
+    return session_end_profile(s);
+}
+
+} // namespace umx

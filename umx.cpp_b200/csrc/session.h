@@ -1,0 +1,87 @@
+// Per-track streaming state and work buffers for up to T tracks demixed in lockstep
+// (replaces lstm_data src/lstm.hpp:10-16, stft_buffers src/dsp.hpp:21-59 and the temporaries of
+// umx_inference src/inference.cpp:12-207).
+#pragma once
+#include "kernels.cuh"
+#include "model.h"
+#include <map>
+#include <string>
+#include <vector>
+
+namespace umx
+{
+
+struct StageTimer
+{
+    std::string stage;
+    cudaEvent_t a, b;
+};
+
+struct Session
+{
+    Model *m = nullptr;
+    int device = 0;
+    int T = 1;      // max tracks in lockstep
+    int n_buf = 0;  // samples per segment window
+    int F = 0;      // frames per window
+    int H = 0, Hh = 0;
+    long Mcap = 0;  // T * F rows
+    cudaStream_t st = nullptr;
+
+    // activations (HBM layout documented in DESIGN.md)
+    float2 *spec = nullptr;                  // [Mcap][2][2049]
+    __half *xh = nullptr, *xl = nullptr;     // [Mcap][2976]
+    __half *act_h = nullptr, *act_l = nullptr; // [4][Mcap][2H]  (fc1 out | lstm out)
+    __half *lb_h[2] = {}, *lb_l[2] = {};     // [4][Mcap][H] ping-pong LSTM layer outputs
+    float *xproj = nullptr;                  // [4][Mcap][4H]
+    __half *fc2_h = nullptr, *fc2_l = nullptr; // [4][Mcap][H]
+    float *mask = nullptr;                   // [4][Mcap][kMaskLd]
+    float2 *stems = nullptr;                 // [4][Mcap][2][2049]
+    float *maxabs = nullptr;                 // [T]
+    float *partials = nullptr, *stats = nullptr;
+    float *h_state = nullptr, *c_state = nullptr; // [T][3][4][2][Hh]
+    float *lstm_f32 = nullptr;               // optional fp32 LSTM output (kernel-level API), [4][Mcap][H]
+
+    StftTrack *d_stft = nullptr;   // descriptor arrays [seg_cap][T]
+    IstftTrack *d_istft = nullptr;
+    int seg_cap = 0;
+
+    // grow-only pools for whole-track demixing
+    std::vector<float2 *> acc_pool, in_pool, out_pool;
+    std::vector<long> acc_cap, in_cap, out_cap;
+
+    std::vector<void *> allocs;
+    // options
+    int gemm_impl = 0, gemm_terms = 3, lstm_impl = 1;
+    // measurement
+    bool profiling = false;
+    std::vector<StageTimer> timers;
+    std::map<std::string, double> stage_ms;
+    long launches = 0;
+};
+
+int session_create(Model *m, int max_tracks, int n_buf, Session **out);
+void session_destroy(Session *s);
+int session_reset(Session *s);
+// one lockstep pass over descriptor row `seg` for n_tracks tracks (stft .. istft)
+int session_run_segment(Session *s, int seg, int n_tracks);
+int session_network(Session *s, int n_tracks);
+int session_lstm(Session *s, int n_tracks, int target_begin, int target_count, bool want_f32);
+int session_demix_device(Session *s, const float *const *d_audio, const int64_t *n_samples, int n_tracks,
+                         int shift_offset, float *const *d_out);
+int session_demix_host(Session *s, const float *const *audio, const int64_t *n_samples, int n_tracks,
+                       int shift_offset, float *const *out);
+int session_infer_segment(Session *s, const float *audio, int n, float *out);
+void session_begin_profile(Session *s);
+int session_end_profile(Session *s);
+int ensure_desc_capacity(Session *s, int segs);
+
+struct StageScope
+{
+    Session *s;
+    int idx = -1;
+    StageScope(Session *s_, const char *stage);
+    ~StageScope();
+};
+
+} // namespace umx

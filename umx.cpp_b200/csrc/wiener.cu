@@ -1,0 +1,191 @@
+// Wiener-EM (reference: src/wiener.cpp:92-425, one EM iteration, whole-segment statistics).
+//
+// Three launches per segment batch, all bandwidth-bound, thread-per-bin so every global access is
+// coalesced along the bin axis of the internal [frame][channel][bin] layout:
+//   wiener_reduce    per (bin tile, frame chunk, track): partial sums over frames of y y^H (2x2, Hermitian:
+//                    R00, R11, Re/Im R01) and of the PSD v for each of the 4 sources  (wiener.cpp:181-258)
+//   wiener_finalize  fixed-order sum of the chunk partials, R = S / (eps + sum v)     (wiener.cpp:260-271)
+//   wiener_apply     per (frame, bin): v_j, Cxx = sum_j (sqrt(eps) I + v_j R_j) (regulariser added once PER
+//                    SOURCE, wiener.cpp:301-325), 2x2 inverse (:54-84), gain_j = v_j R_j Cxx^-1 (:335-375),
+//                    y_j = gain_j x (:380-401), times max_abs (:408-422)
+// The initial estimate is y_j = polar(mag_j, arg X)/max_abs (wiener.cpp:99-146).  In the pipeline
+// mag_j = mask_j |X| (inference.cpp:173-185), so y_j = mask_j X / max_abs and neither the magnitudes nor
+// the phase are materialised.  PSD quirk kept: v = sum_ch (re+im)^2 / 2 (wiener.cpp:187-202).
+#include "common.cuh"
+#include "kernels.cuh"
+
+namespace umx
+{
+
+constexpr int kWienerQ = 20;         // per source: S00, S11, Re S01, Im S01, V
+constexpr int kWienerApplyFrames = 16;
+
+__device__ __forceinline__ float wiener_max_abs(const float *maxabs, int trk)
+{
+    return fmaxf(1.0f, maxabs[trk] / kWienerScale); // wiener.cpp:36-52
+}
+
+// y_jc / max_abs for one channel
+__device__ __forceinline__ float2 initial_estimate(float m, float2 X, float ma, int is_mag)
+{
+    float2 y;
+    if (is_mag)
+    { // polar(mag, arg X): X == 0 has phase 0
+        const float ax = sqrtf(X.x * X.x + X.y * X.y);
+        y = ax > 0.f ? make_float2(m * (X.x / ax), m * (X.y / ax)) : make_float2(m, 0.f);
+    }
+    else
+        y = make_float2(m * X.x, m * X.y);
+    return make_float2(y.x / ma, y.y / ma);
+}
+
+__global__ void __launch_bounds__(256) wiener_reduce_kernel(const WienerArgs a)
+{
+    const int b = blockIdx.x * 256 + threadIdx.x;
+    const int chunk = blockIdx.y, trk = blockIdx.z;
+    if (b >= kBins)
+        return;
+    const int fc = (a.F + kWienerChunks - 1) / kWienerChunks;
+    const int f_begin = chunk * fc, f_end = min(a.F, f_begin + fc);
+    const float ma = wiener_max_abs(a.maxabs, trk);
+    float acc[kWienerQ];
+#pragma unroll
+    for (int i = 0; i < kWienerQ; ++i)
+        acc[i] = 0.f;
+    for (int f = f_begin; f < f_end; ++f)
+    {
+        const long row = (long)trk * a.F + f;
+        const float2 XL = a.spec[(row * 2 + 0) * kBins + b];
+        const float2 XR = a.spec[(row * 2 + 1) * kBins + b];
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+        {
+            const float *mk = a.mask + (long)j * a.mask_target_stride + row * a.mask_ld;
+            const float2 yL = initial_estimate(mk[b], XL, ma, a.mask_is_mag);
+            const float2 yR = initial_estimate(mk[kBins + b], XR, ma, a.mask_is_mag);
+            const float sL = yL.x + yL.y, sR = yR.x + yR.y;
+            acc[5 * j + 0] += yL.x * yL.x + yL.y * yL.y;
+            acc[5 * j + 1] += yR.x * yR.x + yR.y * yR.y;
+            acc[5 * j + 2] += yL.x * yR.x + yL.y * yR.y; // yL * conj(yR)
+            acc[5 * j + 3] += yL.y * yR.x - yL.x * yR.y;
+            acc[5 * j + 4] += (sL * sL + sR * sR) / 2.0f;
+        }
+    }
+    float *p = a.partials + ((long)trk * kWienerChunks + chunk) * kWienerQ * kBins + b;
+#pragma unroll
+    for (int i = 0; i < kWienerQ; ++i)
+        p[(long)i * kBins] = acc[i];
+}
+
+__global__ void __launch_bounds__(256) wiener_finalize_kernel(const WienerArgs a)
+{
+    const int b = blockIdx.x * 256 + threadIdx.x;
+    const int trk = blockIdx.y;
+    if (b >= kBins)
+        return;
+    const float *p = a.partials + (long)trk * kWienerChunks * kWienerQ * kBins + b;
+    float *s = a.stats + (long)trk * 16 * kBins + b;
+#pragma unroll
+    for (int j = 0; j < 4; ++j)
+    {
+        float q[5] = {0.f, 0.f, 0.f, 0.f, kWienerEps}; // weight starts at eps (wiener.cpp:210)
+        for (int c = 0; c < kWienerChunks; ++c)
+#pragma unroll
+            for (int i = 0; i < 5; ++i)
+                q[i] += p[((long)c * kWienerQ + 5 * j + i) * kBins];
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+            s[(long)(4 * j + i) * kBins] = q[i] / q[4];
+    }
+}
+
+__global__ void __launch_bounds__(256) wiener_apply_kernel(const WienerArgs a)
+{
+    const int b = blockIdx.x * 256 + threadIdx.x;
+    const int trk = blockIdx.z;
+    if (b >= kBins)
+        return;
+    const int f_begin = blockIdx.y * kWienerApplyFrames, f_end = min(a.F, f_begin + kWienerApplyFrames);
+    const float ma = wiener_max_abs(a.maxabs, trk);
+    const float reg = sqrtf(kWienerEps); // wiener.cpp:155-163
+    float R[16];
+    {
+        const float *s = a.stats + (long)trk * 16 * kBins + b;
+#pragma unroll
+        for (int i = 0; i < 16; ++i)
+            R[i] = s[(long)i * kBins];
+    }
+    for (int f = f_begin; f < f_end; ++f)
+    {
+        const long row = (long)trk * a.F + f;
+        const float2 XL = a.spec[(row * 2 + 0) * kBins + b];
+        const float2 XR = a.spec[(row * 2 + 1) * kBins + b];
+        const float2 x0 = make_float2(XL.x / ma, XL.y / ma); // wiener.cpp:118-129
+        const float2 x1 = make_float2(XR.x / ma, XR.y / ma);
+        float v[4];
+        float c00 = 0.f, c11 = 0.f, c01r = 0.f, c01i = 0.f;
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+        {
+            const float *mk = a.mask + (long)j * a.mask_target_stride + row * a.mask_ld;
+            const float2 yL = initial_estimate(mk[b], XL, ma, a.mask_is_mag);
+            const float2 yR = initial_estimate(mk[kBins + b], XR, ma, a.mask_is_mag);
+            const float sL = yL.x + yL.y, sR = yR.x + yR.y;
+            v[j] = (sL * sL + sR * sR) / 2.0f;
+            c00 += reg + v[j] * R[4 * j + 0];
+            c11 += reg + v[j] * R[4 * j + 1];
+            c01r += v[j] * R[4 * j + 2];
+            c01i += v[j] * R[4 * j + 3];
+        }
+        // inverse of the Hermitian 2x2 [[c00, c01],[conj c01, c11]] (invert4D, wiener.cpp:54-84)
+        const float det = c00 * c11 - (c01r * c01r + c01i * c01i);
+        const float inv_det = det / (det * det); // conj(det)/norm(det), det real
+        const float i00 = inv_det * c11, i11 = inv_det * c00;
+        const float i01r = -inv_det * c01r, i01i = -inv_det * c01i; // inv01 ; inv10 = conj(inv01)
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+        {
+            const float r00 = R[4 * j + 0], r11 = R[4 * j + 1], r01r = R[4 * j + 2], r01i = R[4 * j + 3];
+            // gain = v * R * inv ; R10 = conj(R01), inv10 = conj(inv01)
+            // g00 = r00*i00 + R01*conj(inv01)
+            const float g00r = v[j] * (r00 * i00 + (r01r * i01r + r01i * i01i));
+            const float g00i = v[j] * (r01i * i01r - r01r * i01i);
+            // g01 = r00*inv01 + R01*i11
+            const float g01r = v[j] * (r00 * i01r + r01r * i11);
+            const float g01i = v[j] * (r00 * i01i + r01i * i11);
+            // g10 = conj(R01)*i00 + r11*conj(inv01)
+            const float g10r = v[j] * (r01r * i00 + r11 * i01r);
+            const float g10i = v[j] * (-r01i * i00 - r11 * i01i);
+            // g11 = conj(R01)*inv01 + r11*i11
+            const float g11r = v[j] * ((r01r * i01r + r01i * i01i) + r11 * i11);
+            const float g11i = v[j] * (r01r * i01i - r01i * i01r);
+            float2 y0, y1;
+            y0.x = (g00r * x0.x - g00i * x0.y) + (g01r * x1.x - g01i * x1.y);
+            y0.y = (g00r * x0.y + g00i * x0.x) + (g01r * x1.y + g01i * x1.x);
+            y1.x = (g10r * x0.x - g10i * x0.y) + (g11r * x1.x - g11i * x1.y);
+            y1.y = (g10r * x0.y + g10i * x0.x) + (g11r * x1.y + g11i * x1.x);
+            float2 *o = a.out + (long)j * a.out_stem_stride + (row * 2) * kBins + b;
+            o[0] = make_float2(y0.x * ma, y0.y * ma);
+            o[kBins] = make_float2(y1.x * ma, y1.y * ma);
+        }
+        if (a.mix_out)
+        {
+            a.mix_out[(row * 2 + 0) * kBins + b] = x0;
+            a.mix_out[(row * 2 + 1) * kBins + b] = x1;
+        }
+    }
+}
+
+int launch_wiener(const WienerArgs &a, cudaStream_t st)
+{
+    const int tiles = ceil_div(kBins, 256);
+    wiener_reduce_kernel<<<dim3(tiles, kWienerChunks, a.n_tracks), 256, 0, st>>>(a);
+    UMX_CUDA_OK(cudaGetLastError());
+    wiener_finalize_kernel<<<dim3(tiles, a.n_tracks), 256, 0, st>>>(a);
+    UMX_CUDA_OK(cudaGetLastError());
+    wiener_apply_kernel<<<dim3(tiles, ceil_div(a.F, kWienerApplyFrames), a.n_tracks), 256, 0, st>>>(a);
+    UMX_CUDA_OK(cudaGetLastError());
+    return 0;
+}
+
+} // namespace umx
