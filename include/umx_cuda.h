@@ -73,7 +73,8 @@ int umx_cuda_session_get_state(umx_cuda_session *s, int track, int target, int l
 int umx_cuda_infer_segment(umx_cuda_session *s, const float *audio, int n, float *out);
 
 /* ---- whole tracks: shift_inference + split_inference (umx.cpp:99-295) ------------------------ */
-/* n_tracks <= max_tracks independent tracks, each shifted by shift_offset (umx.cpp:112-122), cut into
+/* n_tracks <= max_tracks independent tracks, each shifted by shift_offset in [0, 11025] (umx.cpp:112-122;
+ * a larger offset overruns the reference's own (N + 22050 - offset)-column buffer), cut into
  * n_buf-sample segments at 0.75*n_buf stride, demixed with streaming LSTM state, recombined with the
  * triangular weights and sum_weight normalisation (umx.cpp:197-273), trimmed (umx.cpp:136-147).
  * Session state is reset first (a fresh process per track in the reference).
@@ -110,6 +111,9 @@ int umx_cuda_target_mags(umx_cuda_session *s, const float *spec, float *mags);
 int umx_cuda_session_set_profiling(umx_cuda_session *s, int enabled);
 double umx_cuda_session_stage_ms(umx_cuda_session *s, const char *stage);
 long umx_cuda_session_launches(umx_cuda_session *s);
+/* Launch everything on the caller's cudaStream_t (NULL restores the session's own stream), so a caller
+ * can bracket the work with its own CUDA events. */
+int umx_cuda_session_set_stream(umx_cuda_session *s, void *stream);
 /* Tuning knobs (documented in DESIGN.md): "gemm_terms" 1..3 fp16 split terms per tensor-core GEMM,
  * "gemm_impl" 0 = tcgen05, 1 = SIMT fp32 validation kernel, "lstm_impl" 0 = cluster kernel, 1 = simple. */
 int umx_cuda_session_set_option(umx_cuda_session *s, const char *name, int value);

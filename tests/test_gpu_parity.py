@@ -201,7 +201,7 @@ def test_demix_shift_offsets_and_trim(umx, small):
     saved = (O.SEGMENT_SAMPLES, O.STRIDE_SAMPLES)
     O.SEGMENT_SAMPLES, O.STRIDE_SAMPLES = n_buf, int(np.float32(0.75) * np.float32(n_buf))
     try:
-        for shift in (0, 4033, 22049):
+        for shift in (0, 4033, 11025):  # offsets > 11025 overrun the reference's own buffer (umx.cpp:120-122)
             got = sess.demix([t], shift_offset=shift)[0]
             want = O.demix(om, t, shift_offset=shift)
             assert np.abs(got - want).max() < WAVE_ATOL

@@ -35,7 +35,7 @@ EXPORTS = [
     "umx_cuda_session_reset", "umx_cuda_session_get_state", "umx_cuda_infer_segment", "umx_cuda_demix",
     "umx_cuda_demix_device", "umx_cuda_segment_plan", "umx_cuda_stft", "umx_cuda_istft", "umx_cuda_lstm_forward",
     "umx_cuda_wiener", "umx_cuda_target_mags", "umx_cuda_session_set_profiling", "umx_cuda_session_stage_ms",
-    "umx_cuda_session_launches", "umx_cuda_session_set_option",
+    "umx_cuda_session_launches", "umx_cuda_session_set_option", "umx_cuda_session_set_stream",
 ]
 
 _lib = None
@@ -84,6 +84,7 @@ def lib():
     l.umx_cuda_session_launches.restype = C.c_long
     l.umx_cuda_session_launches.argtypes = [vp]
     l.umx_cuda_session_set_option.argtypes = [vp, C.c_char_p, ip]
+    l.umx_cuda_session_set_stream.argtypes = [vp, vp]
     _lib = l
     return l
 
@@ -172,6 +173,10 @@ class Session:
 
     def set_option(self, name: str, value: int):
         _check(self._lib.umx_cuda_session_set_option(self._h, name.encode(), value), "umx_cuda_session_set_option")
+
+    def set_stream(self, cuda_stream: int | None):
+        """Run on the caller's CUDA stream (e.g. torch.cuda.current_stream().cuda_stream); None = own stream."""
+        _check(self._lib.umx_cuda_session_set_stream(self._h, cuda_stream), "umx_cuda_session_set_stream")
 
     def set_profiling(self, on: bool):
         _check(self._lib.umx_cuda_session_set_profiling(self._h, int(on)), "umx_cuda_session_set_profiling")

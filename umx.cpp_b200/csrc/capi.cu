@@ -212,7 +212,7 @@ int umx_cuda_demix_device(umx_cuda_session *s, const float *const *d_audio, cons
 
 int umx_cuda_segment_plan(int64_t n_samples, int shift_offset, int n_buf, int64_t *offsets, int *lengths, int cap)
 {
-    UMX_CHECK(n_samples >= 0 && shift_offset >= 0 && shift_offset < kMaxShift && n_buf >= kNfft,
+    UMX_CHECK(n_samples >= 0 && shift_offset >= 0 && shift_offset <= kMaxShift / 2 && n_buf >= kNfft,
               "umx_cuda_segment_plan: bad argument");
     const long L = (long)n_samples + kMaxShift - shift_offset;
     const int stride = (int)((1 - 0.25f) * n_buf);
@@ -249,6 +249,15 @@ double umx_cuda_session_stage_ms(umx_cuda_session *s, const char *stage)
     }
     auto it = s->s->stage_ms.find(stage);
     return it == s->s->stage_ms.end() ? -1.0 : it->second;
+}
+
+int umx_cuda_session_set_stream(umx_cuda_session *s, void *stream)
+{
+    UMX_CHECK(s, "umx_cuda_session_set_stream: null session");
+    UMX_CUDA_OK(cudaSetDevice(s->s->device));
+    UMX_CUDA_OK(cudaStreamSynchronize(s->s->st));
+    s->s->st = stream ? static_cast<cudaStream_t>(stream) : s->s->own_st;
+    return 0;
 }
 
 long umx_cuda_session_launches(umx_cuda_session *s) { return s ? s->s->launches : -1; }

@@ -91,11 +91,12 @@ int session_create(Model *m, int max_tracks, int n_buf, Session **out)
         session_destroy(s);
         return rc;
     };
-    if (cudaStreamCreateWithFlags(&s->st, cudaStreamNonBlocking) != cudaSuccess)
+    if (cudaStreamCreateWithFlags(&s->own_st, cudaStreamNonBlocking) != cudaSuccess)
     {
         set_error("session_create: cudaStreamCreate failed");
         return fail(-1);
     }
+    s->st = s->own_st;
     int rc = 0;
     rc |= salloc(s, &s->spec, M * 2 * kBins);
     rc |= salloc(s, &s->xh, M * kFc1InPad, true); // pad columns stay zero
@@ -166,8 +167,8 @@ void session_destroy(Session *s)
         cudaFree(p);
     cudaFree(s->d_stft);
     cudaFree(s->d_istft);
-    if (s->st)
-        cudaStreamDestroy(s->st);
+    if (s->own_st)
+        cudaStreamDestroy(s->own_st);
     delete s;
 }
 
@@ -433,7 +434,9 @@ int session_demix_device(Session *s, const float *const *d_audio, const int64_t 
                          int shift_offset, float *const *d_out)
 {
     UMX_CHECK(n_tracks >= 1 && n_tracks <= s->T, "umx_cuda_demix: n_tracks must be in [1, max_tracks]");
-    UMX_CHECK(shift_offset >= 0 && shift_offset < kMaxShift, "umx_cuda_demix: shift_offset must be in [0, 22050)");
+    // umx.cpp:120-122 places N samples at column `offset` of an (N + 22050 - offset)-column buffer: only
+    // offsets <= 11025 stay inside it (the reference's own rand() % 22050 draw is 4033)
+    UMX_CHECK(shift_offset >= 0 && shift_offset <= kMaxShift / 2, "umx_cuda_demix: shift_offset must be in [0, 11025]");
     UMX_CUDA_OK(cudaSetDevice(s->device));
     const int stride = stride_of(s->n_buf);
     std::vector<long> L(n_tracks);

@@ -26,7 +26,8 @@ struct Session
     int F = 0;      // frames per window
     int H = 0, Hh = 0;
     long Mcap = 0;  // T * F rows
-    cudaStream_t st = nullptr;
+    cudaStream_t st = nullptr;      // stream every launch goes to
+    cudaStream_t own_st = nullptr;  // the session's own stream (st may be replaced by a caller's)
 
     // activations (HBM layout documented in DESIGN.md)
     float2 *spec = nullptr;                  // [Mcap][2][2049]
