@@ -104,6 +104,21 @@ int umx_cuda_wiener(float *mix, const float *mags, int F, float *out);
  * 4 x float[2049][F][2]; LSTM state of track slot 0 advances. F == nb_frames(n_buf) of the session. */
 int umx_cuda_target_mags(umx_cuda_session *s, const float *spec, float *mags);
 
+/* Wiener-EM that allocates nothing.  NO COUNTERPART IN THE REFERENCE: it exists for callers that may not
+ * call cudaMalloc when they need the filter (a real-time audio thread, which cannot take cudaMalloc's
+ * device-wide synchronisation and unbounded latency; a plugin inside a process whose GPU memory belongs
+ * entirely to another allocator).  Same arithmetic as umx_cuda_wiener, but inputs and outputs are DEVICE
+ * buffers the caller already owns, in the library's internal order, and the kernels' scratch is a static
+ * device array inside the library (about 6.5 MB, held by every GPU that loads the library):
+ *   d_mix   complex float[n_tracks*F][2][2049] (left untouched), d_mags 4 x float[n_tracks*F][2][2049],
+ *   d_out   4 x complex float[n_tracks*F][2][2049], stream a cudaStream_t (NULL = default stream).
+ * n_tracks > UMX_WIENER_NOALLOC_MAX_TRACKS is rejected.  The first call on each device resolves the
+ * array's address: make it before any stream capture.  All calls share the array (its max|X| slots are
+ * re-zeroed per call, the rest is overwritten before use), so calls that overlap on the GPU race:
+ * serialise them. */
+#define UMX_WIENER_NOALLOC_MAX_TRACKS 2
+int umx_cuda_wiener_noalloc(const float *d_mix, const float *d_mags, int F, int n_tracks, float *d_out, void *stream);
+
 /* ---- measurement ------------------------------------------------------------------------------ */
 /* Per-stage device time of the most recent demix / infer_segment call, from CUDA events recorded on
  * the session's own stream.  Stage names: "stft", "gemm", "lstm", "wiener", "istft", "finalize",

@@ -36,6 +36,7 @@ EXPORTS = [
     "umx_cuda_demix_device", "umx_cuda_segment_plan", "umx_cuda_stft", "umx_cuda_istft", "umx_cuda_lstm_forward",
     "umx_cuda_wiener", "umx_cuda_target_mags", "umx_cuda_session_set_profiling", "umx_cuda_session_stage_ms",
     "umx_cuda_session_launches", "umx_cuda_session_set_option", "umx_cuda_session_set_stream",
+    "umx_cuda_wiener_noalloc",
 ]
 
 _lib = None
@@ -85,6 +86,7 @@ def lib():
     l.umx_cuda_session_launches.argtypes = [vp]
     l.umx_cuda_session_set_option.argtypes = [vp, C.c_char_p, ip]
     l.umx_cuda_session_set_stream.argtypes = [vp, vp]
+    l.umx_cuda_wiener_noalloc.argtypes = [vp, vp, ip, ip, vp, vp]
     _lib = l
     return l
 
@@ -294,3 +296,9 @@ def wiener_filter(mix: np.ndarray, mags: np.ndarray):
     out = np.empty((4, NB_BINS, F, 2), dtype=np.complex64)
     _check(lib().umx_cuda_wiener(_p(m), _p(g), F, _p(out)), "wiener_filter")
     return np.ascontiguousarray(out.transpose(0, 3, 2, 1)), _spec_from_ref(m.reshape(-1), F)
+
+
+def wiener_noalloc(d_mix: int, d_mags: int, F: int, n_tracks: int, d_out: int, stream: int | None = None):
+    """umx_cuda_wiener_noalloc: device pointers in the internal [frame][channel][bin] order; nothing is
+    allocated (see include/umx_cuda.h for who needs that and what it costs)."""
+    _check(lib().umx_cuda_wiener_noalloc(d_mix, d_mags, F, n_tracks, d_out, stream), "umx_cuda_wiener_noalloc")

@@ -189,3 +189,130 @@ int launch_wiener(const WienerArgs &a, cudaStream_t st)
 }
 
 } // namespace umx
+
+// =====================================================================================================
+// Allocation-free Wiener entry point (no counterpart in the reference; declared in include/umx_cuda.h).
+//
+// Some hosts of this library may not allocate device memory at the time they need a Wiener pass: a
+// real-time audio thread cannot afford cudaMalloc's implicit device-wide synchronisation and unbounded
+// latency, and a plugin living inside a process whose GPU memory is entirely owned by another
+// allocator (a fixed start-up budget, no driver allocations afterwards) is simply not allowed to.
+// For them the scratch of the three Wiener kernels (per-chunk partial sums, the normalised spatial
+// covariances and the per-track max|X|) lives in the file-scope device array below instead of in
+// cudaMalloc'ed buffers.  Costs and rules, all visible to the caller:
+//   * the array (UMX_WIENER_NOALLOC_MAX_TRACKS tracks, about 6.5 MB) is part of the library image:
+//     every GPU that loads the library carries it until the process exits, used or not;
+//   * the FIRST call on each device looks the array's device address up (cudaGetSymbolAddress with that
+//     device current).  Make that first call outside any stream capture;
+//   * all calls share the one array and it keeps the previous call's contents: the max|X| slots are
+//     cleared at the start of every call, everything else is fully overwritten before it is read;
+//   * two calls whose kernels overlap on the GPU (different streams, different host threads) race on
+//     the array.  Serialise them.
+// =====================================================================================================
+#include "../../include/umx_cuda.h"
+
+#include <mutex>
+
+namespace umx
+{
+namespace
+{
+constexpr int kNoAllocMaxTracks = UMX_WIENER_NOALLOC_MAX_TRACKS;
+constexpr size_t kNaPartials = (size_t)kWienerChunks * kWienerQ * kBins; // floats per track
+constexpr size_t kNaStats = (size_t)16 * kBins;
+constexpr size_t kNaMaxabsOff = (size_t)kNoAllocMaxTracks * (kNaPartials + kNaStats);
+constexpr size_t kNaTotal = kNaMaxabsOff + 64;
+
+// In HOST code this name is only a stand-in for the symbol, never a device address.
+static __device__ __align__(256) float g_wiener_noalloc_scratch[kNaTotal];
+
+// per-track max |X| over a [n_tracks*F][2][2049] spectrogram (non-negative floats order like ints)
+__global__ void __launch_bounds__(256) spec_maxabs_kernel(const float2 *__restrict__ spec, long per_track,
+                                                          float *__restrict__ maxabs)
+{
+    __shared__ float red[8];
+    const int trk = blockIdx.y;
+    const float2 *p = spec + (long)trk * per_track;
+    float mx = 0.f;
+    for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < per_track; i += (long)gridDim.x * blockDim.x)
+    {
+        const float2 x = p[i];
+        mx = fmaxf(mx, sqrtf(x.x * x.x + x.y * x.y));
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1)
+        mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+    if ((threadIdx.x & 31) == 0)
+        red[threadIdx.x >> 5] = mx;
+    __syncthreads();
+    if (threadIdx.x == 0)
+    {
+        for (int i = 1; i < 8; ++i)
+            mx = fmaxf(mx, red[i]);
+        atomicMax(reinterpret_cast<int *>(maxabs) + trk, __float_as_int(mx));
+    }
+}
+
+// device address of the scratch array on the current device, looked up once per device
+int noalloc_scratch(float **out)
+{
+    static std::mutex mu;
+    static float *ptr[64] = {};
+    int dev = 0;
+    UMX_CUDA_OK(cudaGetDevice(&dev));
+    UMX_CHECK(dev >= 0 && dev < 64, "umx_cuda_wiener_noalloc: device index out of range");
+    std::lock_guard<std::mutex> lk(mu);
+    if (!ptr[dev])
+    {
+        float *p = nullptr;
+        UMX_CUDA_OK(cudaGetSymbolAddress(reinterpret_cast<void **>(&p), g_wiener_noalloc_scratch));
+        UMX_CHECK(p != nullptr, "umx_cuda_wiener_noalloc: cudaGetSymbolAddress returned a null address");
+        ptr[dev] = p;
+    }
+    *out = ptr[dev];
+    return 0;
+}
+} // namespace
+} // namespace umx
+
+extern "C" int umx_cuda_wiener_noalloc(const float *d_mix, const float *d_mags, int F, int n_tracks, float *d_out,
+                                       void *stream)
+{
+    using namespace umx;
+    UMX_CHECK(d_mix && d_mags && d_out, "umx_cuda_wiener_noalloc: null pointer");
+    UMX_CHECK(F >= 1, "umx_cuda_wiener_noalloc: F must be >= 1");
+    if (n_tracks < 1 || n_tracks > kNoAllocMaxTracks)
+    {
+        set_error("umx_cuda_wiener_noalloc: n_tracks = " + std::to_string(n_tracks) + " is outside [1, " +
+                  std::to_string(kNoAllocMaxTracks) + "]: the built-in scratch array holds at most " +
+                  std::to_string(kNoAllocMaxTracks) + " tracks; use umx_cuda_wiener or a session for more");
+        return -2;
+    }
+    float *scratch = nullptr;
+    if (int rc = noalloc_scratch(&scratch))
+        return rc;
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    const long e = (long)n_tracks * F * 2 * kBins; // elements of one [n_tracks*F][2][2049] tensor
+    float *maxabs = scratch + kNaMaxabsOff;
+    // the only state that must start at zero: the atomicMax targets
+    UMX_CUDA_OK(cudaMemsetAsync(maxabs, 0, sizeof(float) * kNoAllocMaxTracks, st));
+    const long per_track = (long)F * 2 * kBins;
+    spec_maxabs_kernel<<<dim3((unsigned)std::min<long>(ceil_div(per_track, 256), 592), n_tracks), 256, 0, st>>>(
+        reinterpret_cast<const float2 *>(d_mix), per_track, maxabs);
+    UMX_CUDA_OK(cudaGetLastError());
+    WienerArgs w{};
+    w.spec = reinterpret_cast<const float2 *>(d_mix);
+    w.mask = d_mags;
+    w.mask_target_stride = e;
+    w.mask_ld = 2 * kBins;
+    w.mask_is_mag = 1;
+    w.maxabs = maxabs;
+    w.partials = scratch;
+    w.stats = scratch + (size_t)kNoAllocMaxTracks * kNaPartials;
+    w.out = reinterpret_cast<float2 *>(d_out);
+    w.out_stem_stride = e;
+    w.mix_out = nullptr; // the caller's mix is left untouched
+    w.F = F;
+    w.n_tracks = n_tracks;
+    return launch_wiener(w, st);
+}
