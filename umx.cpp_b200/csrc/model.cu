@@ -376,6 +376,16 @@ static int build_operands(Model *m, std::map<std::string, uint8_t *> (&whh_raw)[
                 if (rc)
                     return rc;
                 tw.whh_q[l][d] = packed;
+                if (lstm_cluster_supported(Hh))
+                {
+                    uint8_t *img = nullptr;
+                    if (dev_alloc(m, &img, whh_image_bytes()))
+                        return -1;
+                    rc = launch_whh_image(whh_raw[t]["lstm.weight_hh" + sfx], img, 0);
+                    if (rc)
+                        return rc;
+                    tw.whh_img[l][d] = img;
+                }
             }
             if (upload(m, &tw.wih_beta[l], beta))
                 return -1;

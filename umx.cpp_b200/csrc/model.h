@@ -22,6 +22,7 @@ struct TargetWeights
     // recurrent weights stay quantised: [k][unit][gate] uint8 + (scale, offset)
     uint8_t *whh_q[3][2] = {};
     float whh_scale[3][2] = {}, whh_offset[3][2] = {};
+    uint8_t *whh_img[3][2] = {}; // pre-swizzled SMEM image for the cluster kernel (hidden 1024 only)
     // GEMM operands (fp16 hi/lo planes, K-major) and fused-epilogue constants
     __half *wih_hi[3] = {}, *wih_lo[3] = {}; // [2 dirs * 2H][H]
     float *wih_beta[3] = {};                 // b_ih + b_hh, [2 dirs * 2H]

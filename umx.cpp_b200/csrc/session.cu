@@ -262,7 +262,16 @@ int session_lstm(Session *s, int n_tracks, int target_begin, int target_count, b
         a.target_begin = target_begin;
         a.target_count = target_count;
         s->launches++;
-        if (int rc = launch_lstm_simple(a, s->st))
+        if (s->lstm_impl == 0 && lstm_cluster_supported(Hh))
+        {
+            const uint8_t *img[kTargets][2];
+            for (int t = 0; t < kTargets; ++t)
+                for (int d = 0; d < 2; ++d)
+                    img[t][d] = m->t[t].whh_img[l][d];
+            if (int rc = launch_lstm_cluster(a, img, s->st))
+                return rc;
+        }
+        else if (int rc = launch_lstm_simple(a, s->st))
             return rc;
     }
     return 0;

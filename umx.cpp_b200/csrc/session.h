@@ -53,7 +53,7 @@ struct Session
 
     std::vector<void *> allocs;
     // options
-    int gemm_impl = 0, gemm_terms = 3, lstm_impl = 1;
+    int gemm_impl = 0, gemm_terms = 3, lstm_impl = 0;
     // measurement
     bool profiling = false;
     std::vector<StageTimer> timers;
