@@ -11,9 +11,10 @@
 //     sum_k h_k for the offset term of W = scale*q + offset;
 //   * 8 epilogue warps read TMEM (lane = gate row, ordered 4*unit + gate so one quad of lanes holds the
 //     four gates of a unit), add the input projection, apply the activations, update c and h, and
-//     write the new h as digits straight into the B operand of ALL 8 CTAs through distributed shared
-//     memory, then arrive (release.cluster) on the destination's mbarrier;
-//   * the MMA thread waits for the 256 arrivals (acquire.cluster), fences the async proxy and goes on.
+//     write the new h as digits into this CTA's own tile of the h buffer; one bulk DSMEM copy per peer
+//     (cp.async.bulk shared::cta -> shared::cluster) then ships the tile, its bytes counted on the peer's
+//     mbarrier: 7 transactions per CTA per step, async proxy end to end;
+//   * the MMA thread posts expect_tx for the 7 peer tiles, waits, and issues the next step's MMAs.
 // There is no cluster-wide barrier in the loop; two h buffers alternate by step parity.
 // h / c are loaded from and stored to the session so the state streams across segments (lstm.cpp:160-161).
 #include "common.cuh"
@@ -33,9 +34,9 @@ constexpr int kMaxTracks = 16;   // tracks per cluster (N = 4 digits * tracks <=
 constexpr int kATile = 128 * 128;                 // one (half, k-block) tile of W_hh: 128 rows x 128 bytes
 constexpr int kABytes = 2 * 4 * kATile;           // 128 KB
 constexpr int kOnesOff = kABytes;                 // all-ones tile, 16 KB
-constexpr int kBOff = kOnesOff + kATile;          // h digits: [2 buffers][4 k-blocks][64 rows][128 B]
-constexpr int kBTile = 64 * 128;
-constexpr int kBBuf = 4 * kBTile;
+constexpr int kBOff = kOnesOff + kATile;          // h digits: [2 buffers][8 source CTAs][64 rows][64 B], 64-byte swizzle
+constexpr int kBTile = 64 * 64;                   // one source CTA's 64 units x up to 64 (track, digit) rows
+constexpr int kBBuf = kC * kBTile;
 constexpr int kBarOff = kBOff + 2 * kBBuf;
 constexpr int kSmemBytes = kBarOff + 64 + 1024;
 constexpr int kThreads = 288;    // 8 epilogue warps + 1 control warp
@@ -46,14 +47,6 @@ __device__ __forceinline__ uint32_t mapa(uint32_t local_addr, uint32_t cta)
     uint32_t r;
     asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(local_addr), "r"(cta));
     return r;
-}
-__device__ __forceinline__ void st_cluster_v2(uint32_t addr, uint32_t a, uint32_t b)
-{
-    asm volatile("st.shared::cluster.v2.b32 [%0], {%1, %2};" ::"r"(addr), "r"(a), "r"(b) : "memory");
-}
-__device__ __forceinline__ void arrive_remote_release(uint32_t addr)
-{
-    asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(addr) : "memory");
 }
 __device__ __forceinline__ bool try_wait_cluster(uint32_t bar, uint32_t parity)
 {
@@ -102,9 +95,39 @@ struct ClusterArgs
     const uint8_t *img[kTargets][2]; // pre-swizzled W_hh image per (target, dir): [8 CTAs][128 KB]
 };
 
-// Writes this warp's 8 units of one track (h identical in the 4 lanes of a quad) as digit bytes into
-// the B operand buffer `buf` of every CTA of the cluster: lane (q, g) sends digit g to CTA q.
-__device__ __forceinline__ void publish_h(float h, int q, int g, int track, uint32_t b_local_base, uint32_t chunk, uint32_t within)
+// gate activation with per-lane constants: sigmoid = 1 * rcp(1 + 2^(-log2e x)) + 0, tanh = -2 * rcp(1 + 2^(2 log2e x)) + 1
+__device__ __forceinline__ float act_rcp(float x, float A, float B, float Cc)
+{
+    float e, r;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(x * B));
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(1.0f + e));
+    return fmaf(A, r, Cc);
+}
+__device__ __forceinline__ float tanh_fast(float x) { return act_rcp(x, -2.0f, 2.885390081777927f, 1.0f); }
+
+// One bulk copy of this CTA's freshly written h tile into the same place of a peer CTA's shared memory;
+// the bytes are counted on the peer's mbarrier (async proxy end to end: no fence on the consumer side).
+__device__ __forceinline__ void bulk_copy_to_peer(uint32_t remote_dst, uint32_t local_src, uint32_t bytes, uint32_t remote_bar)
+{
+    asm volatile("cp.async.bulk.shared::cluster.shared::cta.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(remote_dst),
+                 "r"(local_src), "r"(bytes), "r"(remote_bar)
+                 : "memory");
+}
+__device__ __forceinline__ void st_shared_v2(uint32_t addr, uint32_t a, uint32_t b)
+{
+    asm volatile("st.shared.v2.b32 [%0], {%1, %2};" ::"r"(addr), "r"(a), "r"(b) : "memory");
+}
+// K-major tile with 64-byte rows and 64-byte swizzle (16-byte chunk index ^= (row >> 1) & 3); 8-row groups 512 B apart
+__device__ __forceinline__ uint64_t smem_desc_sw64(uint32_t smem_addr)
+{
+    return (uint64_t)((smem_addr & 0x3FFFF) >> 4) | ((uint64_t)1 << 16) | ((uint64_t)(512 >> 4) << 32) | ((uint64_t)1 << 46) |
+           ((uint64_t)4 << 61);
+}
+
+// Lane (q, g) holds h of (unit q of this warp, track 4*jc + g).  The 8 lanes with the same g collect the
+// 8 units' digit words, transpose them to per-digit byte rows and write them into this CTA's own tile of the
+// h buffer (B row n = 4*track + digit, 8 consecutive k bytes); publish_tile() then ships the tile to the peers.
+__device__ __forceinline__ void publish_quad(float h, int g, int jc, uint32_t tile, uint32_t chunk, uint32_t within)
 {
     int v = __float2int_rn(h * 134217728.0f); // 2^27
     const int d3 = ((v + 64) & 127) - 64;
@@ -112,18 +135,34 @@ __device__ __forceinline__ void publish_h(float h, int q, int g, int track, uint
     const int d2 = ((v + 64) & 127) - 64;
     v = (v - d2) >> 7;
     const int d1 = ((v + 64) & 127) - 64;
-    v = (v - d1) >> 7;
-    const int mine = g == 0 ? v : (g == 1 ? d1 : (g == 2 ? d2 : d3));
-    const uint32_t b = (uint32_t)mine & 0xffu;
-    uint32_t o = __shfl_xor_sync(0xffffffffu, b, 4);
-    const uint32_t w2 = (q & 1) ? (o | (b << 8)) : (b | (o << 8));
-    o = __shfl_xor_sync(0xffffffffu, w2, 8);
-    const uint32_t w4 = (q & 2) ? (o | (w2 << 16)) : (w2 | (o << 16));
-    o = __shfl_xor_sync(0xffffffffu, w4, 16);
-    const uint32_t lo = (q & 4) ? o : w4, hi = (q & 4) ? w4 : o;
-    const uint32_t n = 4u * track + g; // B row: (track, digit)
-    const uint32_t la = b_local_base + n * 128u + ((chunk ^ (n & 7u)) << 4) + within;
-    st_cluster_v2(mapa(la, (uint32_t)q), lo, hi);
+    v = (v - d1) >> 7; // d0
+    const uint32_t w = ((uint32_t)v & 0xffu) | (((uint32_t)d1 & 0xffu) << 8) | (((uint32_t)d2 & 0xffu) << 16) | ((uint32_t)d3 << 24);
+    uint32_t W[8];
+#pragma unroll
+    for (int u = 0; u < 8; ++u)
+        W[u] = __shfl_sync(0xffffffffu, w, 4 * u + g);
+    uint32_t lo[4], hi[4];
+    {
+        const uint32_t a0 = __byte_perm(W[0], W[1], 0x5140), a1 = __byte_perm(W[0], W[1], 0x7362);
+        const uint32_t b0 = __byte_perm(W[2], W[3], 0x5140), b1 = __byte_perm(W[2], W[3], 0x7362);
+        lo[0] = __byte_perm(a0, b0, 0x5410);
+        lo[1] = __byte_perm(a0, b0, 0x7632);
+        lo[2] = __byte_perm(a1, b1, 0x5410);
+        lo[3] = __byte_perm(a1, b1, 0x7632);
+        const uint32_t c0 = __byte_perm(W[4], W[5], 0x5140), c1 = __byte_perm(W[4], W[5], 0x7362);
+        const uint32_t e0 = __byte_perm(W[6], W[7], 0x5140), e1 = __byte_perm(W[6], W[7], 0x7362);
+        hi[0] = __byte_perm(c0, e0, 0x5410);
+        hi[1] = __byte_perm(c0, e0, 0x7632);
+        hi[2] = __byte_perm(c1, e1, 0x5410);
+        hi[3] = __byte_perm(c1, e1, 0x7632);
+    }
+    const uint32_t n0 = 4u * (4u * jc + g); // row of digit 0 of this lane's track
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+    {
+        const uint32_t n = n0 + i;
+        st_shared_v2(tile + n * 64u + ((chunk ^ ((n >> 1) & 3u)) << 4) + within, lo[i], hi[i]);
+    }
 }
 
 template <int TP>
@@ -139,6 +178,9 @@ __global__ void __cluster_dims__(kC, 1, 1) __launch_bounds__(kThreads, 1) lstm_c
     const int n_valid = min(kMaxTracks, a.n_tracks - trk0);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     constexpr int N = 4 * TP;
+    constexpr int NQ = TP / 4; // track quads
+    constexpr uint32_t kTileBytes = 64u * N;               // one CTA's contribution per step: N rows x 64 units
+    constexpr uint32_t kStepBytes = (kC - 1) * kTileBytes; // bytes arriving from the 7 peers per step
 
     uint64_t *bars = reinterpret_cast<uint64_t *>(smem + kBarOff);
     const uint32_t hfull0 = smem_u32(bars), mma_done = smem_u32(bars + 2);
@@ -160,8 +202,8 @@ __global__ void __cluster_dims__(kC, 1, 1) __launch_bounds__(kThreads, 1) lstm_c
     }
     if (threadIdx.x == 0)
     {
-        mbar_init(hfull0, 256);
-        mbar_init(hfull0 + 8, 256);
+        mbar_init(hfull0, 2);     // MMA thread (expect_tx of the peers' bytes) + this CTA's own epilogue
+        mbar_init(hfull0 + 8, 2);
         mbar_init(mma_done, 1);
         fence_barrier_init();
     }
@@ -180,107 +222,130 @@ __global__ void __cluster_dims__(kC, 1, 1) __launch_bounds__(kThreads, 1) lstm_c
         // ================= epilogue warps =================
         const int qd = warp & 3, hh = warp >> 2, q = lane >> 2, g = lane & 3;
         const int k = kUnits * r + 32 * hh + 8 * qd + q; // hidden unit of this quad
-        const uint32_t kk0 = (uint32_t)((kUnits * r + 32 * hh + 8 * qd) & 127); // first unit of the warp inside its k-block
-        const uint32_t kb = (uint32_t)(kUnits * r) >> 7;
+        const uint32_t kk0 = (uint32_t)(32 * hh + 8 * qd); // first unit of this warp inside the CTA's 64-byte rows
         const uint32_t chunk = kk0 >> 4, within = kk0 & 15u;
         const float scale = a.whh_scale[target][dir], offset = a.whh_offset[target][dir];
-        const float gm = (g == 2) ? 1.0f : 0.5f, ga = (g == 2) ? 0.0f : 0.5f; // sigmoid(x) = 0.5 tanh(x/2) + 0.5
+        // per-lane activation constants: gate 2 (g) is tanh, gates 0,1,3 (i,f,o) are sigmoids
+        const float actA = (g == 2) ? -2.0f : 1.0f, actB = (g == 2) ? 2.885390081777927f : -1.4426950408889634f,
+                    actC = (g == 2) ? 1.0f : 0.0f;
         const uint32_t t_lane = tmem_base + ((uint32_t)(32 * qd) << 16);
-        const long st_base = ((long)target * 2 + dir) * kHhC + k;
-        const float *xp_base = a.xproj + (long)target * a.xproj_target_stride + (long)dir * 4 * kHhC + g * kHhC + k;
+        // this CTA's own tile (source index r) of h buffer 0; lanes 0..7 of warp 0 ship it to CTA `lane`
+        const uint32_t tile0 = sB + (uint32_t)r * kBTile;
+        const bool shipper = (warp == 0 && lane < kC);
+        const uint32_t peer_tile0 = shipper ? mapa(tile0, (uint32_t)lane) : 0u;
+        const uint32_t peer_bar0 = shipper ? mapa(hfull0, (uint32_t)lane) : 0u;
+        // after every epilogue thread has written its digits: make them visible to the async proxy, meet on a
+        // named barrier, then 7 bulk copies (one per peer) + one local arrive
+        auto publish_tile = [&](uint32_t pbuf) {
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+            asm volatile("bar.sync 1, 256;" ::: "memory");
+            if (shipper)
+            {
+                if (lane == r)
+                    mbar_arrive(hfull0 + 8u * pbuf);
+                else
+                    bulk_copy_to_peer(peer_tile0 + pbuf * kBBuf, tile0 + pbuf * kBBuf, kTileBytes, peer_bar0 + 8u * pbuf);
+            }
+        };
         const int ldx = 8 * kHhC;
+        const float *xrow = a.xproj + (long)target * a.xproj_target_stride + (long)dir * 4 * kHhC + g * kHhC + k;
+        const long trk_x = (long)F * ldx; // floats between tracks in xproj
+        // unit-level ownership: lane (q, g) owns tracks 4*jc + g of unit k
+        const long st_base = ((long)target * 2 + dir) * kHhC + k;
+        const long out_base = (long)target * a.out_target_stride + a.col_offset + dir * kHhC + k;
+        const long trk_o = (long)F * a.ldo;
 
-        float c[TP], xp[TP];
+        float c[NQ], hlast[NQ], xp[TP];
 #pragma unroll
-        for (int j = 0; j < TP; ++j)
+        for (int jc = 0; jc < NQ; ++jc)
         {
-            const bool ok = j < n_valid;
-            const long so = (long)(trk0 + j) * a.state_track_stride + st_base;
-            c[j] = ok ? a.c_state[so] : 0.f;
-            const float h0 = ok ? a.h_state[so] : 0.f;
-            publish_h(h0, q, g, j, sB + kb * kBTile, chunk, within); // buffer 0
-            const int t0 = dir == 0 ? 0 : F - 1;
-            xp[j] = ok ? __ldg(xp_base + ((long)(trk0 + j) * F + t0) * ldx) : 0.f;
+            const int trk = min(trk0 + 4 * jc + g, a.n_tracks - 1); // padded tracks mirror a real one, never stored
+            const long so = (long)trk * a.state_track_stride + st_base;
+            c[jc] = a.c_state[so];
+            hlast[jc] = a.h_state[so];
+            publish_quad(hlast[jc], g, jc, tile0, chunk, within); // buffer 0
         }
-        fence_proxy_async();
-        arrive_remote_release(mapa(hfull0, (uint32_t)q));
+        publish_tile(0);
+        {
+            const int t0 = dir == 0 ? 0 : F - 1;
+#pragma unroll
+            for (int j = 0; j < TP; ++j)
+                xp[j] = __ldg(xrow + (long)min(trk0 + j, a.n_tracks - 1) * trk_x + (long)t0 * ldx);
+        }
 
-        float hcur[TP];
         for (int step = 0; step < F; ++step)
         {
             const int t = dir == 0 ? step : F - 1 - step;
-            const bool more = step + 1 < F;
+            const int tn = dir == 0 ? min(step + 1, F - 1) : max(F - 2 - step, 0);
             float xn[TP];
-            if (more)
-            {
-                const int tn = dir == 0 ? step + 1 : F - 2 - step;
 #pragma unroll
-                for (int j = 0; j < TP; ++j)
-                    xn[j] = (j < n_valid) ? __ldg(xp_base + ((long)(trk0 + j) * F + tn) * ldx) : 0.f;
-            }
+            for (int j = 0; j < TP; ++j) // next step's input projection, in flight during this step
+                xn[j] = __ldg(xrow + (long)min(trk0 + j, a.n_tracks - 1) * trk_x + (long)tn * ldx);
+            const uint32_t pn = (uint32_t)((step + 1) & 1);
+            const uint32_t tile = tile0 + pn * kBBuf;
+
             mbar_wait(mma_done, (uint32_t)(step & 1));
             tc_fence_after();
-            const uint32_t bnext = sB + (uint32_t)((step + 1) & 1) * kBBuf + kb * kBTile;
 #pragma unroll
-            for (int jc = 0; jc < TP / 4; ++jc)
+            for (int jc = 0; jc < NQ; ++jc)
             {
                 uint32_t d[16], s[16];
                 tmem_ld16(t_lane + hh * 64 + 16 * jc, d);
                 tmem_ld16(t_lane + 128 + 16 * jc, s);
                 tc_wait_ld();
+                float act[4];
 #pragma unroll
                 for (int jj = 0; jj < 4; ++jj)
                 {
-                    const int j = 4 * jc + jj;
                     const float dot = combine_digits(d[4 * jj], d[4 * jj + 1], d[4 * jj + 2], d[4 * jj + 3]);
                     const float hs = combine_digits(s[4 * jj], s[4 * jj + 1], s[4 * jj + 2], s[4 * jj + 3]);
-                    const float pre = xp[j] + fmaf(scale, dot, offset * hs);
-                    const float act = fmaf(gm, tanhf(gm * pre), ga);
-                    const int qb = lane & ~3;
-                    const float i_t = __shfl_sync(0xffffffffu, act, qb);
-                    const float f_t = __shfl_sync(0xffffffffu, act, qb + 1);
-                    const float g_t = __shfl_sync(0xffffffffu, act, qb + 2);
-                    const float o_t = __shfl_sync(0xffffffffu, act, qb + 3);
-                    c[j] = f_t * c[j] + i_t * g_t;       // lstm.cpp:152-154
-                    const float h = o_t * tanhf(c[j]);    // lstm.cpp:155
-                    hcur[j] = h;
-                    if (more)
-                        publish_h(h, q, g, j, bnext, chunk, within);
-                    if (j < n_valid)
-                    {
-                        const long row = (long)(trk0 + j) * F + t;
-                        const long o = (long)target * a.out_target_stride + row * a.ldo + a.col_offset + dir * kHhC + k;
-                        __half hh16, hl16;
-                        split_half(h, hh16, hl16);
-                        if (g == 0)
-                            a.out_hi[o] = hh16;
-                        else if (g == 1)
-                            a.out_lo[o] = hl16;
-                        else if (g == 2 && a.out_f32)
-                            a.out_f32[(long)target * a.out_f32_target_stride + row * (2 * kHhC) + dir * kHhC + k] = h;
-                    }
+                    const float pre = xp[4 * jc + jj] + fmaf(scale, dot, offset * hs); // lstm.cpp:132-140
+                    act[jj] = act_rcp(pre, actA, actB, actC);
+                }
+                // 4x4 transpose inside the quad: afterwards lane g holds the four gates of track 4*jc + g
+                const bool b0 = g & 1, b1 = g & 2;
+                const float keepA = b0 ? act[1] : act[0], keepB = b0 ? act[3] : act[2];
+                const float recvA = __shfl_xor_sync(0xffffffffu, b0 ? act[0] : act[1], 1);
+                const float recvB = __shfl_xor_sync(0xffffffffu, b0 ? act[2] : act[3], 1);
+                // now: track (b0) gates {g: keepA, g^1: recvA}, track (2+b0) gates {g: keepB, g^1: recvB}
+                const float v0 = b1 ? keepB : keepA, v1 = b1 ? recvB : recvA;             // gates g, g^1 of track g
+                const float v2 = __shfl_xor_sync(0xffffffffu, b1 ? keepA : keepB, 2);     // gate g^2
+                const float v3 = __shfl_xor_sync(0xffffffffu, b1 ? recvA : recvB, 2);     // gate g^3
+                // value with gate label x sits at index g ^ x
+                const float w0 = b0 ? v1 : v0, w1 = b0 ? v0 : v1, w2 = b0 ? v3 : v2, w3 = b0 ? v2 : v3; // labels (g&2)+{0,1}, (g&2)^2+{0,1}
+                const float i_t = b1 ? w2 : w0, f_t = b1 ? w3 : w1, g_t = b1 ? w0 : w2, o_t = b1 ? w1 : w3;
+                c[jc] = fmaf(f_t, c[jc], i_t * g_t);          // lstm.cpp:152-154
+                const float h = o_t * tanh_fast(c[jc]);       // lstm.cpp:155
+                hlast[jc] = h;
+                publish_quad(h, g, jc, tile, chunk, within);
+                const int trk = trk0 + 4 * jc + g;
+                if (trk < a.n_tracks)
+                {
+                    const long o = out_base + (long)trk * trk_o + (long)t * a.ldo;
+                    __half hh16, hl16;
+                    split_half(h, hh16, hl16);
+                    a.out_hi[o] = hh16;
+                    a.out_lo[o] = hl16;
+                    if (a.out_f32)
+                        a.out_f32[(long)target * a.out_f32_target_stride + ((long)trk * F + t) * (2 * kHhC) + dir * kHhC + k] = h;
                 }
             }
-            if (more)
-            {
-                tc_fence_before();   // our TMEM reads are done before the next MMAs may overwrite the accumulators
-                fence_proxy_async(); // our SMEM (DSMEM) writes become visible to the async proxy (MMA operand reads)
-                arrive_remote_release(mapa(hfull0 + 8u * (uint32_t)((step + 1) & 1), (uint32_t)q));
+            publish_tile(pn);
 #pragma unroll
-                for (int j = 0; j < TP; ++j)
-                    xp[j] = xn[j];
-            }
+            for (int j = 0; j < TP; ++j)
+                xp[j] = xn[j];
         }
 #pragma unroll
-        for (int j = 0; j < TP; ++j)
-            if (j < n_valid)
+        for (int jc = 0; jc < NQ; ++jc)
+        {
+            const int trk = trk0 + 4 * jc + g;
+            if (trk < a.n_tracks)
             {
-                const long so = (long)(trk0 + j) * a.state_track_stride + st_base;
-                if (g == 0)
-                    a.h_state[so] = hcur[j];
-                else if (g == 1)
-                    a.c_state[so] = c[j];
+                const long so = (long)trk * a.state_track_stride + st_base;
+                a.h_state[so] = hlast[jc];
+                a.c_state[so] = c[jc];
             }
+        }
     }
     else if (lane == 0)
     {
@@ -290,8 +355,8 @@ __global__ void __cluster_dims__(kC, 1, 1) __launch_bounds__(kThreads, 1) lstm_c
         for (int step = 0; step < F; ++step)
         {
             const uint32_t p = (uint32_t)(step & 1);
+            mbar_arrive_expect_tx(hfull0 + 8 * p, kStepBytes); // the 7 peers' bulk copies complete this phase
             wait_cluster(hfull0 + 8 * p, (uint32_t)((step >> 1) & 1));
-            fence_proxy_async();
             tc_fence_after();
             const uint32_t bb = sB + p * kBBuf;
 #pragma unroll
@@ -300,21 +365,24 @@ __global__ void __cluster_dims__(kC, 1, 1) __launch_bounds__(kThreads, 1) lstm_c
                 for (int kb = 0; kb < 4; ++kb)
                 {
                     const uint64_t da = smem_desc_sw128(sA + (h2 * 4 + kb) * kATile);
-                    const uint64_t db = smem_desc_sw128(bb + kb * kBTile);
 #pragma unroll
-                    for (int ks = 0; ks < 4; ++ks) // 32 bytes (K = 32) per MMA
-                        mma_i8(tmem_base + h2 * 64, da + 2 * ks, db + 2 * ks, idesc, (kb | ks) ? 1u : 0u);
+                    for (int ks = 0; ks < 4; ++ks) // 32 bytes (K = 32) per MMA; the h tile of source CTA 2*kb + ks/2
+                        mma_i8(tmem_base + h2 * 64, da + 2 * ks, smem_desc_sw64(bb + (2 * kb + (ks >> 1)) * kBTile) + 2 * (ks & 1), idesc,
+                               (kb | ks) ? 1u : 0u);
                 }
 #pragma unroll
             for (int kb = 0; kb < 4; ++kb)
-            {
-                const uint64_t db = smem_desc_sw128(bb + kb * kBTile);
 #pragma unroll
                 for (int ks = 0; ks < 4; ++ks)
-                    mma_i8(tmem_base + 128, dOnes + 2 * ks, db + 2 * ks, idesc, (kb | ks) ? 1u : 0u);
-            }
+                    mma_i8(tmem_base + 128, dOnes + 2 * ks, smem_desc_sw64(bb + (2 * kb + (ks >> 1)) * kBTile) + 2 * (ks & 1), idesc,
+                           (kb | ks) ? 1u : 0u);
             tc_commit(mma_done);
         }
+        // the last step also published (into the other buffer): absorb those bytes so no transaction is
+        // in flight towards this CTA when it exits
+        const uint32_t p = (uint32_t)(F & 1);
+        mbar_arrive_expect_tx(hfull0 + 8 * p, kStepBytes);
+        wait_cluster(hfull0 + 8 * p, (uint32_t)((F >> 1) & 1));
     }
 
     tc_fence_before();
