@@ -21,6 +21,8 @@
 #include "kernels.cuh"
 #include "tc_common.cuh"
 
+#include <cstdlib>
+
 namespace umx
 {
 using namespace tc;
@@ -88,6 +90,36 @@ __device__ __forceinline__ float combine_digits(uint32_t d0, uint32_t d1, uint32
     const float b = fmaf((float)(int)d3, 1.0f / 134217728.0f, (float)(int)d2 * (1.0f / 1048576.0f));
     return a + b;
 }
+
+__device__ __forceinline__ bool elect_one()
+{
+    uint32_t pred;
+    asm volatile("{\n\t.reg .pred p;\n\telect.sync _|p, 0xffffffff;\n\tselp.u32 %0, 1, 0, p;\n\t}" : "=r"(pred));
+    return pred != 0;
+}
+// tcgen05.mma kind::i8 with the descriptors given as (lo, hi) words and a compile-time accumulate flag
+__device__ __forceinline__ void mma_i8_lohi(uint32_t d_tmem, uint32_t a_lo, uint32_t a_hi, uint32_t b_lo, uint32_t b_hi, uint32_t idesc,
+                                            bool accumulate)
+{
+    if (accumulate)
+        asm volatile("{\n\t.reg .b64 da, db;\n\t.reg .pred p;\n\tmov.b64 da, {%1, %2};\n\tmov.b64 db, {%3, %4};\n\tsetp.eq.u32 p, 0, 0;\n\t"
+                     "tcgen05.mma.cta_group::1.kind::i8 [%0], da, db, %5, p;\n\t}" ::"r"(d_tmem),
+                     "r"(a_lo), "r"(a_hi), "r"(b_lo), "r"(b_hi), "r"(idesc)
+                     : "memory");
+    else
+        asm volatile("{\n\t.reg .b64 da, db;\n\t.reg .pred p;\n\tmov.b64 da, {%1, %2};\n\tmov.b64 db, {%3, %4};\n\tsetp.ne.u32 p, 0, 0;\n\t"
+                     "tcgen05.mma.cta_group::1.kind::i8 [%0], da, db, %5, p;\n\t}" ::"r"(d_tmem),
+                     "r"(a_lo), "r"(a_hi), "r"(b_lo), "r"(b_hi), "r"(idesc)
+                     : "memory");
+}
+
+// debug (compile with -DUMX_LSTM_TIMING): clock64 stamps of one step of CTA (0,0,0); UMX_LSTM_DEBUG=1 prints them
+__device__ long long g_lstm_dbg[16];
+#ifdef UMX_LSTM_TIMING
+#define UMX_DBG_STAMP(i) do { if (dbg) g_lstm_dbg[i] = clock64(); } while (0)
+#else
+#define UMX_DBG_STAMP(i) do { (void)dbg; } while (0)
+#endif
 
 struct ClusterArgs
 {
@@ -284,8 +316,11 @@ __global__ void __cluster_dims__(kC, 1, 1) __launch_bounds__(kThreads, 1) lstm_c
             const uint32_t pn = (uint32_t)((step + 1) & 1);
             const uint32_t tile = tile0 + pn * kBBuf;
 
+            const bool dbg = (step == 200 && threadIdx.x == 0 && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0);
+            UMX_DBG_STAMP(0);
             mbar_wait(mma_done, (uint32_t)(step & 1));
             tc_fence_after();
+            UMX_DBG_STAMP(1);
 #pragma unroll
             for (int jc = 0; jc < NQ; ++jc)
             {
@@ -330,7 +365,9 @@ __global__ void __cluster_dims__(kC, 1, 1) __launch_bounds__(kThreads, 1) lstm_c
                         a.out_f32[(long)target * a.out_f32_target_stride + ((long)trk * F + t) * (2 * kHhC) + dir * kHhC + k] = h;
                 }
             }
+            UMX_DBG_STAMP(2);
             publish_tile(pn);
+            UMX_DBG_STAMP(3);
 #pragma unroll
             for (int j = 0; j < TP; ++j)
                 xp[j] = xn[j];
@@ -347,41 +384,52 @@ __global__ void __cluster_dims__(kC, 1, 1) __launch_bounds__(kThreads, 1) lstm_c
             }
         }
     }
-    else if (lane == 0)
+    else
     {
-        // ================= MMA issuer =================
+        // ================= MMA issuer: the whole warp runs the loop converged, one elected lane issues =================
         constexpr uint32_t idesc = idesc_i8(128, N, /*a_signed=*/0, /*b_signed=*/1);
-        const uint64_t dOnes = smem_desc_sw128(sOnes);
+        // descriptor low words (address >> 4 | LBO << 16); high words are constants per swizzle mode
+        const uint32_t a_lo = (uint32_t)(smem_desc_sw128(sA) & 0xffffffffu), a_hi = (uint32_t)(smem_desc_sw128(sA) >> 32);
+        const uint32_t o_lo = (uint32_t)(smem_desc_sw128(sOnes) & 0xffffffffu);
+        const uint32_t b_lo0 = (uint32_t)(smem_desc_sw64(sB) & 0xffffffffu), b_hi = (uint32_t)(smem_desc_sw64(sB) >> 32);
         for (int step = 0; step < F; ++step)
         {
             const uint32_t p = (uint32_t)(step & 1);
-            mbar_arrive_expect_tx(hfull0 + 8 * p, kStepBytes); // the 7 peers' bulk copies complete this phase
+            const bool dbg = ((step == 200 || step == 201) && lane == 0 && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0);
+            const int dbo = step == 200 ? 4 : 8;
+            UMX_DBG_STAMP(dbo + 0);
+            if (lane == 0)
+                mbar_arrive_expect_tx(hfull0 + 8 * p, kStepBytes); // the 7 peers' bulk copies complete this phase
             wait_cluster(hfull0 + 8 * p, (uint32_t)((step >> 1) & 1));
             tc_fence_after();
-            const uint32_t bb = sB + p * kBBuf;
+            UMX_DBG_STAMP(dbo + 1);
+            const uint32_t b_lo = b_lo0 + p * (kBBuf >> 4);
+            if (elect_one())
+            {
 #pragma unroll
-            for (int h2 = 0; h2 < 2; ++h2)
+                for (int h2 = 0; h2 < 2; ++h2)
+#pragma unroll
+                    for (int kb = 0; kb < 4; ++kb)
+#pragma unroll
+                        for (int ks = 0; ks < 4; ++ks) // 32 bytes (K = 32) per MMA; B = the h tile of source CTA 2*kb + ks/2
+                            mma_i8_lohi(tmem_base + h2 * 64, a_lo + (((h2 * 4 + kb) * kATile) >> 4) + 2 * ks, a_hi,
+                                        b_lo + (((2 * kb + (ks >> 1)) * kBTile) >> 4) + 2 * (ks & 1), b_hi, idesc, (kb | ks) != 0);
 #pragma unroll
                 for (int kb = 0; kb < 4; ++kb)
-                {
-                    const uint64_t da = smem_desc_sw128(sA + (h2 * 4 + kb) * kATile);
 #pragma unroll
-                    for (int ks = 0; ks < 4; ++ks) // 32 bytes (K = 32) per MMA; the h tile of source CTA 2*kb + ks/2
-                        mma_i8(tmem_base + h2 * 64, da + 2 * ks, smem_desc_sw64(bb + (2 * kb + (ks >> 1)) * kBTile) + 2 * (ks & 1), idesc,
-                               (kb | ks) ? 1u : 0u);
-                }
-#pragma unroll
-            for (int kb = 0; kb < 4; ++kb)
-#pragma unroll
-                for (int ks = 0; ks < 4; ++ks)
-                    mma_i8(tmem_base + 128, dOnes + 2 * ks, smem_desc_sw64(bb + (2 * kb + (ks >> 1)) * kBTile) + 2 * (ks & 1), idesc,
-                           (kb | ks) ? 1u : 0u);
-            tc_commit(mma_done);
+                    for (int ks = 0; ks < 4; ++ks)
+                        mma_i8_lohi(tmem_base + 128, o_lo + 2 * ks, a_hi, b_lo + (((2 * kb + (ks >> 1)) * kBTile) >> 4) + 2 * (ks & 1),
+                                    b_hi, idesc, (kb | ks) != 0);
+                tc_commit(mma_done);
+            }
+            __syncwarp();
+            UMX_DBG_STAMP(dbo + 2);
         }
         // the last step also published (into the other buffer): absorb those bytes so no transaction is
         // in flight towards this CTA when it exits
         const uint32_t p = (uint32_t)(F & 1);
-        mbar_arrive_expect_tx(hfull0 + 8 * p, kStepBytes);
+        if (lane == 0)
+            mbar_arrive_expect_tx(hfull0 + 8 * p, kStepBytes);
         wait_cluster(hfull0 + 8 * p, (uint32_t)((F >> 1) & 1));
     }
 
@@ -427,6 +475,17 @@ int launch_tp(const ClusterArgs &P, int groups, cudaStream_t st)
     dim3 grid(kC, 2 * P.a.target_count, groups);
     lstm_cluster_kernel<TP><<<grid, kThreads, kSmemBytes, st>>>(P);
     UMX_CUDA_OK(cudaGetLastError());
+#ifdef UMX_LSTM_TIMING
+    if (getenv("UMX_LSTM_DEBUG"))
+    {
+        long long h[16];
+        UMX_CUDA_OK(cudaStreamSynchronize(st));
+        UMX_CUDA_OK(cudaMemcpyFromSymbol(h, g_lstm_dbg, sizeof h));
+        fprintf(stderr, "lstm_cluster<%d> step 200: epi wait_begin 0, mma_done +%lld, stored +%lld, shipped +%lld | mma200: wait_begin %+lld, "
+                        "hfull %+lld, issued %+lld | mma201: wait_begin %+lld, hfull %+lld, issued %+lld\n",
+                TP, h[1] - h[0], h[2] - h[0], h[3] - h[0], h[4] - h[0], h[5] - h[0], h[6] - h[0], h[8] - h[0], h[9] - h[0], h[10] - h[0]);
+    }
+#endif
     return 0;
 }
 } // namespace
