@@ -129,6 +129,8 @@ long umx_cuda_session_launches(umx_cuda_session *s);
 /* Launch everything on the caller's cudaStream_t (NULL restores the session's own stream), so a caller
  * can bracket the work with its own CUDA events. */
 int umx_cuda_session_set_stream(umx_cuda_session *s, void *stream);
+/* How many 8-CTA clusters of the recurrence kernel the current device can hold at once (diagnostic). */
+int umx_cuda_lstm_max_active_clusters(void);
 /* Tuning knobs (documented in DESIGN.md): "gemm_terms" 1..3 fp16 split terms per tensor-core GEMM,
  * "gemm_impl" 0 = tcgen05, 1 = SIMT fp32 validation kernel, "lstm_impl" 0 = cluster kernel, 1 = simple. */
 int umx_cuda_session_set_option(umx_cuda_session *s, const char *name, int value);

@@ -36,7 +36,7 @@ EXPORTS = [
     "umx_cuda_demix_device", "umx_cuda_segment_plan", "umx_cuda_stft", "umx_cuda_istft", "umx_cuda_lstm_forward",
     "umx_cuda_wiener", "umx_cuda_target_mags", "umx_cuda_session_set_profiling", "umx_cuda_session_stage_ms",
     "umx_cuda_session_launches", "umx_cuda_session_set_option", "umx_cuda_session_set_stream",
-    "umx_cuda_wiener_noalloc",
+    "umx_cuda_wiener_noalloc", "umx_cuda_lstm_max_active_clusters",
 ]
 
 _lib = None

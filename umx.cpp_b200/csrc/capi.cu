@@ -260,6 +260,8 @@ int umx_cuda_session_set_stream(umx_cuda_session *s, void *stream)
     return 0;
 }
 
+int umx_cuda_lstm_max_active_clusters(void) { return lstm_cluster_max_active(); }
+
 long umx_cuda_session_launches(umx_cuda_session *s) { return s ? s->s->launches : -1; }
 
 int umx_cuda_session_set_option(umx_cuda_session *s, const char *name, int value)

@@ -29,7 +29,7 @@ constexpr int kABytes = BM * BK * 2;       // 16 KB
 constexpr int kBBytes = BN * BK * 2;       // 32 KB
 constexpr int kStageBytes = kABytes + kBBytes;
 constexpr int kEpiWarps = 4;
-constexpr int kEpiBytesPerWarp = 32 * 33 * 4;
+constexpr int kEpiBytesPerWarp = 32 * 36 * 4; // 32 rows x (32 + 4 pad) floats
 constexpr int kSmemBytes = kStages * kStageBytes + kEpiWarps * kEpiBytesPerWarp + 256 + 1024; // + barriers + align slack
 constexpr int kThreads = 32 * (2 + kEpiWarps);
 constexpr uint32_t kTmemCols = 512;
@@ -188,15 +188,26 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_tc_kernel(const __grid_const
     else
     {
         // ================= epilogue =================
+        // TMEM lane = output row.  Each 32-column chunk is transposed through a per-warp SMEM tile with
+        // 128-bit accesses (row pitch 36 floats: conflict-free), so that 8 lanes cover one row's 32 columns
+        // and every global store instruction writes four full 128-byte lines.
         const int q = warp & 3; // TMEM lane quadrant this warp may read
         float *stage_buf = reinterpret_cast<float *>(epi_base + (warp - 2) * kEpiBytesPerWarp);
+        const int sub = lane >> 3, c4 = (lane & 7) * 4;
         int acc = 0;
         uint32_t acc_phase = 0;
         for (int tile = blockIdx.x; tile < P.total_tiles; tile += gridDim.x)
         {
             int pi, m0, n0;
             locate(tile, pi, m0, n0);
-            const TcProblem &pb = P.p[pi];
+            // hoist the problem description into registers once per tile
+            const int M = P.p[pi].M, N = P.p[pi].N, ldo = P.p[pi].ldo, act = P.p[pi].act, n_group = P.p[pi].n_group;
+            const long gstride = P.p[pi].group_stride;
+            const float *__restrict__ alpha = P.p[pi].alpha;
+            const float *__restrict__ beta = P.p[pi].beta;
+            float *__restrict__ of32 = P.p[pi].out_f32;
+            __half *__restrict__ ohi = P.p[pi].out_hi;
+            __half *__restrict__ olo = P.p[pi].out_lo;
             mbar_wait(tfull0 + 8 * acc, acc_phase);
             tc_fence_after();
             const uint32_t taddr = tmem_base + acc * BN + ((uint32_t)(32 * q) << 16);
@@ -214,36 +225,71 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_tc_kernel(const __grid_const
                     if (lane == 0)
                         mbar_arrive(tempty0 + 8 * acc);
                 }
-                const int n = n0 + ch * 32 + lane;
-                if (n0 + ch * 32 >= pb.N)
+                const int nc0 = n0 + ch * 32;
+                if (nc0 >= N)
                     continue;
-                // transpose 32x32 through smem: lane = row -> lane = column
 #pragma unroll
-                for (int c = 0; c < 32; ++c)
-                    stage_buf[lane * 33 + c] = __uint_as_float(r[c]);
+                for (int i = 0; i < 8; ++i)
+                    *reinterpret_cast<float4 *>(stage_buf + lane * 36 + 4 * i) =
+                        make_float4(__uint_as_float(r[4 * i]), __uint_as_float(r[4 * i + 1]), __uint_as_float(r[4 * i + 2]),
+                                    __uint_as_float(r[4 * i + 3]));
                 __syncwarp();
-                const bool col_ok = n < pb.N;
-                const float al = (col_ok && pb.alpha) ? pb.alpha[n] : 1.f;
-                const float be = (col_ok && pb.beta) ? pb.beta[n] : 0.f;
-                const long obase = col_ok ? (long)(n / pb.n_group) * pb.group_stride + (n % pb.n_group) : 0;
-#pragma unroll 4
-                for (int rr = 0; rr < 32; ++rr)
+                const int n = nc0 + c4;
+                float al[4], be[4];
+#pragma unroll
+                for (int e = 0; e < 4; ++e)
                 {
-                    const int m = row0 + rr;
-                    if (m >= pb.M)
-                        break;
-                    if (col_ok)
+                    const bool ok = n + e < N;
+                    al[e] = (alpha && ok) ? __ldg(alpha + n + e) : 1.f;
+                    be[e] = (beta && ok) ? __ldg(beta + n + e) : 0.f;
+                }
+                const int grp = n / n_group;
+                const long obase = (long)grp * gstride + (n - grp * n_group);
+                const bool full4 = n + 3 < N;
+#pragma unroll
+                for (int it = 0; it < 8; ++it)
+                {
+                    const int row = it * 4 + sub;
+                    const int m = row0 + row;
+                    const float4 t4 = *reinterpret_cast<const float4 *>(stage_buf + row * 36 + c4);
+                    float v[4] = {t4.x, t4.y, t4.z, t4.w};
+#pragma unroll
+                    for (int e = 0; e < 4; ++e)
+                        v[e] = act_apply(fmaf(v[e], al[e], be[e]), act);
+                    if (m < M && n < N)
                     {
-                        const float v = act_apply(fmaf(stage_buf[rr * 33 + lane], al, be), pb.act);
-                        const long o = obase + (long)m * pb.ldo;
-                        if (pb.out_f32)
-                            pb.out_f32[o] = v;
-                        if (pb.out_hi)
+                        const long o = obase + (long)m * ldo;
+                        if (of32)
                         {
-                            __half h, l;
-                            split_half(v, h, l);
-                            pb.out_hi[o] = h;
-                            pb.out_lo[o] = l;
+                            if (full4)
+                                *reinterpret_cast<float4 *>(of32 + o) = make_float4(v[0], v[1], v[2], v[3]);
+                            else
+                                for (int e = 0; e < 4; ++e)
+                                    if (n + e < N)
+                                        of32[o + e] = v[e];
+                        }
+                        if (ohi)
+                        {
+                            __half h[4], l[4];
+#pragma unroll
+                            for (int e = 0; e < 4; ++e)
+                                split_half(v[e], h[e], l[e]);
+                            if (full4)
+                            {
+                                *reinterpret_cast<uint2 *>(ohi + o) =
+                                    make_uint2((uint32_t)__half_as_ushort(h[0]) | ((uint32_t)__half_as_ushort(h[1]) << 16),
+                                               (uint32_t)__half_as_ushort(h[2]) | ((uint32_t)__half_as_ushort(h[3]) << 16));
+                                *reinterpret_cast<uint2 *>(olo + o) =
+                                    make_uint2((uint32_t)__half_as_ushort(l[0]) | ((uint32_t)__half_as_ushort(l[1]) << 16),
+                                               (uint32_t)__half_as_ushort(l[2]) | ((uint32_t)__half_as_ushort(l[3]) << 16));
+                            }
+                            else
+                                for (int e = 0; e < 4; ++e)
+                                    if (n + e < N)
+                                    {
+                                        ohi[o + e] = h[e];
+                                        olo[o + e] = l[e];
+                                    }
                         }
                     }
                 }
@@ -320,6 +366,8 @@ int launch_gemm_tc(const GemmBatch &batch, int terms, cudaStream_t st)
     {
         const GemmProblem &g = batch.p[i];
         UMX_CHECK(g.M > 0 && g.N > 0 && g.K > 0, "gemm_tc: empty problem");
+        UMX_CHECK(g.ldo % 4 == 0 && g.n_group % 4 == 0 && g.group_stride % 4 == 0,
+                  "gemm_tc: output pitch, column group and group stride must be multiples of 4 (vector stores)");
         UMX_CHECK(g.A.lo != nullptr && g.B.lo != nullptr, "gemm_tc: operands need hi and lo planes");
         if (make_map(&P.a_hi[i], g.A.hi, g.K, g.M, g.A.ld, BM) || make_map(&P.a_lo[i], g.A.lo, g.K, g.M, g.A.ld, BM) ||
             make_map(&P.b_hi[i], g.B.hi, g.K, g.N, g.B.ld, BN) || make_map(&P.b_lo[i], g.B.lo, g.K, g.N, g.B.ld, BN))

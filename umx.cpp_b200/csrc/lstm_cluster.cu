@@ -501,6 +501,28 @@ int launch_whh_image(const uint8_t *q, uint8_t *img, cudaStream_t st)
 
 bool lstm_cluster_supported(int Hh) { return Hh == kHhC; }
 
+// how many 8-CTA clusters of the recurrence kernel the current device can run at once (0 on error)
+int lstm_cluster_max_active()
+{
+    int n = 0;
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3(kC, 64, 1);
+    cfg.blockDim = dim3(kThreads);
+    cfg.dynamicSmemBytes = kSmemBytes;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeClusterDimension;
+    at[0].val.clusterDim.x = kC;
+    at[0].val.clusterDim.y = 1;
+    at[0].val.clusterDim.z = 1;
+    cfg.attrs = at;
+    cfg.numAttrs = 1;
+    if (cudaFuncSetAttribute(lstm_cluster_kernel<16>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes) != cudaSuccess)
+        return 0;
+    if (cudaOccupancyMaxActiveClusters(&n, lstm_cluster_kernel<16>, &cfg) != cudaSuccess)
+        return 0;
+    return n;
+}
+
 int launch_lstm_cluster(const LstmLayerArgs &a, const uint8_t *const (*img)[2], cudaStream_t st)
 {
     UMX_CHECK(a.Hh == kHhC, "lstm_cluster: built for 512 hidden units per direction (UMX-L)");
