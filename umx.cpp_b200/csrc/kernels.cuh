@@ -24,6 +24,14 @@ struct IstftTrack
     int accumulate;       // 1: out[off+k] += w[k]*y[k] (umx.cpp:234-249), 0: plain store
 };
 
+struct FinalizeTrack
+{
+    const float2 *acc; // [n_stems][L] weighted overlap-add accumulator of the shifted track
+    float2 *out;       // [n_stems][n]
+    long L, n;
+    long i_begin, i_end; // output sample range to finalise
+};
+
 constexpr int kIstftFramesPerCta = 16;
 
 int init_fft_tables(int device);
@@ -31,7 +39,7 @@ int launch_stft(const StftTrack *d_tracks, int n_tracks, int n_buf, float2 *spec
                 float *maxabs, cudaStream_t st);
 int launch_istft(const float2 *stems, long stem_stride, int n_stems, const IstftTrack *d_tracks, int n_tracks,
                  int n_buf, cudaStream_t st);
-int launch_finalize(const float2 *acc, long L, float2 *out, long n, int shift, int n_buf, int stride, int n_stems,
+int launch_finalize(const FinalizeTrack *d_tracks, int n_tracks, long max_range, int shift, int n_buf, int stride, int n_stems,
                     cudaStream_t st);
 int launch_to_ref_layout_c64(const float2 *in, float2 *out, int F, cudaStream_t st);
 int launch_from_ref_layout_c64(const float2 *in, float2 *out, int F, cudaStream_t st);

@@ -97,6 +97,12 @@ int session_create(Model *m, int max_tracks, int n_buf, Session **out)
         return fail(-1);
     }
     s->st = s->own_st;
+    if (cudaStreamCreateWithFlags(&s->st_in, cudaStreamNonBlocking) != cudaSuccess ||
+        cudaStreamCreateWithFlags(&s->st_out, cudaStreamNonBlocking) != cudaSuccess)
+    {
+        set_error("session_create: cudaStreamCreate failed");
+        return fail(-1);
+    }
     int rc = 0;
     rc |= salloc(s, &s->spec, M * 2 * kBins);
     rc |= salloc(s, &s->xh, M * kFc1InPad, true); // pad columns stay zero
@@ -140,11 +146,15 @@ int ensure_desc_capacity(Session *s, int segs)
         cudaFree(s->d_stft);
     if (s->d_istft)
         cudaFree(s->d_istft);
+    if (s->d_final)
+        cudaFree(s->d_final);
     s->d_stft = nullptr;
     s->d_istft = nullptr;
+    s->d_final = nullptr;
     s->seg_cap = 0;
     UMX_CUDA_OK(cudaMalloc(&s->d_stft, sizeof(StftTrack) * (size_t)segs * s->T));
     UMX_CUDA_OK(cudaMalloc(&s->d_istft, sizeof(IstftTrack) * (size_t)segs * s->T));
+    UMX_CUDA_OK(cudaMalloc(&s->d_final, sizeof(FinalizeTrack) * (size_t)segs * s->T));
     s->seg_cap = segs;
     return 0;
 }
@@ -167,6 +177,13 @@ void session_destroy(Session *s)
         cudaFree(p);
     cudaFree(s->d_stft);
     cudaFree(s->d_istft);
+    cudaFree(s->d_final);
+    for (auto e : s->ev_pool)
+        cudaEventDestroy(e);
+    if (s->st_in)
+        cudaStreamDestroy(s->st_in);
+    if (s->st_out)
+        cudaStreamDestroy(s->st_out);
     if (s->own_st)
         cudaStreamDestroy(s->own_st);
     delete s;
@@ -439,8 +456,19 @@ int session_infer_segment(Session *s, const float *audio, int n, float *out)
 // ---- shift_inference + split_inference (umx.cpp:99-295) ------------------------------------------------
 static int stride_of(int n_buf) { return (int)((1 - 0.25f) * n_buf); } // umx.cpp:180
 
+static cudaEvent_t take_event(Session *s, size_t &cursor)
+{
+    if (cursor == s->ev_pool.size())
+    {
+        cudaEvent_t e;
+        cudaEventCreateWithFlags(&e, cudaEventDisableTiming);
+        s->ev_pool.push_back(e);
+    }
+    return s->ev_pool[cursor++];
+}
+
 int session_demix_device(Session *s, const float *const *d_audio, const int64_t *n_samples, int n_tracks,
-                         int shift_offset, float *const *d_out)
+                         int shift_offset, float *const *d_out, const float *const *host_in, float *const *host_out)
 {
     UMX_CHECK(n_tracks >= 1 && n_tracks <= s->T, "umx_cuda_demix: n_tracks must be in [1, max_tracks]");
     // umx.cpp:120-122 places N samples at column `offset` of an (N + 22050 - offset)-column buffer: only
@@ -463,6 +491,13 @@ int session_demix_device(Session *s, const float *const *d_audio, const int64_t 
     // descriptors for every (segment, track); tracks that have ended run an empty chunk
     std::vector<StftTrack> hs((size_t)max_segs * s->T);
     std::vector<IstftTrack> hi((size_t)max_segs * s->T);
+    std::vector<FinalizeTrack> hf((size_t)max_segs * s->T);
+    // output range that is final once segment sg has been added: shifted positions below (sg+1)*stride
+    auto final_end = [&](int i, int sg) {
+        const long e = (sg == max_segs - 1) ? (long)n_samples[i] : (long)(sg + 1) * stride - shift_offset;
+        return std::max(0L, std::min((long)n_samples[i], e));
+    };
+    std::vector<long> max_range(max_segs, 0);
     for (int i = 0; i < n_tracks; ++i)
     {
         if (grow(&s->acc_pool[i], &s->acc_cap[i], 4 * L[i]))
@@ -475,24 +510,65 @@ int session_demix_device(Session *s, const float *const *d_audio, const int64_t 
             hs[(size_t)sg * s->T + i] = {reinterpret_cast<const float2 *>(d_audio[i]), (long)n_samples[i],
                                          off - shift_offset, clen, 0};
             hi[(size_t)sg * s->T + i] = {s->acc_pool[i], L[i], off, clen, 1};
+            const long b = sg == 0 ? 0 : final_end(i, sg - 1), e = final_end(i, sg);
+            hf[(size_t)sg * s->T + i] = {s->acc_pool[i], reinterpret_cast<float2 *>(d_out[i]), L[i], (long)n_samples[i], b, e};
+            max_range[sg] = std::max(max_range[sg], e - b);
         }
     }
     UMX_CUDA_OK(cudaMemcpyAsync(s->d_stft, hs.data(), sizeof(StftTrack) * hs.size(), cudaMemcpyHostToDevice, s->st));
     UMX_CUDA_OK(cudaMemcpyAsync(s->d_istft, hi.data(), sizeof(IstftTrack) * hi.size(), cudaMemcpyHostToDevice, s->st));
-    UMX_CUDA_OK(cudaStreamSynchronize(s->st)); // hs/hi are pageable host vectors
+    UMX_CUDA_OK(cudaMemcpyAsync(s->d_final, hf.data(), sizeof(FinalizeTrack) * hf.size(), cudaMemcpyHostToDevice, s->st));
+    UMX_CUDA_OK(cudaStreamSynchronize(s->st)); // hs/hi/hf are pageable host vectors
+
+    size_t ev = 0;
+    std::vector<long> copied_in(n_tracks, 0);
     for (int sg = 0; sg < max_segs; ++sg) // sequential: h/c stream from segment to segment
+    {
+        if (host_in)
+        { // the samples this segment reads: original indices below sg*stride - shift + n_buf
+            for (int i = 0; i < n_tracks; ++i)
+            {
+                const long need = std::max(0L, std::min((long)n_samples[i], (long)sg * stride - shift_offset + s->n_buf));
+                if (need > copied_in[i])
+                {
+                    UMX_CUDA_OK(cudaMemcpyAsync(const_cast<float *>(d_audio[i]) + 2 * copied_in[i], host_in[i] + 2 * copied_in[i],
+                                                sizeof(float2) * (size_t)(need - copied_in[i]), cudaMemcpyHostToDevice, s->st_in));
+                    copied_in[i] = need;
+                }
+            }
+            cudaEvent_t e = take_event(s, ev);
+            UMX_CUDA_OK(cudaEventRecord(e, s->st_in));
+            UMX_CUDA_OK(cudaStreamWaitEvent(s->st, e, 0));
+        }
         if (int rc = session_run_segment(s, sg, n_tracks))
             return rc;
-    {
-        StageScope sc(s, "finalize");
-        for (int i = 0; i < n_tracks; ++i)
         {
+            StageScope sc(s, "finalize");
             s->launches++;
-            if (int rc = launch_finalize(s->acc_pool[i], L[i], reinterpret_cast<float2 *>(d_out[i]), (long)n_samples[i],
-                                         shift_offset, s->n_buf, stride, 4, s->st))
+            if (int rc = launch_finalize(s->d_final + (size_t)sg * s->T, n_tracks, max_range[sg], shift_offset, s->n_buf, stride, 4, s->st))
                 return rc;
         }
+        if (host_out)
+        { // ship the finished range of every stem while the next segment computes
+            cudaEvent_t e = take_event(s, ev);
+            UMX_CUDA_OK(cudaEventRecord(e, s->st));
+            UMX_CUDA_OK(cudaStreamWaitEvent(s->st_out, e, 0));
+            for (int i = 0; i < n_tracks; ++i)
+            {
+                const FinalizeTrack &f = hf[(size_t)sg * s->T + i];
+                if (f.i_end <= f.i_begin)
+                    continue;
+                for (int stem = 0; stem < 4; ++stem)
+                {
+                    const size_t o = 2 * ((size_t)stem * n_samples[i] + f.i_begin);
+                    UMX_CUDA_OK(cudaMemcpyAsync(host_out[i] + o, d_out[i] + o, sizeof(float2) * (size_t)(f.i_end - f.i_begin),
+                                                cudaMemcpyDeviceToHost, s->st_out));
+                }
+            }
+        }
     }
+    if (host_out)
+        UMX_CUDA_OK(cudaStreamSynchronize(s->st_out));
     return 0;
 }
 
@@ -504,27 +580,17 @@ int session_demix_host(Session *s, const float *const *audio, const int64_t *n_s
     session_begin_profile(s);
     std::vector<const float *> din(n_tracks);
     std::vector<float *> dout(n_tracks);
+    for (int i = 0; i < n_tracks; ++i)
     {
-        StageScope sc(s, "h2d");
-        for (int i = 0; i < n_tracks; ++i)
-        {
-            const long n = std::max<long>((long)n_samples[i], 1);
-            if (grow(&s->in_pool[i], &s->in_cap[i], n) || grow(&s->out_pool[i], &s->out_cap[i], 4 * n))
-                return -1;
-            UMX_CUDA_OK(cudaMemcpyAsync(s->in_pool[i], audio[i], sizeof(float2) * (size_t)n_samples[i],
-                                        cudaMemcpyHostToDevice, s->st));
-            din[i] = reinterpret_cast<const float *>(s->in_pool[i]);
-            dout[i] = reinterpret_cast<float *>(s->out_pool[i]);
-        }
+        const long n = std::max<long>((long)n_samples[i], 1);
+        if (grow(&s->in_pool[i], &s->in_cap[i], n) || grow(&s->out_pool[i], &s->out_cap[i], 4 * n))
+            return -1;
+        din[i] = reinterpret_cast<const float *>(s->in_pool[i]);
+        dout[i] = reinterpret_cast<float *>(s->out_pool[i]);
     }
-    if (int rc = session_demix_device(s, din.data(), n_samples, n_tracks, shift_offset, dout.data()))
+    // inputs stream in and finished output ranges stream out on their own copy streams, segment by segment
+    if (int rc = session_demix_device(s, din.data(), n_samples, n_tracks, shift_offset, dout.data(), audio, out))
         return rc;
-    {
-        StageScope sc(s, "d2h");
-        for (int i = 0; i < n_tracks; ++i)
-            UMX_CUDA_OK(cudaMemcpyAsync(out[i], s->out_pool[i], sizeof(float2) * 4 * (size_t)n_samples[i],
-                                        cudaMemcpyDeviceToHost, s->st));
-    }
     UMX_CUDA_OK(cudaStreamSynchronize(s->st));
     return session_end_profile(s);
 }

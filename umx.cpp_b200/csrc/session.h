@@ -45,7 +45,10 @@ struct Session
 
     StftTrack *d_stft = nullptr;   // descriptor arrays [seg_cap][T]
     IstftTrack *d_istft = nullptr;
+    FinalizeTrack *d_final = nullptr;
     int seg_cap = 0;
+    cudaStream_t st_in = nullptr, st_out = nullptr; // host<->device copy streams (overlap with compute)
+    std::vector<cudaEvent_t> ev_pool;
 
     // grow-only pools for whole-track demixing
     std::vector<float2 *> acc_pool, in_pool, out_pool;
@@ -68,8 +71,11 @@ int session_reset(Session *s);
 int session_run_segment(Session *s, int seg, int n_tracks);
 int session_network(Session *s, int n_tracks);
 int session_lstm(Session *s, int n_tracks, int target_begin, int target_count, bool want_f32);
+// host_in / host_out (optional): stream the inputs in and the finished output ranges out, segment by segment,
+// on the copy streams while the compute stream keeps going
 int session_demix_device(Session *s, const float *const *d_audio, const int64_t *n_samples, int n_tracks,
-                         int shift_offset, float *const *d_out);
+                         int shift_offset, float *const *d_out, const float *const *host_in = nullptr,
+                         float *const *host_out = nullptr);
 int session_demix_host(Session *s, const float *const *audio, const int64_t *n_samples, int n_tracks,
                        int shift_offset, float *const *out);
 int session_infer_segment(Session *s, const float *audio, int n, float *out);

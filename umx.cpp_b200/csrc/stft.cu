@@ -289,13 +289,14 @@ __global__ void __launch_bounds__(256) istft_kernel(const float2 *__restrict__ s
 }
 
 // ------------------------------------------------------------------------------------------------
-// out = acc / sum_weight, trimmed to the original track (umx.cpp:251-273,136-147)
+// out = acc / sum_weight, trimmed to the original track (umx.cpp:251-273,136-147); output samples
+// [i_begin, i_end) of each track (a range is final as soon as the last segment touching it has been added)
 // ------------------------------------------------------------------------------------------------
-__global__ void finalize_kernel(const float2 *__restrict__ acc, long L, float2 *__restrict__ out, long n,
-                                int shift, int n_buf, int stride, int n_stems)
+__global__ void finalize_kernel(const FinalizeTrack *__restrict__ tracks, int shift, int n_buf, int stride, int n_stems)
 {
-    const long i = (long)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n)
+    const FinalizeTrack tk = tracks[blockIdx.y];
+    const long i = tk.i_begin + (long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= tk.i_end)
         return;
     const long p = i + shift;
     // segments s with s*stride <= p < s*stride + chunk_len(s), added in increasing s
@@ -304,17 +305,17 @@ __global__ void finalize_kernel(const float2 *__restrict__ acc, long L, float2 *
     for (long sgm = (s_hi > 0 ? s_hi - 1 : 0); sgm <= s_hi; ++sgm)
     {
         const long off = sgm * stride;
-        if (off >= L)
+        if (off >= tk.L)
             continue;
-        const long clen = min((long)n_buf, L - off);
+        const long clen = min((long)n_buf, tk.L - off);
         const long k = p - off;
         if (k >= 0 && k < clen)
             sw += tri_weight((int)k, n_buf);
     }
     for (int st = 0; st < n_stems; ++st)
     {
-        const float2 a = acc[(long)st * L + p];
-        out[(long)st * n + i] = make_float2(a.x / sw, a.y / sw);
+        const float2 a = tk.acc[(long)st * tk.L + p];
+        tk.out[(long)st * tk.n + i] = make_float2(a.x / sw, a.y / sw);
     }
 }
 
@@ -397,12 +398,12 @@ int launch_istft(const float2 *stems, long stem_stride, int n_stems, const Istft
     return 0;
 }
 
-int launch_finalize(const float2 *acc, long L, float2 *out, long n, int shift, int n_buf, int stride, int n_stems,
+int launch_finalize(const FinalizeTrack *d_tracks, int n_tracks, long max_range, int shift, int n_buf, int stride, int n_stems,
                     cudaStream_t st)
 {
-    if (n <= 0)
+    if (max_range <= 0 || n_tracks <= 0)
         return 0;
-    finalize_kernel<<<ceil_div(n, 256), 256, 0, st>>>(acc, L, out, n, shift, n_buf, stride, n_stems);
+    finalize_kernel<<<dim3(ceil_div(max_range, 256), n_tracks), 256, 0, st>>>(d_tracks, shift, n_buf, stride, n_stems);
     UMX_CUDA_OK(cudaGetLastError());
     return 0;
 }
