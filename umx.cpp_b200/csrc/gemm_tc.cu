@@ -23,14 +23,25 @@ using namespace tc;
 
 namespace
 {
-constexpr int BM = 128, BN = 256, BK = 64; // BK fp16 = 128 bytes = one swizzle row
-constexpr int kStages = 4;
-constexpr int kABytes = BM * BK * 2;       // 16 KB
-constexpr int kBBytes = BN * BK * 2;       // 32 KB
-constexpr int kStageBytes = kABytes + kBBytes;
+constexpr int BM = 128, BN = 256;
+// One pipeline stage holds, for one k-block, every operand plane the chosen precision needs, so each plane is
+// fetched from L2 once per k-block however many MMA passes use it:
+//   TERMS 1: A_hi, B_hi              k-block 64 (128-byte rows, SWIZZLE_128B)   48 KB/stage, 4 stages
+//   TERMS 2: A_hi, A_lo, B_hi        k-block 32 ( 64-byte rows, SWIZZLE_64B)    32 KB/stage, 6 stages
+//   TERMS 3: A_hi, A_lo, B_hi, B_lo  k-block 32 ( 64-byte rows, SWIZZLE_64B)    48 KB/stage, 4 stages
+template <int TERMS>
+struct Cfg
+{
+    static constexpr int BK = TERMS == 1 ? 64 : 32;
+    static constexpr int nA = TERMS >= 2 ? 2 : 1, nB = TERMS == 3 ? 2 : 1;
+    static constexpr int kAPlane = BM * BK * 2, kBPlane = BN * BK * 2;
+    static constexpr int kStageBytes = nA * kAPlane + nB * kBPlane;
+    static constexpr int kStages = TERMS == 2 ? 6 : 4;
+};
 constexpr int kEpiWarps = 4;
 constexpr int kEpiBytesPerWarp = 32 * 36 * 4; // 32 rows x (32 + 4 pad) floats
-constexpr int kSmemBytes = kStages * kStageBytes + kEpiWarps * kEpiBytesPerWarp + 256 + 1024; // + barriers + align slack
+constexpr int kMaxStages = 6;
+constexpr int kSmemBytes = 4 * 49152 + kEpiWarps * kEpiBytesPerWarp + 256 + 1024; // stages + epilogue + barriers + align slack
 constexpr int kThreads = 32 * (2 + kEpiWarps);
 constexpr uint32_t kTmemCols = 512;
 
@@ -66,17 +77,28 @@ __device__ __forceinline__ float act_apply(float v, int act)
     return v;
 }
 
+// 64-byte-row K-major tile, 64-byte swizzle: 8-row groups 512 bytes apart
+__device__ __forceinline__ uint64_t smem_desc_sw64(uint32_t smem_addr)
+{
+    return (uint64_t)((smem_addr & 0x3FFFF) >> 4) | ((uint64_t)1 << 16) | ((uint64_t)(512 >> 4) << 32) | ((uint64_t)1 << 46) |
+           ((uint64_t)4 << 61);
+}
+
+template <int TERMS>
 __global__ void __launch_bounds__(kThreads, 1) gemm_tc_kernel(const __grid_constant__ TcParams P)
 {
+    using C = Cfg<TERMS>;
+    constexpr int BK = C::BK, kStages = C::kStages, kStageBytes = C::kStageBytes, kAPlane = C::kAPlane, kBPlane = C::kBPlane;
+    static_assert(kStages * kStageBytes <= 4 * 49152 && kStages <= kMaxStages, "stage ring does not fit");
     extern __shared__ uint8_t smem_raw[];
     // 1024-byte alignment for the 128-byte swizzle atoms
     uint8_t *smem = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-    uint8_t *epi_base = smem + kStages * kStageBytes;
+    uint8_t *epi_base = smem + 4 * 49152;
     uint64_t *bars = reinterpret_cast<uint64_t *>(epi_base + kEpiWarps * kEpiBytesPerWarp);
-    // bars: full[kStages], empty[kStages], tmem_full[2], tmem_empty[2], then the TMEM base address
-    const uint32_t full0 = smem_u32(bars), empty0 = smem_u32(bars + kStages);
-    const uint32_t tfull0 = smem_u32(bars + 2 * kStages), tempty0 = smem_u32(bars + 2 * kStages + 2);
-    uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + 2 * kStages + 4);
+    // bars: full[kMaxStages], empty[kMaxStages], tmem_full[2], tmem_empty[2], then the TMEM base address
+    const uint32_t full0 = smem_u32(bars), empty0 = smem_u32(bars + kMaxStages);
+    const uint32_t tfull0 = smem_u32(bars + 2 * kMaxStages), tempty0 = smem_u32(bars + 2 * kMaxStages + 2);
+    uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + 2 * kMaxStages + 4);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
@@ -123,22 +145,23 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_tc_kernel(const __grid_const
                 locate(tile, pi, m0, n0);
                 const int kblocks = (P.p[pi].K + BK - 1) / BK;
                 for (int kb = 0; kb < kblocks; ++kb)
-                    for (int term = 0; term < P.terms; ++term)
+                {
+                    mbar_wait(empty0 + 8 * stage, phase ^ 1);
+                    const uint32_t bar = full0 + 8 * stage;
+                    mbar_arrive_expect_tx(bar, kStageBytes);
+                    const uint32_t sa = smem_u32(smem + stage * kStageBytes);
+                    tma_load_2d(sa, &P.a_hi[pi], kb * BK, m0, bar);
+                    if (C::nA == 2)
+                        tma_load_2d(sa + kAPlane, &P.a_lo[pi], kb * BK, m0, bar);
+                    tma_load_2d(sa + C::nA * kAPlane, &P.b_hi[pi], kb * BK, n0, bar);
+                    if (C::nB == 2)
+                        tma_load_2d(sa + C::nA * kAPlane + kBPlane, &P.b_lo[pi], kb * BK, n0, bar);
+                    if (++stage == kStages)
                     {
-                        mbar_wait(empty0 + 8 * stage, phase ^ 1);
-                        const uint32_t bar = full0 + 8 * stage;
-                        mbar_arrive_expect_tx(bar, kStageBytes);
-                        const CUtensorMap *ma = (term == 1) ? &P.a_lo[pi] : &P.a_hi[pi];
-                        const CUtensorMap *mb = (term == 2) ? &P.b_lo[pi] : &P.b_hi[pi];
-                        const uint32_t sa = smem_u32(smem + stage * kStageBytes);
-                        tma_load_2d(sa, ma, kb * BK, m0, bar);
-                        tma_load_2d(sa + kABytes, mb, kb * BK, n0, bar);
-                        if (++stage == kStages)
-                        {
-                            stage = 0;
-                            phase ^= 1;
-                        }
+                        stage = 0;
+                        phase ^= 1;
                     }
+                }
             }
         }
     }
@@ -156,7 +179,7 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_tc_kernel(const __grid_const
             {
                 int pi, m0, n0;
                 locate(tile, pi, m0, n0);
-                const int kiters = ((P.p[pi].K + BK - 1) / BK) * P.terms;
+                const int kiters = (P.p[pi].K + BK - 1) / BK;
                 mbar_wait(tempty0 + 8 * acc, acc_phase ^ 1); // epilogue has drained this accumulator
                 tc_fence_after();
                 const uint32_t d_tmem = tmem_base + acc * BN;
@@ -165,10 +188,18 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_tc_kernel(const __grid_const
                     mbar_wait(full0 + 8 * stage, phase);
                     tc_fence_after();
                     const uint32_t sa = smem_u32(smem + stage * kStageBytes);
-                    const uint64_t da = smem_desc_sw128(sa), db = smem_desc_sw128(sa + kABytes);
+                    const uint32_t sb = sa + C::nA * kAPlane;
+                    auto desc = [](uint32_t addr) { return TERMS == 1 ? smem_desc_sw128(addr) : smem_desc_sw64(addr); };
+                    const uint64_t a_hi = desc(sa), b_hi = desc(sb);
 #pragma unroll
                     for (int k = 0; k < BK / 16; ++k) // +32 bytes per K=16 step inside the swizzle row
-                        mma_f16(d_tmem, da + 2 * k, db + 2 * k, idesc, (it > 0 || k > 0) ? 1u : 0u);
+                    {
+                        mma_f16(d_tmem, a_hi + 2 * k, b_hi + 2 * k, idesc, (it > 0 || k > 0) ? 1u : 0u); // hi * hi
+                        if (C::nA == 2)
+                            mma_f16(d_tmem, desc(sa + kAPlane) + 2 * k, b_hi + 2 * k, idesc, 1u);          // lo * hi
+                        if (C::nB == 2)
+                            mma_f16(d_tmem, a_hi + 2 * k, desc(sb + kBPlane) + 2 * k, idesc, 1u);          // hi * lo
+                    }
                     tc_commit(empty0 + 8 * stage); // frees the smem slot when these MMAs retire
                     if (++stage == kStages)
                     {
@@ -331,18 +362,19 @@ EncodeTiledFn get_encode_fn()
     return fn;
 }
 
-// 2-D fp16 K-major operand: dims (K, rows), row pitch ld elements, box (64, box_rows), 128-byte swizzle
-int make_map(CUtensorMap *map, const __half *ptr, int K, int rows, int ld, int box_rows)
+// 2-D fp16 K-major operand: dims (K, rows), row pitch ld elements, box (bk, box_rows), swizzle = row bytes
+int make_map(CUtensorMap *map, const __half *ptr, int K, int rows, int ld, int box_rows, int bk)
 {
     EncodeTiledFn fn = get_encode_fn();
     UMX_CHECK(fn != nullptr, "cuTensorMapEncodeTiled is not available from the CUDA driver");
     UMX_CHECK((reinterpret_cast<uintptr_t>(ptr) & 15) == 0 && (ld % 8) == 0, "GEMM operand must be 16-byte aligned with a 16-byte row pitch");
     const cuuint64_t dims[2] = {(cuuint64_t)K, (cuuint64_t)rows};
     const cuuint64_t strides[1] = {(cuuint64_t)ld * 2};
-    const cuuint32_t box[2] = {(cuuint32_t)BK, (cuuint32_t)box_rows};
+    const cuuint32_t box[2] = {(cuuint32_t)bk, (cuuint32_t)box_rows};
     const cuuint32_t estr[2] = {1, 1};
     const CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, const_cast<__half *>(ptr), dims, strides, box, estr,
-                          CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                          CU_TENSOR_MAP_INTERLEAVE_NONE, bk == 64 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B,
+                          CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                           CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS)
     {
@@ -369,8 +401,9 @@ int launch_gemm_tc(const GemmBatch &batch, int terms, cudaStream_t st)
         UMX_CHECK(g.ldo % 4 == 0 && g.n_group % 4 == 0 && g.group_stride % 4 == 0,
                   "gemm_tc: output pitch, column group and group stride must be multiples of 4 (vector stores)");
         UMX_CHECK(g.A.lo != nullptr && g.B.lo != nullptr, "gemm_tc: operands need hi and lo planes");
-        if (make_map(&P.a_hi[i], g.A.hi, g.K, g.M, g.A.ld, BM) || make_map(&P.a_lo[i], g.A.lo, g.K, g.M, g.A.ld, BM) ||
-            make_map(&P.b_hi[i], g.B.hi, g.K, g.N, g.B.ld, BN) || make_map(&P.b_lo[i], g.B.lo, g.K, g.N, g.B.ld, BN))
+        const int bk = terms == 1 ? 64 : 32;
+        if (make_map(&P.a_hi[i], g.A.hi, g.K, g.M, g.A.ld, BM, bk) || make_map(&P.a_lo[i], g.A.lo, g.K, g.M, g.A.ld, BM, bk) ||
+            make_map(&P.b_hi[i], g.B.hi, g.K, g.N, g.B.ld, BN, bk) || make_map(&P.b_lo[i], g.B.lo, g.K, g.N, g.B.ld, BN, bk))
             return -1;
         TcProblem &p = P.p[i];
         p.M = g.M;
@@ -399,12 +432,19 @@ int launch_gemm_tc(const GemmBatch &batch, int terms, cudaStream_t st)
     dev &= 63;
     if (!attr_set[dev])
     {
-        UMX_CUDA_OK(cudaFuncSetAttribute(gemm_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
+        UMX_CUDA_OK(cudaFuncSetAttribute(gemm_tc_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
+        UMX_CUDA_OK(cudaFuncSetAttribute(gemm_tc_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
+        UMX_CUDA_OK(cudaFuncSetAttribute(gemm_tc_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
         UMX_CUDA_OK(cudaDeviceGetAttribute(&sm_count[dev], cudaDevAttrMultiProcessorCount, dev));
         attr_set[dev] = true;
     }
     const int grid = std::min(tiles, sm_count[dev]);
-    gemm_tc_kernel<<<grid, kThreads, kSmemBytes, st>>>(P);
+    if (terms == 1)
+        gemm_tc_kernel<1><<<grid, kThreads, kSmemBytes, st>>>(P);
+    else if (terms == 2)
+        gemm_tc_kernel<2><<<grid, kThreads, kSmemBytes, st>>>(P);
+    else
+        gemm_tc_kernel<3><<<grid, kThreads, kSmemBytes, st>>>(P);
     UMX_CUDA_OK(cudaGetLastError());
     return 0;
 }
