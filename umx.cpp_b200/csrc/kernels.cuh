@@ -32,7 +32,7 @@ struct FinalizeTrack
     long i_begin, i_end; // output sample range to finalise
 };
 
-constexpr int kIstftFramesPerCta = 16;
+constexpr int kIstftFramesPerCta = 32; // + 3 halo frames recomputed per CTA
 
 int init_fft_tables(int device);
 int launch_stft(const StftTrack *d_tracks, int n_tracks, int n_buf, float2 *spec, __half *xh, __half *xl,

@@ -163,7 +163,7 @@ __device__ __forceinline__ float wss_at(int f, int n, int F, const float *win)
         const int fp = fb - j;
         if (fp >= 0 && fp < F)
         {
-            const float w = win[nl + 1024 * j];
+            const float w = __ldg(&win[nl + 1024 * j]);
             acc += w * w;
         }
     }
@@ -177,14 +177,14 @@ __device__ __forceinline__ float tri_weight(int k, int n_buf)
     return (float)tri / (float)(n_buf / 2);
 }
 
-__global__ void __launch_bounds__(256) istft_kernel(const float2 *__restrict__ stems, long stem_stride, int F,
+__global__ void __launch_bounds__(256, 3) istft_kernel(const float2 *__restrict__ stems, long stem_stride, int F,
                                                     int frames_per_cta, const IstftTrack *__restrict__ tracks,
                                                     int n_buf)
 {
     extern __shared__ float2 sm[];
     float2 *s = sm;                      // FFT workspace
     float2 *ring = sm + kFftSmemFloat2;  // overlap-add accumulators (L,R), 4096 positions
-    __shared__ float s_win[4096];
+    const float *s_win = g_win;          // 16 KB table, served by L1 (keeping it out of SMEM allows 3 CTAs per SM)
 
     const int t = threadIdx.x;
     const int stem = blockIdx.y;
@@ -195,10 +195,7 @@ __global__ void __launch_bounds__(256) istft_kernel(const float2 *__restrict__ s
     const bool last_cta = (f1 == F);
 
     for (int i = t; i < 4096; i += 256)
-    {
-        s_win[i] = g_win[i];
         ring[i] = make_float2(0.f, 0.f);
-    }
     __syncthreads();
 
     const float2 *base = stems + (long)stem * stem_stride;
@@ -244,10 +241,11 @@ __global__ void __launch_bounds__(256) istft_kernel(const float2 *__restrict__ s
         for (int k = 0; k < 16; ++k)
         {
             const int n = t + 256 * k;
-            const float w = s_win[n];
+            const float w = __ldg(&s_win[n]);
             const float den = wss_at(f, n, F, s_win) + 1e-8f;
-            const float cL = r[k].x * w * 1.0f / (float)kNfft / den;
-            const float cR = r[k].y * w * 1.0f / (float)kNfft / den;
+            const float sc = w * (1.0f / (float)kNfft) / den; // one division for both channels
+            const float cL = r[k].x * sc;
+            const float cR = r[k].y * sc;
             const int idx = (kHop * f + n) & 4095;
             if (n >= 3072)
                 ring[idx] = make_float2(cL, cR);

@@ -25,19 +25,44 @@ __device__ __forceinline__ float wiener_max_abs(const float *maxabs, int trk)
     return fmaxf(1.0f, maxabs[trk] / kWienerScale); // wiener.cpp:36-52
 }
 
-// y_jc / max_abs for one channel
-__device__ __forceinline__ float2 initial_estimate(float m, float2 X, float ma, int is_mag)
+// y_jc / max_abs for one channel.  inv_ma = 1 / max_abs: the reference's own build uses -freciprocal-math, and an
+// IEEE division per element (with its divergent slow path) made these kernels issue-bound instead of HBM-bound.
+__device__ __forceinline__ float2 initial_estimate(float m, float2 X, float inv_ma, int is_mag)
 {
-    float2 y;
     if (is_mag)
     { // polar(mag, arg X): X == 0 has phase 0
-        const float ax = sqrtf(X.x * X.x + X.y * X.y);
-        y = ax > 0.f ? make_float2(m * (X.x / ax), m * (X.y / ax)) : make_float2(m, 0.f);
+        const float a2 = X.x * X.x + X.y * X.y;
+        if (a2 > 0.f)
+        {
+            const float sc = m * rsqrtf(a2) * inv_ma;
+            return make_float2(sc * X.x, sc * X.y);
+        }
+        return make_float2(m * inv_ma, 0.f);
     }
-    else
-        y = make_float2(m * X.x, m * X.y);
-    return make_float2(y.x / ma, y.y / ma);
+    const float sc = m * inv_ma;
+    return make_float2(sc * X.x, sc * X.y);
 }
+
+// one frame of inputs for one bin: mix (L, R) and the 4 sources' (L, R) masks / magnitudes
+struct WienerIn
+{
+    float2 XL, XR;
+    float mL[4], mR[4];
+};
+__device__ __forceinline__ void wiener_load(const WienerArgs &a, long row, int b, WienerIn &w)
+{
+    w.XL = __ldg(&a.spec[(row * 2 + 0) * kBins + b]);
+    w.XR = __ldg(&a.spec[(row * 2 + 1) * kBins + b]);
+#pragma unroll
+    for (int j = 0; j < 4; ++j)
+    {
+        const float *mk = a.mask + (long)j * a.mask_target_stride + row * a.mask_ld;
+        w.mL[j] = __ldg(mk + b);
+        w.mR[j] = __ldg(mk + kBins + b);
+    }
+}
+
+constexpr int kWienerUnroll = 4; // frames whose loads are in flight together (the kernels are latency-bound otherwise)
 
 __global__ void __launch_bounds__(256) wiener_reduce_kernel(const WienerArgs a)
 {
@@ -47,28 +72,34 @@ __global__ void __launch_bounds__(256) wiener_reduce_kernel(const WienerArgs a)
         return;
     const int fc = (a.F + kWienerChunks - 1) / kWienerChunks;
     const int f_begin = chunk * fc, f_end = min(a.F, f_begin + fc);
-    const float ma = wiener_max_abs(a.maxabs, trk);
+    const float ma = 1.0f / wiener_max_abs(a.maxabs, trk); // reciprocal: see initial_estimate
     float acc[kWienerQ];
 #pragma unroll
     for (int i = 0; i < kWienerQ; ++i)
         acc[i] = 0.f;
-    for (int f = f_begin; f < f_end; ++f)
+    for (int f0 = f_begin; f0 < f_end; f0 += kWienerUnroll)
     {
-        const long row = (long)trk * a.F + f;
-        const float2 XL = a.spec[(row * 2 + 0) * kBins + b];
-        const float2 XR = a.spec[(row * 2 + 1) * kBins + b];
+        WienerIn in[kWienerUnroll];
 #pragma unroll
-        for (int j = 0; j < 4; ++j)
+        for (int u = 0; u < kWienerUnroll; ++u)
+            wiener_load(a, (long)trk * a.F + min(f0 + u, f_end - 1), b, in[u]);
+#pragma unroll
+        for (int u = 0; u < kWienerUnroll; ++u)
         {
-            const float *mk = a.mask + (long)j * a.mask_target_stride + row * a.mask_ld;
-            const float2 yL = initial_estimate(mk[b], XL, ma, a.mask_is_mag);
-            const float2 yR = initial_estimate(mk[kBins + b], XR, ma, a.mask_is_mag);
-            const float sL = yL.x + yL.y, sR = yR.x + yR.y;
-            acc[5 * j + 0] += yL.x * yL.x + yL.y * yL.y;
-            acc[5 * j + 1] += yR.x * yR.x + yR.y * yR.y;
-            acc[5 * j + 2] += yL.x * yR.x + yL.y * yR.y; // yL * conj(yR)
-            acc[5 * j + 3] += yL.y * yR.x - yL.x * yR.y;
-            acc[5 * j + 4] += (sL * sL + sR * sR) / 2.0f;
+            if (f0 + u >= f_end)
+                break;
+#pragma unroll
+            for (int j = 0; j < 4; ++j)
+            {
+                const float2 yL = initial_estimate(in[u].mL[j], in[u].XL, ma, a.mask_is_mag);
+                const float2 yR = initial_estimate(in[u].mR[j], in[u].XR, ma, a.mask_is_mag);
+                const float sL = yL.x + yL.y, sR = yR.x + yR.y;
+                acc[5 * j + 0] += yL.x * yL.x + yL.y * yL.y;
+                acc[5 * j + 1] += yR.x * yR.x + yR.y * yR.y;
+                acc[5 * j + 2] += yL.x * yR.x + yL.y * yR.y; // yL * conj(yR)
+                acc[5 * j + 3] += yL.y * yR.x - yL.x * yR.y;
+                acc[5 * j + 4] += (sL * sL + sR * sR) * 0.5f;
+            }
         }
     }
     float *p = a.partials + ((long)trk * kWienerChunks + chunk) * kWienerQ * kBins + b;
@@ -107,6 +138,7 @@ __global__ void __launch_bounds__(256) wiener_apply_kernel(const WienerArgs a)
         return;
     const int f_begin = blockIdx.y * kWienerApplyFrames, f_end = min(a.F, f_begin + kWienerApplyFrames);
     const float ma = wiener_max_abs(a.maxabs, trk);
+    const float inv_ma = 1.0f / ma;
     const float reg = sqrtf(kWienerEps); // wiener.cpp:155-163
     float R[16];
     {
@@ -115,23 +147,31 @@ __global__ void __launch_bounds__(256) wiener_apply_kernel(const WienerArgs a)
         for (int i = 0; i < 16; ++i)
             R[i] = s[(long)i * kBins];
     }
-    for (int f = f_begin; f < f_end; ++f)
+    for (int f0 = f_begin; f0 < f_end; f0 += 2)
     {
+      WienerIn in[2];
+#pragma unroll
+      for (int u = 0; u < 2; ++u)
+          wiener_load(a, (long)trk * a.F + min(f0 + u, f_end - 1), b, in[u]);
+#pragma unroll
+      for (int u = 0; u < 2; ++u)
+      {
+        const int f = f0 + u;
+        if (f >= f_end)
+            break;
         const long row = (long)trk * a.F + f;
-        const float2 XL = a.spec[(row * 2 + 0) * kBins + b];
-        const float2 XR = a.spec[(row * 2 + 1) * kBins + b];
-        const float2 x0 = make_float2(XL.x / ma, XL.y / ma); // wiener.cpp:118-129
-        const float2 x1 = make_float2(XR.x / ma, XR.y / ma);
+        const float2 XL = in[u].XL, XR = in[u].XR;
+        const float2 x0 = make_float2(XL.x * inv_ma, XL.y * inv_ma); // wiener.cpp:118-129
+        const float2 x1 = make_float2(XR.x * inv_ma, XR.y * inv_ma);
         float v[4];
         float c00 = 0.f, c11 = 0.f, c01r = 0.f, c01i = 0.f;
 #pragma unroll
         for (int j = 0; j < 4; ++j)
         {
-            const float *mk = a.mask + (long)j * a.mask_target_stride + row * a.mask_ld;
-            const float2 yL = initial_estimate(mk[b], XL, ma, a.mask_is_mag);
-            const float2 yR = initial_estimate(mk[kBins + b], XR, ma, a.mask_is_mag);
+            const float2 yL = initial_estimate(in[u].mL[j], XL, inv_ma, a.mask_is_mag);
+            const float2 yR = initial_estimate(in[u].mR[j], XR, inv_ma, a.mask_is_mag);
             const float sL = yL.x + yL.y, sR = yR.x + yR.y;
-            v[j] = (sL * sL + sR * sR) / 2.0f;
+            v[j] = (sL * sL + sR * sR) * 0.5f;
             c00 += reg + v[j] * R[4 * j + 0];
             c11 += reg + v[j] * R[4 * j + 1];
             c01r += v[j] * R[4 * j + 2];
@@ -139,7 +179,7 @@ __global__ void __launch_bounds__(256) wiener_apply_kernel(const WienerArgs a)
         }
         // inverse of the Hermitian 2x2 [[c00, c01],[conj c01, c11]] (invert4D, wiener.cpp:54-84)
         const float det = c00 * c11 - (c01r * c01r + c01i * c01i);
-        const float inv_det = det / (det * det); // conj(det)/norm(det), det real
+        const float inv_det = 1.0f / det; // conj(det)/norm(det) with det real (one division per bin-frame)
         const float i00 = inv_det * c11, i11 = inv_det * c00;
         const float i01r = -inv_det * c01r, i01i = -inv_det * c01i; // inv01 ; inv10 = conj(inv01)
 #pragma unroll
@@ -173,6 +213,7 @@ __global__ void __launch_bounds__(256) wiener_apply_kernel(const WienerArgs a)
             a.mix_out[(row * 2 + 0) * kBins + b] = x0;
             a.mix_out[(row * 2 + 1) * kBins + b] = x1;
         }
+      }
     }
 }
 
