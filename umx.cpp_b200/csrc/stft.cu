@@ -21,6 +21,7 @@ namespace umx
 
 __device__ float2 g_tw[4096];  // exp(-2*pi*i*j/4096)
 __device__ float g_win[4096];  // periodic Hann, src/dsp.hpp:61-77
+__device__ float g_istft_scale[4096]; // win[n] / 4096 / (wss + 1e-8) of a frame fully inside the signal (dsp.cpp:247-256)
 
 // ------------------------------------------------------------------------------------------------
 // tables (once per device)
@@ -50,6 +51,18 @@ int init_fft_tables(int device)
     }
     UMX_CUDA_OK(cudaMemcpyToSymbol(g_tw, tw.data(), sizeof(float2) * 4096));
     UMX_CUDA_OK(cudaMemcpyToSymbol(g_win, win.data(), sizeof(float) * 4096));
+    // interior frames: every output position is covered by 4 frames, added in increasing frame order, i.e.
+    // window offsets nl + 3072, + 2048, + 1024, + 0 (init_const_normalized_window, src/dsp.hpp:79-102)
+    std::vector<float> scale(4096);
+    for (int n = 0; n < 4096; ++n)
+    {
+        const int nl = n & 1023;
+        float wss = 0.f;
+        for (int j = 3; j >= 0; --j)
+            wss += win[nl + 1024 * j] * win[nl + 1024 * j];
+        scale[n] = win[n] * (1.0f / (float)kNfft) / (wss + 1e-8f);
+    }
+    UMX_CUDA_OK(cudaMemcpyToSymbol(g_istft_scale, scale.data(), sizeof(float) * 4096));
     done[device] = true;
     return 0;
 }
@@ -181,10 +194,11 @@ __global__ void __launch_bounds__(256, 3) istft_kernel(const float2 *__restrict_
                                                     int frames_per_cta, const IstftTrack *__restrict__ tracks,
                                                     int n_buf)
 {
+    // 66 KB of SMEM and <= 85 registers: 3 CTAs per SM.  (A cp.async-staged variant that prefetched the next
+    // frame at 2 CTAs per SM measured slower: the kernel is bound by FFT instruction issue, not by load latency.)
     extern __shared__ float2 sm[];
-    float2 *s = sm;                      // FFT workspace
-    float2 *ring = sm + kFftSmemFloat2;  // overlap-add accumulators (L,R), 4096 positions
-    const float *s_win = g_win;          // 16 KB table, served by L1 (keeping it out of SMEM allows 3 CTAs per SM)
+    float2 *s = sm;                     // FFT workspace
+    float2 *ring = sm + kFftSmemFloat2; // overlap-add accumulators (L,R), 4096 positions
 
     const int t = threadIdx.x;
     const int stem = blockIdx.y;
@@ -193,42 +207,36 @@ __global__ void __launch_bounds__(256, 3) istft_kernel(const float2 *__restrict_
     const int f0 = blockIdx.x * frames_per_cta;
     const int f1 = min(F, f0 + frames_per_cta);
     const bool last_cta = (f1 == F);
+    const float2 *base = stems + (long)stem * stem_stride;
+    const int f_first = max(f0 - 3, 0);
 
     for (int i = t; i < 4096; i += 256)
         ring[i] = make_float2(0.f, 0.f);
-    __syncthreads();
 
-    const float2 *base = stems + (long)stem * stem_stride;
     float2 r[16];
-    for (int f = max(f0 - 3, 0); f < f1; ++f)
+    for (int f = f_first; f < f1; ++f)
     {
-        const long row = (long)trk * F + f;
-        const float2 *yL = base + (row * 2 + 0) * kBins;
-        const float2 *yR = base + (row * 2 + 1) * kBins;
+        const float2 *yL = base + ((long)trk * F + f) * 2 * kBins;
+        const float2 *yR = yL + kBins;
 #pragma unroll
         for (int a = 0; a < 16; ++a)
         {
             const int k = 256 * a + t;
-            float2 L, R;
-            if (k <= 2048)
-            {
-                L = __ldg(&yL[k]);
-                R = __ldg(&yR[k]);
-                if (k == 0 || k == 2048)
-                { // the half-spectrum inverse ignores the imaginary part of DC and Nyquist
-                    L.y = 0.f;
-                    R.y = 0.f;
-                }
-            }
-            else
-            {
-                L = __ldg(&yL[4096 - k]);
-                R = __ldg(&yR[4096 - k]);
+            const int kk = k <= 2048 ? k : 4096 - k;
+            float2 L = __ldg(&yL[kk]), R = __ldg(&yR[kk]);
+            if (k > 2048)
+            { // Hermitian extension
                 L.y = -L.y;
                 R.y = -R.y;
             }
+            else if (k == 0 || k == 2048)
+            { // the half-spectrum inverse ignores the imaginary part of DC and Nyquist
+                L.y = 0.f;
+                R.y = 0.f;
+            }
             r[a] = make_float2(L.x - R.y, L.y + R.x); // Z = YL + i*YR
         }
+        __syncthreads(); // the previous frame's emission (ring reads) and FFT workspace reads are finished
         fft_pass1<true>(t, r, s, g_tw);
         __syncthreads();
         fft_pass2_load(t, r, s);
@@ -237,13 +245,16 @@ __global__ void __launch_bounds__(256, 3) istft_kernel(const float2 *__restrict_
         __syncthreads();
         fft_pass3<true>(t, r, s);
         // r[k] = (yL, yR)[n], n = t + 256k ; window, 1/4096, 1/(wss+1e-8), overlap-add
+        const bool interior = (f >= 3 && f + 3 < F); // every sample of the frame is covered by 4 frames
 #pragma unroll
         for (int k = 0; k < 16; ++k)
         {
             const int n = t + 256 * k;
-            const float w = __ldg(&s_win[n]);
-            const float den = wss_at(f, n, F, s_win) + 1e-8f;
-            const float sc = w * (1.0f / (float)kNfft) / den; // one division for both channels
+            float sc;
+            if (interior)
+                sc = __ldg(&g_istft_scale[n]);
+            else
+                sc = __ldg(&g_win[n]) * (1.0f / (float)kNfft) / (wss_at(f, n, F, g_win) + 1e-8f);
             const float cL = r[k].x * sc;
             const float cR = r[k].y * sc;
             const int idx = (kHop * f + n) & 4095;
@@ -282,7 +293,7 @@ __global__ void __launch_bounds__(256, 3) istft_kernel(const float2 *__restrict_
                 }
             }
         }
-        __syncthreads();
+        // (the __syncthreads at the top of the next iteration orders this emission before the next overlap-add)
     }
 }
 
