@@ -164,14 +164,17 @@ def umx_inference(model: Model, state: LstmState, audio: np.ndarray, n_buf: int)
     return np.ascontiguousarray(out.transpose(0, 2, 1))
 
 
+MAIN_PATH = os.path.join(HERE, "_ref", "umx.cpp.main.ref")
+
+
 def main(model_gz: str, wav: str, out_dir: str) -> int:
-    """The reference CLI (umx.cpp:26) run in-process. Only safe for tracks >= 30 s."""
-    args = [b"umx.cpp.main", os.path.abspath(model_gz).encode(), os.path.abspath(wav).encode(), os.path.abspath(out_dir).encode()]
-    arr = (C.c_char_p * len(args))(*args)
-    cwd = os.getcwd()
-    with tempfile.TemporaryDirectory() as td:
-        os.chdir(td)
-        try:
-            return lib().ref_main(len(args), arr)
-        finally:
-            os.chdir(cwd)
+    """The reference CLI (umx.cpp:26) as a separate process.  Only for tracks >= 30 s, and even then
+    its istft writes past the end of the chunk's waveform matrix whenever a chunk is shorter than 60 s
+    (src/dsp.cpp:203-205 under -DNDEBUG), so the process may die in free() AFTER the four WAVs are written:
+    callers check the files, not the exit status."""
+    import subprocess
+
+    with tempfile.TemporaryDirectory() as td:  # the loader drops ./temp.decompressed
+        r = subprocess.run([MAIN_PATH, os.path.abspath(model_gz), os.path.abspath(wav), os.path.abspath(out_dir)],
+                           cwd=td, stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
+    return r.returncode

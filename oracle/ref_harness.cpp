@@ -136,11 +136,15 @@ void ref_istft(const float *spec, int n_buf, int n_wave, float *wave_out)
 {
     quiet_scope qs(g_quiet);
     stft_buffers buf(n_buf);
-    buf.waveform = Eigen::MatrixXf::Zero(2, n_wave);
+    // keep the waveform at its full n_buf columns: a shorter one is overrun by istft (see ref_umx_inference)
     std::memcpy((void *)buf.spec.data(), spec,
                 sizeof(std::complex<float>) * buf.spec.size());
     istft(buf);
-    std::memcpy(wave_out, buf.waveform.data(), sizeof(float) * 2 * n_wave);
+    for (int i = 0; i < n_wave; ++i)
+    {
+        wave_out[2 * i] = buf.waveform(0, i);
+        wave_out[2 * i + 1] = buf.waveform(1, i);
+    }
 }
 
 // ---- lstm (src/lstm.cpp:41,101) -------------------------------------------
@@ -211,10 +215,19 @@ void ref_umx_inference(void *model, void *state, const float *audio, int n,
     auto *m = static_cast<umx_model *>(model);
     auto *s = static_cast<lstm_set *>(state);
     stft_buffers buf(n_buf);
-    Eigen::MatrixXf a = Eigen::Map<const Eigen::MatrixXf>(audio, 2, n);
+    // A chunk shorter than the buffer makes the reference's istft assign an n_buf-long row into an n-long one
+    // (src/dsp.cpp:203-205): with -DNDEBUG that runs past the end of the waveform matrix and corrupts the heap
+    // of whoever hosts this library.  The zero-extended chunk gives bit-identical results for the first n
+    // samples (the buffers are zero past the chunk anyway) without the overflow.
+    Eigen::MatrixXf a = Eigen::MatrixXf::Zero(2, n_buf);
+    a.leftCols(n) = Eigen::Map<const Eigen::MatrixXf>(audio, 2, n);
     auto w = umx_inference(*m, a, buf, s->d);
     for (int j = 0; j < 4; ++j)
-        std::memcpy(out + (size_t)j * 2 * n, w[j].data(), sizeof(float) * 2 * n);
+        for (int i = 0; i < n; ++i)
+        {
+            out[(size_t)j * 2 * n + 2 * i] = w[j](0, i);
+            out[(size_t)j * 2 * n + 2 * i + 1] = w[j](1, i);
+        }
 }
 
 // ---- the reference CLI itself (umx.cpp:26) --------------------------------
