@@ -119,6 +119,14 @@ int umx_cuda_target_mags(umx_cuda_session *s, const float *spec, float *mags);
 #define UMX_WIENER_NOALLOC_MAX_TRACKS 2
 int umx_cuda_wiener_noalloc(const float *d_mix, const float *d_mags, int F, int n_tracks, float *d_out, void *stream);
 
+/* ---- target-parallel mode over NCCL (no counterpart in the single-process reference; BASELINE config 5) ------ */
+/* The 4 stem networks are independent until wiener_filter (src/inference.cpp:70-186): rank j of a 1/2/4-GPU group
+ * runs targets [j*4/world, (j+1)*4/world); one ncclAllGather of the fc3 masks per segment precedes the Wiener
+ * stage, which every rank then runs for its own stems.  After umx_cuda_demix* each rank's output buffers hold
+ * ITS stems only.  One process per GPU; rank 0 creates the 128-byte id and hands it to the others. */
+int umx_cuda_nccl_unique_id(void *id128);
+int umx_cuda_session_init_target_parallel(umx_cuda_session *s, const void *id128, int rank, int world);
+
 /* ---- measurement ------------------------------------------------------------------------------ */
 /* Per-stage device time of the most recent demix / infer_segment call, from CUDA events recorded on
  * the session's own stream.  Stage names: "stft", "gemm", "lstm", "wiener", "istft", "finalize",

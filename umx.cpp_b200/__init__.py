@@ -36,7 +36,8 @@ EXPORTS = [
     "umx_cuda_demix_device", "umx_cuda_segment_plan", "umx_cuda_stft", "umx_cuda_istft", "umx_cuda_lstm_forward",
     "umx_cuda_wiener", "umx_cuda_target_mags", "umx_cuda_session_set_profiling", "umx_cuda_session_stage_ms",
     "umx_cuda_session_launches", "umx_cuda_session_set_option", "umx_cuda_session_set_stream",
-    "umx_cuda_wiener_noalloc", "umx_cuda_lstm_max_active_clusters",
+    "umx_cuda_wiener_noalloc", "umx_cuda_lstm_max_active_clusters", "umx_cuda_nccl_unique_id",
+    "umx_cuda_session_init_target_parallel",
 ]
 
 _lib = None
@@ -87,6 +88,8 @@ def lib():
     l.umx_cuda_session_set_option.argtypes = [vp, C.c_char_p, ip]
     l.umx_cuda_session_set_stream.argtypes = [vp, vp]
     l.umx_cuda_wiener_noalloc.argtypes = [vp, vp, ip, ip, vp, vp]
+    l.umx_cuda_nccl_unique_id.argtypes = [vp]
+    l.umx_cuda_session_init_target_parallel.argtypes = [vp, vp, ip, ip]
     _lib = l
     return l
 
@@ -180,6 +183,13 @@ class Session:
         """Run on the caller's CUDA stream (e.g. torch.cuda.current_stream().cuda_stream); None = own stream."""
         _check(self._lib.umx_cuda_session_set_stream(self._h, cuda_stream), "umx_cuda_session_set_stream")
 
+    def init_target_parallel(self, unique_id: bytes, rank: int, world: int):
+        """Target-parallel mode: this rank runs targets [rank*4/world, (rank+1)*4/world); masks are all-gathered
+        over NCCL before the Wiener stage.  `unique_id`: the 128 bytes of nccl_unique_id() made on rank 0."""
+        buf = (C.c_char * 128).from_buffer_copy(unique_id) if unique_id else None
+        _check(self._lib.umx_cuda_session_init_target_parallel(self._h, buf, rank, world),
+               "umx_cuda_session_init_target_parallel")
+
     def set_profiling(self, on: bool):
         _check(self._lib.umx_cuda_session_set_profiling(self._h, int(on)), "umx_cuda_session_set_profiling")
 
@@ -256,6 +266,12 @@ class Session:
             self.close()
         except Exception:
             pass
+
+
+def nccl_unique_id() -> bytes:
+    buf = (C.c_char * 128)()
+    _check(lib().umx_cuda_nccl_unique_id(buf), "umx_cuda_nccl_unique_id")
+    return bytes(buf)
 
 
 def segment_plan(n_samples: int, shift_offset: int = DEFAULT_SHIFT_OFFSET, n_buf: int = SEGMENT_SAMPLES):

@@ -262,6 +262,18 @@ int umx_cuda_session_set_stream(umx_cuda_session *s, void *stream)
 
 int umx_cuda_lstm_max_active_clusters(void) { return lstm_cluster_max_active(); }
 
+int umx_cuda_nccl_unique_id(void *id128)
+{
+    UMX_CHECK(id128, "umx_cuda_nccl_unique_id: null argument");
+    return tp_unique_id(id128);
+}
+
+int umx_cuda_session_init_target_parallel(umx_cuda_session *s, const void *id128, int rank, int world)
+{
+    UMX_CHECK(s && (id128 || world == 1), "umx_cuda_session_init_target_parallel: null argument");
+    return tp_init(s->s, id128, rank, world);
+}
+
 long umx_cuda_session_launches(umx_cuda_session *s) { return s ? s->s->launches : -1; }
 
 int umx_cuda_session_set_option(umx_cuda_session *s, const char *name, int value)
@@ -393,6 +405,8 @@ int umx_cuda_wiener(float *mix, const float *mags, int F, float *out)
     w.mix_out = d_mixo.as<float2>();
     w.F = F;
     w.n_tracks = 1;
+    w.stem_begin = 0;
+    w.stem_count = 4;
     if (int rc = launch_wiener(w, 0))
         return rc;
     for (int j = 0; j < 4; ++j)

@@ -38,9 +38,9 @@ int init_fft_tables(int device);
 int launch_stft(const StftTrack *d_tracks, int n_tracks, int n_buf, float2 *spec, __half *xh, __half *xl,
                 float *maxabs, cudaStream_t st);
 int launch_istft(const float2 *stems, long stem_stride, int n_stems, const IstftTrack *d_tracks, int n_tracks,
-                 int n_buf, cudaStream_t st);
+                 int n_buf, cudaStream_t st, int stem_begin = 0);
 int launch_finalize(const FinalizeTrack *d_tracks, int n_tracks, long max_range, int shift, int n_buf, int stride, int n_stems,
-                    cudaStream_t st);
+                    cudaStream_t st, int stem_begin = 0);
 int launch_to_ref_layout_c64(const float2 *in, float2 *out, int F, cudaStream_t st);
 int launch_from_ref_layout_c64(const float2 *in, float2 *out, int F, cudaStream_t st);
 int launch_to_ref_layout_f32(const float *in, float *out, int F, cudaStream_t st);
@@ -139,6 +139,7 @@ struct WienerArgs
     float2 *mix_out;      // optional: mix / max_abs (the reference mutates its argument)
     int F;
     int n_tracks;
+    int stem_begin, stem_count; // stems whose output is written (all 4 unless target-parallel)
 };
 constexpr int kWienerChunks = 19;
 int launch_wiener(const WienerArgs &a, cudaStream_t st);

@@ -167,6 +167,7 @@ void session_destroy(Session *s)
     if (s->st)
         cudaStreamSynchronize(s->st);
     session_begin_profile(s);
+    tp_destroy(s);
     for (void *p : s->allocs)
         cudaFree(p);
     for (auto *p : s->acc_pool)
@@ -304,31 +305,32 @@ int session_network(Session *s, int n_tracks)
         GemmBatch b{};
         b.count = 1;
         GemmProblem &p = b.p[0];
+        const size_t t0 = (size_t)s->tp_t0; // target-parallel ranks only compute their own targets' columns
         p.A = {s->xh, s->xl, kFc1InPad, 0};
-        p.B = {m->fc1_hi, m->fc1_lo, kFc1InPad, 0};
+        p.B = {m->fc1_hi + t0 * H * kFc1InPad, m->fc1_lo + t0 * H * kFc1InPad, kFc1InPad, 0};
         p.M = (int)M;
-        p.N = 4 * H;
+        p.N = s->tp_nt * H;
         p.K = kFc1InPad;
         p.act = kActTanh;
-        p.alpha = m->fc1_alpha;
-        p.beta = m->fc1_beta;
-        p.out_hi = s->act_h;
-        p.out_lo = s->act_l;
+        p.alpha = m->fc1_alpha + t0 * H;
+        p.beta = m->fc1_beta + t0 * H;
+        p.out_hi = s->act_h + t0 * Mc * 2 * H;
+        p.out_lo = s->act_l + t0 * Mc * 2 * H;
         p.ldo = 2 * H;
         p.n_group = H;
         p.group_stride = Mc * 2 * H;
         if (int rc = run_gemm(s, b))
             return rc;
     }
-    if (int rc = session_lstm(s, n_tracks, 0, kTargets, false))
+    if (int rc = session_lstm(s, n_tracks, s->tp_t0, s->tp_nt, false))
         return rc;
     StageScope sc(s, "gemm");
     { // skip concat + fc2 + BN2 + ReLU (inference.cpp:118-140)
         GemmBatch b{};
-        b.count = kTargets;
-        for (int t = 0; t < kTargets; ++t)
+        b.count = s->tp_nt;
+        for (int t = s->tp_t0; t < s->tp_t0 + s->tp_nt; ++t)
         {
-            GemmProblem &p = b.p[t];
+            GemmProblem &p = b.p[t - s->tp_t0];
             p.A = {s->act_h + (size_t)t * Mc * 2 * H, s->act_l + (size_t)t * Mc * 2 * H, 2 * H, 0};
             p.B = {m->t[t].fc2_hi, m->t[t].fc2_lo, 2 * H, 0};
             p.M = (int)M;
@@ -348,10 +350,10 @@ int session_network(Session *s, int n_tracks)
     }
     { // fc3 + BN3 + output affine + ReLU -> mask (inference.cpp:143-166)
         GemmBatch b{};
-        b.count = kTargets;
-        for (int t = 0; t < kTargets; ++t)
+        b.count = s->tp_nt;
+        for (int t = s->tp_t0; t < s->tp_t0 + s->tp_nt; ++t)
         {
-            GemmProblem &p = b.p[t];
+            GemmProblem &p = b.p[t - s->tp_t0];
             p.A = {s->fc2_h + (size_t)t * Mc * H, s->fc2_l + (size_t)t * Mc * H, H, 0};
             p.B = {m->t[t].fc3_hi, m->t[t].fc3_lo, H, 0};
             p.M = (int)M;
@@ -384,6 +386,12 @@ int session_run_segment(Session *s, int seg, int n_tracks)
     }
     if (int rc = session_network(s, n_tracks))
         return rc;
+    if (s->tp_world > 1)
+    { // the one exchange step of the target-parallel mode: every rank needs all four sources' masks
+        StageScope sc(s, "allgather");
+        if (int rc = tp_allgather_masks(s))
+            return rc;
+    }
     {
         StageScope sc(s, "wiener");
         WienerArgs w{};
@@ -400,6 +408,8 @@ int session_run_segment(Session *s, int seg, int n_tracks)
         w.mix_out = nullptr;
         w.F = s->F;
         w.n_tracks = n_tracks;
+        w.stem_begin = s->tp_t0;
+        w.stem_count = s->tp_nt;
         s->launches += 3;
         if (int rc = launch_wiener(w, s->st))
             return rc;
@@ -407,7 +417,7 @@ int session_run_segment(Session *s, int seg, int n_tracks)
     {
         StageScope sc(s, "istft");
         s->launches++;
-        if (int rc = launch_istft(s->stems, s->Mcap * 2 * kBins, 4, dis, n_tracks, s->n_buf, s->st))
+        if (int rc = launch_istft(s->stems, s->Mcap * 2 * kBins, s->tp_nt, dis, n_tracks, s->n_buf, s->st, s->tp_t0))
             return rc;
     }
     return 0;
@@ -545,7 +555,7 @@ int session_demix_device(Session *s, const float *const *d_audio, const int64_t 
         {
             StageScope sc(s, "finalize");
             s->launches++;
-            if (int rc = launch_finalize(s->d_final + (size_t)sg * s->T, n_tracks, max_range[sg], shift_offset, s->n_buf, stride, 4, s->st))
+            if (int rc = launch_finalize(s->d_final + (size_t)sg * s->T, n_tracks, max_range[sg], shift_offset, s->n_buf, stride, s->tp_nt, s->st, s->tp_t0))
                 return rc;
         }
         if (host_out)
@@ -558,7 +568,7 @@ int session_demix_device(Session *s, const float *const *d_audio, const int64_t 
                 const FinalizeTrack &f = hf[(size_t)sg * s->T + i];
                 if (f.i_end <= f.i_begin)
                     continue;
-                for (int stem = 0; stem < 4; ++stem)
+                for (int stem = s->tp_t0; stem < s->tp_t0 + s->tp_nt; ++stem)
                 {
                     const size_t o = 2 * ((size_t)stem * n_samples[i] + f.i_begin);
                     UMX_CUDA_OK(cudaMemcpyAsync(host_out[i] + o, d_out[i] + o, sizeof(float2) * (size_t)(f.i_end - f.i_begin),

@@ -55,6 +55,10 @@ struct Session
     std::vector<long> acc_cap, in_cap, out_cap;
 
     std::vector<void *> allocs;
+    // target-parallel mode (BASELINE config 5): this rank runs targets [tp_t0, tp_t0 + tp_nt) and the masks are
+    // all-gathered over NCCL before the Wiener stage; tp_world == 1 means off
+    int tp_rank = 0, tp_world = 1, tp_t0 = 0, tp_nt = kTargets;
+    void *tp_comm = nullptr; // ncclComm_t
     // options
     int gemm_impl = 0, gemm_terms = 3, lstm_impl = 0;
     // measurement
@@ -82,6 +86,11 @@ int session_infer_segment(Session *s, const float *audio, int n, float *out);
 void session_begin_profile(Session *s);
 int session_end_profile(Session *s);
 int ensure_desc_capacity(Session *s, int segs);
+// tp.cu: NCCL is loaded with dlopen on first use, so the library has no link-time dependency on it
+int tp_unique_id(void *id128);
+int tp_init(Session *s, const void *id128, int rank, int world);
+int tp_allgather_masks(Session *s);
+void tp_destroy(Session *s);
 
 struct StageScope
 {

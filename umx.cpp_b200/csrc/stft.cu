@@ -192,7 +192,7 @@ __device__ __forceinline__ float tri_weight(int k, int n_buf)
 
 __global__ void __launch_bounds__(256, 3) istft_kernel(const float2 *__restrict__ stems, long stem_stride, int F,
                                                     int frames_per_cta, const IstftTrack *__restrict__ tracks,
-                                                    int n_buf)
+                                                    int n_buf, int stem_begin)
 {
     // 66 KB of SMEM and <= 85 registers: 3 CTAs per SM.  (A cp.async-staged variant that prefetched the next
     // frame at 2 CTAs per SM measured slower: the kernel is bound by FFT instruction issue, not by load latency.)
@@ -201,7 +201,7 @@ __global__ void __launch_bounds__(256, 3) istft_kernel(const float2 *__restrict_
     float2 *ring = sm + kFftSmemFloat2; // overlap-add accumulators (L,R), 4096 positions
 
     const int t = threadIdx.x;
-    const int stem = blockIdx.y;
+    const int stem = stem_begin + blockIdx.y;
     const int trk = blockIdx.z;
     const IstftTrack tk = tracks[trk];
     const int f0 = blockIdx.x * frames_per_cta;
@@ -301,7 +301,8 @@ __global__ void __launch_bounds__(256, 3) istft_kernel(const float2 *__restrict_
 // out = acc / sum_weight, trimmed to the original track (umx.cpp:251-273,136-147); output samples
 // [i_begin, i_end) of each track (a range is final as soon as the last segment touching it has been added)
 // ------------------------------------------------------------------------------------------------
-__global__ void finalize_kernel(const FinalizeTrack *__restrict__ tracks, int shift, int n_buf, int stride, int n_stems)
+__global__ void finalize_kernel(const FinalizeTrack *__restrict__ tracks, int shift, int n_buf, int stride, int n_stems,
+                                int stem_begin)
 {
     const FinalizeTrack tk = tracks[blockIdx.y];
     const long i = tk.i_begin + (long)blockIdx.x * blockDim.x + threadIdx.x;
@@ -321,7 +322,7 @@ __global__ void finalize_kernel(const FinalizeTrack *__restrict__ tracks, int sh
         if (k >= 0 && k < clen)
             sw += tri_weight((int)k, n_buf);
     }
-    for (int st = 0; st < n_stems; ++st)
+    for (int st = stem_begin; st < stem_begin + n_stems; ++st)
     {
         const float2 a = tk.acc[(long)st * tk.L + p];
         tk.out[(long)st * tk.n + i] = make_float2(a.x / sw, a.y / sw);
@@ -388,7 +389,7 @@ int launch_stft(const StftTrack *d_tracks, int n_tracks, int n_buf, float2 *spec
 }
 
 int launch_istft(const float2 *stems, long stem_stride, int n_stems, const IstftTrack *d_tracks, int n_tracks,
-                 int n_buf, cudaStream_t st)
+                 int n_buf, cudaStream_t st, int stem_begin)
 {
     const int F = n_buf / kHop + 1;
     const int G = kIstftFramesPerCta;
@@ -402,17 +403,17 @@ int launch_istft(const float2 *stems, long stem_stride, int n_stems, const Istft
         attr_set[dev & 63] = true;
     }
     dim3 grid(ceil_div(F, G), n_stems, n_tracks);
-    istft_kernel<<<grid, 256, smem, st>>>(stems, stem_stride, F, G, d_tracks, n_buf);
+    istft_kernel<<<grid, 256, smem, st>>>(stems, stem_stride, F, G, d_tracks, n_buf, stem_begin);
     UMX_CUDA_OK(cudaGetLastError());
     return 0;
 }
 
 int launch_finalize(const FinalizeTrack *d_tracks, int n_tracks, long max_range, int shift, int n_buf, int stride, int n_stems,
-                    cudaStream_t st)
+                    cudaStream_t st, int stem_begin)
 {
     if (max_range <= 0 || n_tracks <= 0)
         return 0;
-    finalize_kernel<<<dim3(ceil_div(max_range, 256), n_tracks), 256, 0, st>>>(d_tracks, shift, n_buf, stride, n_stems);
+    finalize_kernel<<<dim3(ceil_div(max_range, 256), n_tracks), 256, 0, st>>>(d_tracks, shift, n_buf, stride, n_stems, stem_begin);
     UMX_CUDA_OK(cudaGetLastError());
     return 0;
 }

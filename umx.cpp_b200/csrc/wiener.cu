@@ -184,6 +184,7 @@ __global__ void __launch_bounds__(256) wiener_apply_kernel(const WienerArgs a)
         const float i01r = -inv_det * c01r, i01i = -inv_det * c01i; // inv01 ; inv10 = conj(inv01)
 #pragma unroll
         for (int j = 0; j < 4; ++j)
+          if (j >= a.stem_begin && j < a.stem_begin + a.stem_count) // target-parallel ranks only write their own stems
         {
             const float r00 = R[4 * j + 0], r11 = R[4 * j + 1], r01r = R[4 * j + 2], r01i = R[4 * j + 3];
             // gain = v * R * inv ; R10 = conj(R01), inv10 = conj(inv01)
@@ -355,5 +356,7 @@ extern "C" int umx_cuda_wiener_noalloc(const float *d_mix, const float *d_mags, 
     w.mix_out = nullptr; // the caller's mix is left untouched
     w.F = F;
     w.n_tracks = n_tracks;
+    w.stem_begin = 0;
+    w.stem_count = 4;
     return launch_wiener(w, st);
 }
