@@ -290,6 +290,11 @@ int umx_cuda_session_set_option(umx_cuda_session *s, const char *name, int value
         UMX_CHECK(value == 0 || value == 1, "gemm_impl must be 0 (tcgen05) or 1 (SIMT validation)");
         s->s->gemm_impl = value;
     }
+    else if (n == "pipeline")
+    {
+        UMX_CHECK(value == 0 || value == 1, "pipeline must be 0 or 1");
+        s->s->pipeline = value;
+    }
     else if (n == "lstm_impl")
     {
         UMX_CHECK(value == 0 || value == 1, "lstm_impl must be 0 (cluster) or 1 (simple)");

@@ -89,7 +89,8 @@ __global__ void __launch_bounds__(256) gemm_simt_kernel(const GemmBatch batch)
                 continue;
             const float al = pb.alpha ? pb.alpha[n] : 1.f;
             const float be = pb.beta ? pb.beta[n] : 0.f;
-            const float v = apply_act(fmaf(acc[i][j], al, be), pb.act);
+            const float rv = pb.rowvec ? pb.rowvec[m] * pb.gamma[n] : 0.f;
+            const float v = apply_act(fmaf(acc[i][j], al, be + rv), pb.act);
             const long o = (long)(n / pb.n_group) * pb.group_stride + (long)m * pb.ldo + (n % pb.n_group);
             if (pb.out_f32)
                 pb.out_f32[o] = v;

@@ -51,6 +51,8 @@ struct TcProblem
     int act;
     const float *alpha;
     const float *beta;
+    const float *rowvec;
+    const float *gamma;
     float *out_f32;
     __half *out_hi;
     __half *out_lo;
@@ -236,6 +238,8 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_tc_kernel(const __grid_const
             const long gstride = P.p[pi].group_stride;
             const float *__restrict__ alpha = P.p[pi].alpha;
             const float *__restrict__ beta = P.p[pi].beta;
+            const float *__restrict__ rowvec = P.p[pi].rowvec;
+            const float *__restrict__ gamma = P.p[pi].gamma;
             float *__restrict__ of32 = P.p[pi].out_f32;
             __half *__restrict__ ohi = P.p[pi].out_hi;
             __half *__restrict__ olo = P.p[pi].out_lo;
@@ -266,13 +270,14 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_tc_kernel(const __grid_const
                                     __uint_as_float(r[4 * i + 3]));
                 __syncwarp();
                 const int n = nc0 + c4;
-                float al[4], be[4];
+                float al[4], be[4], ga[4];
 #pragma unroll
                 for (int e = 0; e < 4; ++e)
                 {
                     const bool ok = n + e < N;
                     al[e] = (alpha && ok) ? __ldg(alpha + n + e) : 1.f;
                     be[e] = (beta && ok) ? __ldg(beta + n + e) : 0.f;
+                    ga[e] = (rowvec && ok) ? __ldg(gamma + n + e) : 0.f;
                 }
                 const int grp = n / n_group;
                 const long obase = (long)grp * gstride + (n - grp * n_group);
@@ -284,9 +289,10 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_tc_kernel(const __grid_const
                     const int m = row0 + row;
                     const float4 t4 = *reinterpret_cast<const float4 *>(stage_buf + row * 36 + c4);
                     float v[4] = {t4.x, t4.y, t4.z, t4.w};
+                    const float rv = (rowvec && m < M) ? __ldg(rowvec + m) : 0.f;
 #pragma unroll
                     for (int e = 0; e < 4; ++e)
-                        v[e] = act_apply(fmaf(v[e], al[e], be[e]), act);
+                        v[e] = act_apply(fmaf(v[e], al[e], fmaf(rv, ga[e], be[e])), act);
                     if (m < M && n < N)
                     {
                         const long o = obase + (long)m * ldo;
@@ -400,10 +406,12 @@ int launch_gemm_tc(const GemmBatch &batch, int terms, cudaStream_t st)
         UMX_CHECK(g.M > 0 && g.N > 0 && g.K > 0, "gemm_tc: empty problem");
         UMX_CHECK(g.ldo % 4 == 0 && g.n_group % 4 == 0 && g.group_stride % 4 == 0,
                   "gemm_tc: output pitch, column group and group stride must be multiples of 4 (vector stores)");
-        UMX_CHECK(g.A.lo != nullptr && g.B.lo != nullptr, "gemm_tc: operands need hi and lo planes");
+        UMX_CHECK((terms < 2 || g.A.lo != nullptr) && (terms < 3 || g.B.lo != nullptr), "gemm_tc: the chosen terms need lo planes");
+        UMX_CHECK(g.rowvec == nullptr || g.gamma != nullptr, "gemm_tc: rowvec needs gamma");
         const int bk = terms == 1 ? 64 : 32;
-        if (make_map(&P.a_hi[i], g.A.hi, g.K, g.M, g.A.ld, BM, bk) || make_map(&P.a_lo[i], g.A.lo, g.K, g.M, g.A.ld, BM, bk) ||
-            make_map(&P.b_hi[i], g.B.hi, g.K, g.N, g.B.ld, BN, bk) || make_map(&P.b_lo[i], g.B.lo, g.K, g.N, g.B.ld, BN, bk))
+        if (make_map(&P.a_hi[i], g.A.hi, g.K, g.M, g.A.ld, BM, bk) || make_map(&P.b_hi[i], g.B.hi, g.K, g.N, g.B.ld, BN, bk) ||
+            (terms >= 2 && make_map(&P.a_lo[i], g.A.lo, g.K, g.M, g.A.ld, BM, bk)) ||
+            (terms >= 3 && make_map(&P.b_lo[i], g.B.lo, g.K, g.N, g.B.ld, BN, bk)))
             return -1;
         TcProblem &p = P.p[i];
         p.M = g.M;
@@ -412,6 +420,8 @@ int launch_gemm_tc(const GemmBatch &batch, int terms, cudaStream_t st)
         p.act = g.act;
         p.alpha = g.alpha;
         p.beta = g.beta;
+        p.rowvec = g.rowvec;
+        p.gamma = g.gamma;
         p.out_f32 = g.out_f32;
         p.out_hi = g.out_hi;
         p.out_lo = g.out_lo;

@@ -47,7 +47,7 @@ int launch_to_ref_layout_f32(const float *in, float *out, int F, cudaStream_t st
 int launch_from_ref_layout_f32(const float *in, float *out, int F, cudaStream_t st);
 
 // ---- gemm ----------------------------------------------------------------------------------------
-// C[m, n] = act(alpha[n] * sum_k A[m,k] * B[n,k] + beta[n]);  A, B are fp16 (hi, lo) plane pairs, K-major.
+// C[m, n] = act(alpha[n] * sum_k A[m,k] * B[n,k] + rowvec[m] * gamma[n] + beta[n]);  A, B are fp16 (hi, lo) plane pairs, K-major.
 enum GemmAct
 {
     kActNone = 0,
@@ -71,6 +71,10 @@ struct GemmProblem
     int act;
     const float *alpha; // per output column (may be null = 1)
     const float *beta;  // per output column (may be null = 0)
+    // optional rank-1 term rowvec[m] * gamma[n] (exact-integer weight operands: W = scale*q + offset gives
+    // x.W = scale * (x.q) + offset * sum_k x_k; alpha carries scale, gamma the offset, rowvec the row sums)
+    const float *rowvec;
+    const float *gamma;
     // output: column n goes to group g = n / n_group at  base + g*group_stride + m*ldo + n % n_group
     float *out_f32;  // fp32 output (or null)
     __half *out_hi;  // fp16 plane pair output (or null)
@@ -158,6 +162,10 @@ int launch_pack_whh(const uint8_t *q, int Hh, uint8_t *out, cudaStream_t st);
 int launch_colmajor_to_planes(const float *in, int F, int H, __half *hi, __half *lo, int ld, cudaStream_t st);
 int launch_rowmajor_to_colmajor(const float *in, int F, int H, int ld, float *out, cudaStream_t st);
 // mags[c][f][b] = mask[f][c*2049+b] * |spec[f][c][b]|  (src/inference.cpp:173-185), internal layouts
+// rowsum[r] = sum_k (hi + lo)[r][k] over K columns of `rows` rows with pitch ld (one warp per row)
+int launch_rowsum(const __half *hi, const __half *lo, long rows, int K, int ld, float *out, cudaStream_t st);
+// fp16 plane of the centred quantised integers q - 127 (exact for uint8)
+int launch_q_to_half(const uint8_t *q, long n, __half *out, cudaStream_t st);
 int launch_spec_to_x(const float2 *spec, long M, __half *xh, __half *xl, cudaStream_t st);
 int launch_mask_to_mag(const float *mask, int ld, const float2 *spec, float *mag, long M, cudaStream_t st);
 

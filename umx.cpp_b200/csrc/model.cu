@@ -242,6 +242,19 @@ int model_create(const void *bytes, size_t n, int device, Model **out)
                 dt.host[i] = std::fmaf((float)q, scale, offset);
             }
         }
+        if (name.rfind("lstm.weight_ih", 0) == 0)
+        { // keep the quantised input weights: the GEMM consumes the exact integers
+            uint8_t *q = nullptr;
+            if (dev_alloc(m, &q, nbytes))
+                return fail(-1);
+            if (cudaMemcpy(q, staging, nbytes, cudaMemcpyDeviceToDevice) != cudaSuccess)
+                return fail(-1);
+            whh_raw[target][name] = q;
+            const int layer = name[name.find("_l") + 2] - '0';
+            const int dir = name.find("_reverse") != std::string::npos ? 1 : 0;
+            m->t[target].wih_scale[layer][dir] = scale;
+            m->t[target].wih_offset[layer][dir] = offset;
+        }
         if (name.rfind("lstm.weight_hh", 0) == 0)
         { // keep the quantised recurrent weights
             uint8_t *q = nullptr;
@@ -354,17 +367,20 @@ static int build_operands(Model *m, std::map<std::string, uint8_t *> (&whh_raw)[
         // ---- LSTM: W_ih of both directions stacked (rows dir*2H + gate row), bias b_ih + b_hh
         for (int l = 0; l < 3; ++l)
         {
-            if (dev_alloc(m, &tw.wih_hi[l], (size_t)4 * H * H) || dev_alloc(m, &tw.wih_lo[l], (size_t)4 * H * H))
+            if (dev_alloc(m, &tw.wih_q[l], (size_t)4 * H * H))
                 return -1;
-            std::vector<float> beta(4 * H);
+            std::vector<float> beta(4 * H), alpha(4 * H), gamma(4 * H);
             for (int d = 0; d < 2; ++d)
             {
                 const std::string sfx = "_l" + std::to_string(l) + (d ? "_reverse" : "");
-                int rc = launch_make_planes(tw.f32["lstm.weight_ih" + sfx].d, 2 * H, H, nullptr, 1,
-                                            tw.wih_hi[l] + (size_t)d * 2 * H * H, tw.wih_lo[l] + (size_t)d * 2 * H * H,
-                                            2 * H, H, 0);
+                int rc = launch_q_to_half(whh_raw[t]["lstm.weight_ih" + sfx], (long)2 * H * H, tw.wih_q[l] + (size_t)d * 2 * H * H, 0);
                 if (rc)
                     return rc;
+                for (int g = 0; g < 2 * H; ++g)
+                {
+                    alpha[d * 2 * H + g] = tw.wih_scale[l][d];
+                    gamma[d * 2 * H + g] = std::fmaf(127.0f, tw.wih_scale[l][d], tw.wih_offset[l][d]); // W = s*(q-127) + (o + 127 s)
+                }
                 const auto &bi = tw.f32["lstm.bias_ih" + sfx].host;
                 const auto &bh = tw.f32["lstm.bias_hh" + sfx].host;
                 for (int g = 0; g < 2 * H; ++g)
@@ -387,7 +403,7 @@ static int build_operands(Model *m, std::map<std::string, uint8_t *> (&whh_raw)[
                     tw.whh_img[l][d] = img;
                 }
             }
-            if (upload(m, &tw.wih_beta[l], beta))
+            if (upload(m, &tw.wih_beta[l], beta) || upload(m, &tw.wih_alpha[l], alpha) || upload(m, &tw.wih_gamma[l], gamma))
                 return -1;
         }
         // ---- fc2 + BN2 (inference.cpp:127-140)

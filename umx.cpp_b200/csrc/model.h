@@ -22,10 +22,13 @@ struct TargetWeights
     // recurrent weights stay quantised: [k][unit][gate] uint8 + (scale, offset)
     uint8_t *whh_q[3][2] = {};
     float whh_scale[3][2] = {}, whh_offset[3][2] = {};
+    float wih_scale[3][2] = {}, wih_offset[3][2] = {};
     uint8_t *whh_img[3][2] = {}; // pre-swizzled SMEM image for the cluster kernel (hidden 1024 only)
     // GEMM operands (fp16 hi/lo planes, K-major) and fused-epilogue constants
-    __half *wih_hi[3] = {}, *wih_lo[3] = {}; // [2 dirs * 2H][H]
-    float *wih_beta[3] = {};                 // b_ih + b_hh, [2 dirs * 2H]
+    // W_ih of both directions stacked as the EXACT quantised integers in fp16 ([2 dirs * 2H][H]); the GEMM epilogue
+    // applies W = scale*q + offset: x.W = scale*(x.q) + offset*rowsum(x) + (b_ih + b_hh)
+    __half *wih_q[3] = {};
+    float *wih_alpha[3] = {}, *wih_gamma[3] = {}, *wih_beta[3] = {}; // scale, offset, b_ih + b_hh per output row
     __half *fc2_hi = nullptr, *fc2_lo = nullptr; // [H][2H]
     float *fc2_alpha = nullptr, *fc2_beta = nullptr;
     __half *fc3_hi = nullptr, *fc3_lo = nullptr; // [4104][H] (rows >= 4098 zero)

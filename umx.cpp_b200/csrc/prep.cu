@@ -160,6 +160,50 @@ int launch_mask_to_mag(const float *mask, int ld, const float2 *spec, float *mag
     return 0;
 }
 
+__global__ void rowsum_kernel(const __half *__restrict__ hi, const __half *__restrict__ lo, long rows, int K, int ld,
+                              float *__restrict__ out)
+{
+    const long r = (long)blockIdx.x * (blockDim.x / 32) + threadIdx.x / 32;
+    const int lane = threadIdx.x & 31;
+    if (r >= rows)
+        return;
+    const __half2 *h2 = reinterpret_cast<const __half2 *>(hi + r * ld);
+    const __half2 *l2 = reinterpret_cast<const __half2 *>(lo + r * ld);
+    float acc = 0.f;
+    for (int k = lane; k < K / 2; k += 32)
+    {
+        const float2 a = __half22float2(h2[k]), b = __half22float2(l2[k]);
+        acc += (a.x + b.x) + (a.y + b.y);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1)
+        acc += __shfl_xor_sync(0xffffffffu, acc, o);
+    if (lane == 0)
+        out[r] = acc;
+}
+
+int launch_rowsum(const __half *hi, const __half *lo, long rows, int K, int ld, float *out, cudaStream_t st)
+{
+    UMX_CHECK(K % 2 == 0 && ld % 2 == 0, "rowsum: K and pitch must be even");
+    rowsum_kernel<<<ceil_div(rows, 8), 256, 0, st>>>(hi, lo, rows, K, ld, out);
+    UMX_CUDA_OK(cudaGetLastError());
+    return 0;
+}
+
+__global__ void q_to_half_kernel(const uint8_t *__restrict__ q, long n, __half *__restrict__ out)
+{
+    const long i = (long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n)
+        out[i] = __int2half_rn((int)q[i] - 127); // centred: keeps x.q small next to offset*rowsum(x)
+}
+
+int launch_q_to_half(const uint8_t *q, long n, __half *out, cudaStream_t st)
+{
+    q_to_half_kernel<<<ceil_div(n, 256), 256, 0, st>>>(q, n, out);
+    UMX_CUDA_OK(cudaGetLastError());
+    return 0;
+}
+
 // x[f][c*1487 + b] = |spec[f][c][b]|, b < 1487, as fp16 (hi, lo) planes (src/inference.cpp:29,58-68)
 __global__ void spec_to_x_kernel(const float2 *__restrict__ spec, long M, __half *__restrict__ xh, __half *__restrict__ xl)
 {

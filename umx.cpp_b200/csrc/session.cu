@@ -98,13 +98,19 @@ int session_create(Model *m, int max_tracks, int n_buf, Session **out)
     }
     s->st = s->own_st;
     if (cudaStreamCreateWithFlags(&s->st_in, cudaStreamNonBlocking) != cudaSuccess ||
-        cudaStreamCreateWithFlags(&s->st_out, cudaStreamNonBlocking) != cudaSuccess)
+        cudaStreamCreateWithFlags(&s->st_out, cudaStreamNonBlocking) != cudaSuccess ||
+        [&] { // lowest priority: the post stage should only take what the network stage leaves idle
+            int lo = 0, hi = 0;
+            cudaDeviceGetStreamPriorityRange(&lo, &hi);
+            return cudaStreamCreateWithPriority(&s->st_post, cudaStreamNonBlocking, lo);
+        }() != cudaSuccess)
     {
         set_error("session_create: cudaStreamCreate failed");
         return fail(-1);
     }
     int rc = 0;
-    rc |= salloc(s, &s->spec, M * 2 * kBins);
+    rc |= salloc(s, &s->spec_buf[0], M * 2 * kBins);
+    rc |= salloc(s, &s->spec_buf[1], M * 2 * kBins);
     rc |= salloc(s, &s->xh, M * kFc1InPad, true); // pad columns stay zero
     rc |= salloc(s, &s->xl, M * kFc1InPad, true);
     rc |= salloc(s, &s->act_h, 4 * M * 2 * H);
@@ -115,17 +121,23 @@ int session_create(Model *m, int max_tracks, int n_buf, Session **out)
         rc |= salloc(s, &s->lb_l[i], 4 * M * H);
     }
     rc |= salloc(s, &s->xproj, 4 * M * 4 * H);
+    rc |= salloc(s, &s->rowsum, 4 * M);
     rc |= salloc(s, &s->fc2_h, 4 * M * H);
     rc |= salloc(s, &s->fc2_l, 4 * M * H);
-    rc |= salloc(s, &s->mask, 4 * M * kMaskLd);
+    rc |= salloc(s, &s->mask_buf[0], 4 * M * kMaskLd);
+    rc |= salloc(s, &s->mask_buf[1], 4 * M * kMaskLd);
     rc |= salloc(s, &s->stems, 4 * M * 2 * kBins);
-    rc |= salloc(s, &s->maxabs, (size_t)s->T, true);
+    rc |= salloc(s, &s->maxabs_buf[0], (size_t)s->T, true);
+    rc |= salloc(s, &s->maxabs_buf[1], (size_t)s->T, true);
     rc |= salloc(s, &s->partials, (size_t)s->T * kWienerChunks * 20 * kBins);
     rc |= salloc(s, &s->stats, (size_t)s->T * 16 * kBins);
     rc |= salloc(s, &s->h_state, (size_t)s->T * 3 * 8 * s->Hh, true);
     rc |= salloc(s, &s->c_state, (size_t)s->T * 3 * 8 * s->Hh, true);
     if (rc)
         return fail(-1);
+    s->spec = s->spec_buf[0];
+    s->mask = s->mask_buf[0];
+    s->maxabs = s->maxabs_buf[0];
     s->acc_pool.assign(s->T, nullptr);
     s->in_pool.assign(s->T, nullptr);
     s->out_pool.assign(s->T, nullptr);
@@ -185,6 +197,8 @@ void session_destroy(Session *s)
         cudaStreamDestroy(s->st_in);
     if (s->st_out)
         cudaStreamDestroy(s->st_out);
+    if (s->st_post)
+        cudaStreamDestroy(s->st_post);
     if (s->own_st)
         cudaStreamDestroy(s->own_st);
     delete s;
@@ -200,12 +214,12 @@ int session_reset(Session *s)
 }
 
 // ---- the network (src/inference.cpp:58-186) ------------------------------------------------------------
-static int run_gemm(Session *s, const GemmBatch &b)
+static int run_gemm(Session *s, const GemmBatch &b, int terms = 0)
 {
     s->launches++;
     if (s->gemm_impl == 1)
         return launch_gemm_simt(b, s->st);
-    return launch_gemm_tc(b, s->gemm_terms, s->st);
+    return launch_gemm_tc(b, terms ? terms : s->gemm_terms, s->st);
 }
 
 int session_lstm(Session *s, int n_tracks, int target_begin, int target_count, bool want_f32)
@@ -227,19 +241,25 @@ int session_lstm(Session *s, int n_tracks, int target_begin, int target_count, b
                     p.A = {s->act_h + (size_t)t * Mc * 2 * H, s->act_l + (size_t)t * Mc * 2 * H, 2 * H, 0};
                 else
                     p.A = {s->lb_h[(l - 1) & 1] + (size_t)t * Mc * H, s->lb_l[(l - 1) & 1] + (size_t)t * Mc * H, H, 0};
-                p.B = {m->t[t].wih_hi[l], m->t[t].wih_lo[l], H, 0};
+                // W_ih as exact integers (one fp16 plane): x.W = scale*(x.q) + offset*rowsum(x) + bias
+                s->launches++;
+                if (int rc = launch_rowsum(p.A.hi, p.A.lo, M, H, p.A.ld, s->rowsum + (size_t)t * Mc, s->st))
+                    return rc;
+                p.B = {m->t[t].wih_q[l], nullptr, H, 0};
                 p.M = (int)M;
                 p.N = 4 * H;
                 p.K = H;
                 p.act = kActNone;
-                p.alpha = nullptr;
+                p.alpha = m->t[t].wih_alpha[l];
+                p.gamma = m->t[t].wih_gamma[l];
+                p.rowvec = s->rowsum + (size_t)t * Mc;
                 p.beta = m->t[t].wih_beta[l];
                 p.out_f32 = s->xproj + (size_t)t * Mc * 4 * H;
                 p.ldo = 4 * H;
                 p.n_group = 4 * H;
                 p.group_stride = 0;
             }
-            if (int rc = run_gemm(s, b))
+            if (int rc = run_gemm(s, b, std::min(s->gemm_terms, 2))) // no weight lo plane: at most hi*q + lo*q
                 return rc;
         }
         StageScope sc(s, "lstm");
@@ -373,10 +393,9 @@ int session_network(Session *s, int n_tracks)
     return 0;
 }
 
-int session_run_segment(Session *s, int seg, int n_tracks)
+int session_front(Session *s, int seg, int n_tracks)
 {
     const StftTrack *dst = s->d_stft + (size_t)seg * s->T;
-    const IstftTrack *dis = s->d_istft + (size_t)seg * s->T;
     {
         StageScope sc(s, "stft");
         UMX_CUDA_OK(cudaMemsetAsync(s->maxabs, 0, sizeof(float) * s->T, s->st));
@@ -392,6 +411,12 @@ int session_run_segment(Session *s, int seg, int n_tracks)
         if (int rc = tp_allgather_masks(s))
             return rc;
     }
+    return 0;
+}
+
+int session_back(Session *s, int seg, int n_tracks)
+{
+    const IstftTrack *dis = s->d_istft + (size_t)seg * s->T;
     {
         StageScope sc(s, "wiener");
         WienerArgs w{};
@@ -421,6 +446,13 @@ int session_run_segment(Session *s, int seg, int n_tracks)
             return rc;
     }
     return 0;
+}
+
+int session_run_segment(Session *s, int seg, int n_tracks)
+{
+    if (int rc = session_front(s, seg, n_tracks))
+        return rc;
+    return session_back(s, seg, n_tracks);
 }
 
 // ---- umx_inference on host buffers (src/inference.cpp:12-207) ------------------------------------------
@@ -532,6 +564,15 @@ int session_demix_device(Session *s, const float *const *d_audio, const int64_t 
 
     size_t ev = 0;
     std::vector<long> copied_in(n_tracks, 0);
+    const bool pipelined = s->pipeline != 0 && max_segs > 1;
+    cudaStream_t main_st = s->st;
+    std::vector<cudaEvent_t> back_done(max_segs);
+    if (pipelined)
+    { // the post stream starts after everything queued so far (accumulator memsets, descriptors)
+        cudaEvent_t e = take_event(s, ev);
+        UMX_CUDA_OK(cudaEventRecord(e, main_st));
+        UMX_CUDA_OK(cudaStreamWaitEvent(s->st_post, e, 0));
+    }
     for (int sg = 0; sg < max_segs; ++sg) // sequential: h/c stream from segment to segment
     {
         if (host_in)
@@ -550,19 +591,39 @@ int session_demix_device(Session *s, const float *const *d_audio, const int64_t 
             UMX_CUDA_OK(cudaEventRecord(e, s->st_in));
             UMX_CUDA_OK(cudaStreamWaitEvent(s->st, e, 0));
         }
-        if (int rc = session_run_segment(s, sg, n_tracks))
+        // two-stage pipeline: STFT + networks of segment sg on the main stream; Wiener / iSTFT / finalize of the
+        // same segment on st_post, so they fill the SMs the recurrence of segment sg+1 leaves idle
+        const int b = sg & 1;
+        s->spec = s->spec_buf[b];
+        s->mask = s->mask_buf[b];
+        s->maxabs = s->maxabs_buf[b];
+        if (pipelined && sg >= 2)
+            UMX_CUDA_OK(cudaStreamWaitEvent(main_st, back_done[sg - 2], 0)); // buffer b is free again
+        if (int rc = session_front(s, sg, n_tracks))
             return rc;
+        if (pipelined)
+        {
+            cudaEvent_t e = take_event(s, ev);
+            UMX_CUDA_OK(cudaEventRecord(e, main_st));
+            UMX_CUDA_OK(cudaStreamWaitEvent(s->st_post, e, 0));
+            s->st = s->st_post; // the back stage's launches (and stage timers) go to the post stream
+        }
+        int rc_back = session_back(s, sg, n_tracks);
+        if (!rc_back)
         {
             StageScope sc(s, "finalize");
             s->launches++;
-            if (int rc = launch_finalize(s->d_final + (size_t)sg * s->T, n_tracks, max_range[sg], shift_offset, s->n_buf, stride, s->tp_nt, s->st, s->tp_t0))
-                return rc;
+            rc_back = launch_finalize(s->d_final + (size_t)sg * s->T, n_tracks, max_range[sg], shift_offset, s->n_buf, stride, s->tp_nt, s->st, s->tp_t0);
         }
+        cudaStream_t back_st = s->st;
+        s->st = main_st;
+        if (rc_back)
+            return rc_back;
+        back_done[sg] = take_event(s, ev);
+        UMX_CUDA_OK(cudaEventRecord(back_done[sg], back_st));
         if (host_out)
         { // ship the finished range of every stem while the next segment computes
-            cudaEvent_t e = take_event(s, ev);
-            UMX_CUDA_OK(cudaEventRecord(e, s->st));
-            UMX_CUDA_OK(cudaStreamWaitEvent(s->st_out, e, 0));
+            UMX_CUDA_OK(cudaStreamWaitEvent(s->st_out, back_done[sg], 0));
             for (int i = 0; i < n_tracks; ++i)
             {
                 const FinalizeTrack &f = hf[(size_t)sg * s->T + i];
@@ -577,6 +638,8 @@ int session_demix_device(Session *s, const float *const *d_audio, const int64_t 
             }
         }
     }
+    if (pipelined) // completion of the caller-visible stream implies completion of the post stage
+        UMX_CUDA_OK(cudaStreamWaitEvent(main_st, back_done[max_segs - 1], 0));
     if (host_out)
         UMX_CUDA_OK(cudaStreamSynchronize(s->st_out));
     return 0;

@@ -41,6 +41,7 @@ struct Session
     float *maxabs = nullptr;                 // [T]
     float *partials = nullptr, *stats = nullptr;
     float *h_state = nullptr, *c_state = nullptr; // [T][3][4][2][Hh]
+    float *rowsum = nullptr;                 // [4][Mcap] row sums of the LSTM layer input (exact-integer W_ih GEMM)
     float *lstm_f32 = nullptr;               // optional fp32 LSTM output (kernel-level API), [4][Mcap][H]
 
     StftTrack *d_stft = nullptr;   // descriptor arrays [seg_cap][T]
@@ -48,6 +49,10 @@ struct Session
     FinalizeTrack *d_final = nullptr;
     int seg_cap = 0;
     cudaStream_t st_in = nullptr, st_out = nullptr; // host<->device copy streams (overlap with compute)
+    cudaStream_t st_post = nullptr;                 // Wiener/iSTFT/finalize of segment s run here while segment s+1's network runs on st
+    float2 *spec_buf[2] = {};                       // spec / mask / maxabs are double-buffered between the two stages
+    float *mask_buf[2] = {}, *maxabs_buf[2] = {};
+    int pipeline = 0;                               // option "pipeline": 1 = post stage on its own low-priority stream (measured: no gain, the GPU is power-capped)
     std::vector<cudaEvent_t> ev_pool;
 
     // grow-only pools for whole-track demixing
@@ -73,6 +78,8 @@ void session_destroy(Session *s);
 int session_reset(Session *s);
 // one lockstep pass over descriptor row `seg` for n_tracks tracks (stft .. istft)
 int session_run_segment(Session *s, int seg, int n_tracks);
+int session_front(Session *s, int seg, int n_tracks); // STFT + networks (+ mask all-gather)
+int session_back(Session *s, int seg, int n_tracks);  // Wiener-EM + iSTFT / overlap-add
 int session_network(Session *s, int n_tracks);
 int session_lstm(Session *s, int n_tracks, int target_begin, int target_count, bool want_f32);
 // host_in / host_out (optional): stream the inputs in and the finished output ranges out, segment by segment,
