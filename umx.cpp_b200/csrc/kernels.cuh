@@ -102,7 +102,7 @@ struct LstmLayerArgs
     const uint8_t *whh_q[kTargets][2];
     float whh_scale[kTargets][2];
     float whh_offset[kTargets][2];
-    const float *xproj;    // [target][M][2*4*Hh] : W_ih x + b_ih + b_hh, gate order i,f,g,o per direction
+    const float *xproj;    // [target][M][2*4*Hh] : W_ih x + b_ih + b_hh, column dir*4Hh + 4*unit + gate (gates i,f,g,o)
     long xproj_target_stride;
     float *h_state;        // [track][target][dir][Hh] for this layer
     float *c_state;
@@ -165,7 +165,7 @@ int launch_rowmajor_to_colmajor(const float *in, int F, int H, int ld, float *ou
 // rowsum[r] = sum_k (hi + lo)[r][k] over K columns of `rows` rows with pitch ld (one warp per row)
 int launch_rowsum(const __half *hi, const __half *lo, long rows, int K, int ld, float *out, cudaStream_t st);
 // fp16 plane of the centred quantised integers q - 127 (exact for uint8)
-int launch_q_to_half(const uint8_t *q, long n, __half *out, cudaStream_t st);
+int launch_q_to_half(const uint8_t *q, int Hh, int K, __half *out, cudaStream_t st);
 int launch_spec_to_x(const float2 *spec, long M, __half *xh, __half *xl, cudaStream_t st);
 int launch_mask_to_mag(const float *mask, int ld, const float2 *spec, float *mag, long M, cudaStream_t st);
 

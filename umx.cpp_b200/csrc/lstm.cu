@@ -33,14 +33,15 @@ __global__ void lstm_simple_kernel(const LstmLayerArgs a)
     h_s[u] = h;
     __syncthreads();
 
-    const float *xp = a.xproj + (long)target * a.xproj_target_stride + (long)dir * 4 * Hh + u;
+    const float *xp = a.xproj + (long)target * a.xproj_target_stride + (long)dir * 4 * Hh + 4 * u; // gate-interleaved
     const int ldx = 8 * Hh;
     for (int step = 0; step < a.F; ++step)
     {
         const int t = dir == 0 ? step : a.F - 1 - step;
         const long row = (long)trk * a.F + t;
         const float *x = xp + row * ldx;
-        float gi = x[0], gf = x[Hh], gg = x[2 * Hh], go = x[3 * Hh];
+        const float4 xg = *reinterpret_cast<const float4 *>(x);
+        const float gi = xg.x, gf = xg.y, gg = xg.z, go = xg.w;
         float ai = 0.f, af = 0.f, ag = 0.f, ao = 0.f;
 #pragma unroll 8
         for (int k = 0; k < Hh; ++k)

@@ -364,7 +364,7 @@ static int build_operands(Model *m, std::map<std::string, uint8_t *> (&whh_raw)[
     for (int t = 0; t < kTargets; ++t)
     {
         TargetWeights &tw = m->t[t];
-        // ---- LSTM: W_ih of both directions stacked (rows dir*2H + gate row), bias b_ih + b_hh
+        // ---- LSTM: W_ih of both directions stacked (rows dir*2H + 4*unit + gate), bias b_ih + b_hh
         for (int l = 0; l < 3; ++l)
         {
             if (dev_alloc(m, &tw.wih_q[l], (size_t)4 * H * H))
@@ -373,7 +373,7 @@ static int build_operands(Model *m, std::map<std::string, uint8_t *> (&whh_raw)[
             for (int d = 0; d < 2; ++d)
             {
                 const std::string sfx = "_l" + std::to_string(l) + (d ? "_reverse" : "");
-                int rc = launch_q_to_half(whh_raw[t]["lstm.weight_ih" + sfx], (long)2 * H * H, tw.wih_q[l] + (size_t)d * 2 * H * H, 0);
+                int rc = launch_q_to_half(whh_raw[t]["lstm.weight_ih" + sfx], Hh, H, tw.wih_q[l] + (size_t)d * 2 * H * H, 0);
                 if (rc)
                     return rc;
                 for (int g = 0; g < 2 * H; ++g)
@@ -383,8 +383,9 @@ static int build_operands(Model *m, std::map<std::string, uint8_t *> (&whh_raw)[
                 }
                 const auto &bi = tw.f32["lstm.bias_ih" + sfx].host;
                 const auto &bh = tw.f32["lstm.bias_hh" + sfx].host;
-                for (int g = 0; g < 2 * H; ++g)
-                    beta[d * 2 * H + g] = bi[g] + bh[g]; // lstm.cpp:132-140
+                for (int g = 0; g < 4; ++g)
+                    for (int u = 0; u < Hh; ++u)
+                        beta[d * 2 * H + 4 * u + g] = bi[g * Hh + u] + bh[g * Hh + u]; // lstm.cpp:132-140, gate-interleaved rows
                 uint8_t *packed = nullptr;
                 if (dev_alloc(m, &packed, (size_t)4 * Hh * Hh))
                     return -1;

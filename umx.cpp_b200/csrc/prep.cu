@@ -190,16 +190,21 @@ int launch_rowsum(const __half *hi, const __half *lo, long rows, int K, int ld, 
     return 0;
 }
 
-__global__ void q_to_half_kernel(const uint8_t *__restrict__ q, long n, __half *__restrict__ out)
+// W_ih as the centred quantised integers in fp16, rows re-ordered gate-interleaved: out row 4*unit + gate =
+// in row gate*Hh + unit (the order the recurrence kernel reads the input projection in)
+__global__ void q_to_half_kernel(const uint8_t *__restrict__ q, int Hh, int K, __half *__restrict__ out)
 {
     const long i = (long)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < n)
-        out[i] = __int2half_rn((int)q[i] - 127); // centred: keeps x.q small next to offset*rowsum(x)
+    if (i >= (long)4 * Hh * K)
+        return;
+    const int row = (int)(i / K), c = (int)(i % K);
+    const int unit = row >> 2, gate = row & 3;
+    out[i] = __int2half_rn((int)q[((long)gate * Hh + unit) * K + c] - 127); // centred: keeps x.q small next to offset*rowsum(x)
 }
 
-int launch_q_to_half(const uint8_t *q, long n, __half *out, cudaStream_t st)
+int launch_q_to_half(const uint8_t *q, int Hh, int K, __half *out, cudaStream_t st)
 {
-    q_to_half_kernel<<<ceil_div(n, 256), 256, 0, st>>>(q, n, out);
+    q_to_half_kernel<<<ceil_div((long)4 * Hh * K, 256), 256, 0, st>>>(q, Hh, K, out);
     UMX_CUDA_OK(cudaGetLastError());
     return 0;
 }
