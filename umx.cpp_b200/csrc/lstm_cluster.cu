@@ -29,6 +29,7 @@
 #include "tc_common.cuh"
 
 #include <cstdlib>
+#include <type_traits>
 
 namespace umx
 {
@@ -49,19 +50,9 @@ constexpr int kSOff = kBOff + 4 * kBBuf;          // offset * sum_k h_k: [half 2
 constexpr int kBarOff = kSOff + 2 * 64 + 2 * 256;
 constexpr int kSmemBytes = kBarOff + 64;
 static_assert(kSmemBytes <= 232448, "dynamic shared memory budget of one CTA exceeded");
-// epilogue warps: 8 (one per TMEM lane quadrant and row half) x EW groups that split the tracks of a half;
-// then 1 MMA warp, 1 shipper / writer warp and 2 warps that sum the digit bytes
-#ifndef UMX_LSTM_SKIP
-#define UMX_LSTM_SKIP 0 // timing experiments only (results are wrong): 1 no TMEM loads, 2 no digit stores, 4 no h stores, 8 no xp loads
-#endif
-#ifndef UMX_LSTM_ILP
-#define UMX_LSTM_ILP 2
-#endif
-#ifndef UMX_LSTM_EPI_GROUPS
-#define UMX_LSTM_EPI_GROUPS 1
-#endif
-__host__ __device__ constexpr int epi_groups(int tp) { return tp >= 8 ? UMX_LSTM_EPI_GROUPS : 1; }
-__host__ __device__ constexpr int cluster_threads(int tp) { return 32 * (8 * epi_groups(tp) + 4); }
+// 8 epilogue warps (one per TMEM lane quadrant and row half), 1 MMA warp, 1 shipper warp and 2 warps that sum the
+// digit bytes and write the layer output
+constexpr int kThreads = 32 * 12;
 constexpr uint32_t kTmemCols = 512; // [0,256): accumulators (half*128 + row half*64), [256,512): W_hh (row half*128 + k/4)
 constexpr uint32_t kTmemA = 256;
 
@@ -94,12 +85,28 @@ __device__ __forceinline__ void cluster_sync_all()
 {
     asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
 }
-__device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t (&r)[16])
+// tcgen05.ld 16x256b: the warp reads 16 TMEM lanes x (8 * X) columns; thread t gets, for each group j of 8 columns,
+// r[4j], r[4j+1] = lane t/4, columns 8j + 2(t%4) + {0,1} and r[4j+2], r[4j+3] = lane t/4 + 8, same columns
+__device__ __forceinline__ void tmem_ld_16x256b_x4(uint32_t taddr, uint32_t *r)
 {
-    asm volatile("tcgen05.ld.sync.aligned.32x32b.x16.b32"
+    asm volatile("tcgen05.ld.sync.aligned.16x256b.x4.b32"
                  "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
                  : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
                    "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+                 : "r"(taddr)
+                 : "memory");
+}
+__device__ __forceinline__ void tmem_ld_16x256b_x2(uint32_t taddr, uint32_t *r)
+{
+    asm volatile("tcgen05.ld.sync.aligned.16x256b.x2.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
+                 : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7])
+                 : "r"(taddr)
+                 : "memory");
+}
+__device__ __forceinline__ void tmem_ld_16x256b_x1(uint32_t taddr, uint32_t *r)
+{
+    asm volatile("tcgen05.ld.sync.aligned.16x256b.x1.b32 {%0, %1, %2, %3}, [%4];"
+                 : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3])
                  : "r"(taddr)
                  : "memory");
 }
@@ -139,6 +146,13 @@ __device__ __forceinline__ void bulk_copy_to_peer(uint32_t remote_dst, uint32_t 
                  "r"(local_src), "r"(bytes), "r"(remote_bar)
                  : "memory");
 }
+// prmt.b32 with sign-replicating selector nibbles (8 | byte): one byte of x, sign-extended (__byte_perm masks that bit off)
+__device__ __forceinline__ int sext_byte(uint32_t x, uint32_t sel)
+{
+    int r;
+    asm("prmt.b32 %0, %1, 0, %2;" : "=r"(r) : "r"(x), "r"(sel));
+    return r;
+}
 __device__ __forceinline__ void st_shared_u8(uint32_t addr, uint32_t v)
 {
     asm volatile("st.shared.u8 [%0], %1;" ::"r"(addr), "r"(v) : "memory");
@@ -147,44 +161,34 @@ __device__ __forceinline__ void st_shared_f32(uint32_t addr, float v)
 {
     asm volatile("st.shared.f32 [%0], %1;" ::"r"(addr), "f"(v) : "memory");
 }
-__device__ __forceinline__ float ld_shared_f32(uint32_t addr)
-{
-    float v;
-    asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(addr) : "memory");
-    return v;
-}
-__device__ __forceinline__ float4 ld_shared_f32x4(uint32_t addr)
-{
-    float4 v;
-    asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(addr) : "memory");
-    return v;
-}
-__device__ __forceinline__ uint4 ld_shared_u32x4(uint32_t addr)
-{
-    uint4 v;
-    asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(addr) : "memory");
-    return v;
-}
 // K-major tile with 64-byte rows and 64-byte swizzle (16-byte chunk index ^= (row >> 1) & 3); 8-row groups 512 B apart
 __device__ __forceinline__ uint64_t smem_desc_sw64(uint32_t smem_addr)
 {
     return (uint64_t)((smem_addr & 0x3FFFF) >> 4) | ((uint64_t)1 << 16) | ((uint64_t)(512 >> 4) << 32) | ((uint64_t)1 << 46) |
            ((uint64_t)4 << 61);
 }
-// gate activation with per-lane constants: sigmoid = 1 * rcp(1 + 2^(-log2e x)) + 0, tanh = -2 * rcp(1 + 2^(2 log2e x)) + 1
-__device__ __forceinline__ float act_rcp(float x, float A, float B, float Cc)
+// sigmoid(x) = 1 / (1 + 2^(-log2e x)), tanh(x) = 1 - 2 / (1 + 2^(2 log2e x))
+__device__ __forceinline__ float sigmoid_fast(float x)
 {
     float e, r;
-    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(x * B));
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(x * -1.4426950408889634f));
     asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(1.0f + e));
-    return fmaf(A, r, Cc);
+    return r;
 }
-__device__ __forceinline__ float tanh_fast(float x) { return act_rcp(x, -2.0f, 2.885390081777927f, 1.0f); }
-
-// sum_i D_i * 2^(-6-7i): the integer dot products of the three digit planes back to one float
-__device__ __forceinline__ float combine_digits(uint32_t d0, uint32_t d1, uint32_t d2)
+__device__ __forceinline__ float tanh_fast(float x)
 {
-    return fmaf((float)(int)d2, 1.0f / 1048576.0f, fmaf((float)(int)d1, 1.0f / 8192.0f, (float)(int)d0 * (1.0f / 64.0f)));
+    float e, r;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(x * 2.885390081777927f));
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(1.0f + e));
+    return fmaf(-2.0f, r, 1.0f);
+}
+
+// base + scale * sum_i D_i 2^(-6-7i): the integer dot products of the three digit planes back to one float.
+// D0 * 128 + D1 stays inside int32 (|D_i| <= 512 * 255 * 64); s13 = scale * 2^-13, s20 = scale * 2^-20.
+__device__ __forceinline__ float gate_pre(uint32_t d0, uint32_t d1, uint32_t d2, float s13, float s20, float base)
+{
+    const int v = (int)d0 * 128 + (int)d1;
+    return fmaf((float)v, s13, fmaf((float)(int)d2, s20, base));
 }
 
 // debug (compile with -DUMX_LSTM_TIMING): clock64 stamps of one step of CTA (0,0,0); UMX_LSTM_DEBUG=1 prints them
@@ -202,10 +206,11 @@ struct ClusterArgs
     const uint8_t *img[kTargets][2]; // pre-swizzled W_hh image per (target, dir): [8 CTAs][128 KB]
 };
 
-// Lane (q, g) holds h of (unit kk of this CTA, track 4*jc + g of the half): its three digit bytes go straight
-// into this CTA's own tile of the h buffer, B row n = 3*track + digit, byte kk of the (swizzled) 64-byte row.
-// The 8 lanes of a track write 8 consecutive bytes; the four tracks of a warp land in different banks.
-__device__ __forceinline__ void publish_digits(float h, int g, int jc, uint32_t tile, uint32_t kk)
+// The three digit bytes of h of (unit kk of this CTA, track trk of the half) go straight into this CTA's own tile of
+// the h buffer: B row n = TP * digit + track, byte kk of the (swizzled) 64-byte row.  The 8 lanes of a track write
+// 8 consecutive bytes; the four tracks of a warp land in different 16-byte chunks.
+template <int TP>
+__device__ __forceinline__ void publish_digits(float h, uint32_t trk, uint32_t tile, uint32_t kk)
 {
     int v = __float2int_rn(h * 1048576.0f); // 2^20
     const int d2 = ((v + 64) & 127) - 64;
@@ -213,17 +218,16 @@ __device__ __forceinline__ void publish_digits(float h, int g, int jc, uint32_t 
     const int d1 = ((v + 64) & 127) - 64;
     v = (v - d1) >> 7; // d0 in [-64, 64]
     const int dig[3] = {v, d1, d2};
-    const uint32_t n0 = 3u * (4u * jc + g); // row of digit 0 of this lane's track
 #pragma unroll
     for (int i = 0; i < 3; ++i)
     {
-        const uint32_t n = n0 + i;
+        const uint32_t n = (uint32_t)(TP * i) + trk;
         st_shared_u8(tile + n * 64u + ((((kk >> 4) ^ (n >> 1)) & 3u) << 4) + (kk & 15u), (uint32_t)dig[i]);
     }
 }
 
-template <int TP> // tracks per half: 4, 8 or 16
-__global__ void __cluster_dims__(kC, 1, 1) __launch_bounds__(cluster_threads(TP), 1) lstm_cluster_kernel(const ClusterArgs P)
+template <int TP> // tracks per half: 8 or 16
+__global__ void __cluster_dims__(kC, 1, 1) __launch_bounds__(kThreads, 1) lstm_cluster_kernel(const ClusterArgs P)
 {
     extern __shared__ __align__(1024) uint8_t smem[];
     const LstmLayerArgs &a = P.a;
@@ -234,14 +238,11 @@ __global__ void __cluster_dims__(kC, 1, 1) __launch_bounds__(cluster_threads(TP)
     const int n_group = min(2 * TP, a.n_tracks - trk0); // tracks of this cluster
     const int n_halves = n_group > TP ? 2 : 1;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    constexpr int N = (3 * TP + 15) / 16 * 16; // MMA N: (track, digit) rows, padded to a multiple of 16
-    constexpr int NQ = TP / 4;                 // track quads per half
-    constexpr int EW = epi_groups(TP);         // epilogue warp groups
-    constexpr int NE = 8 * EW;                 // epilogue warps; warp NE issues the MMAs, warp NE + 1 ships, NE + 2.. sum
+    static_assert(TP == 8 || TP == 16, "tracks per half");
+    constexpr int N = (3 * TP + 15) / 16 * 16; // MMA N: rows TP * digit + track of the h operand, padded to a multiple of 16
+    constexpr int NT = TP / 4;                 // tracks per half and epilogue thread
+    constexpr int NE = 8;                      // epilogue warps; warp NE issues the MMAs, warp NE + 1 ships, NE + 2.. sum
     constexpr int NSW = TP == 16 ? 2 : 1;      // warps summing the digit bytes (the second one idles for small groups)
-    constexpr int NQW = NQ / EW;               // track quads per half and epilogue warp
-    constexpr int G = NQW >= UMX_LSTM_ILP ? UMX_LSTM_ILP : NQW; // track quads in flight per epilogue warp
-    constexpr int kThreads = cluster_threads(TP);
     constexpr int kBarCount = 32 * (NE + 1);   // named barrier: the epilogue warps arrive, the shipper waits
     constexpr uint32_t kTileBytes = 64u * N;
     constexpr uint32_t kStepBytes = (kC - 1) * kTileBytes; // the 7 peers' digit tiles
@@ -277,7 +278,7 @@ __global__ void __cluster_dims__(kC, 1, 1) __launch_bounds__(cluster_threads(TP)
     const uint32_t tmem_base = *tmem_slot;
     if (warp < 8)
     {
-        // warp (qd, hh) fills TMEM lanes [32 qd, 32 qd + 32) of row half hh: lane = gate row 4*unit' + gate, one
+        // warp (qd, hh) fills TMEM lanes [32 qd, 32 qd + 32) of row half hh: lane = gate row 8*gate + unit', one
         // 512-byte row of the image per lane, four k bytes per 32-bit column
         const int qd = warp & 3, hh = warp >> 2;
         const uint4 *src = reinterpret_cast<const uint4 *>(P.img[target][dir] + (size_t)r * kABytes + (size_t)(hh * 128 + 32 * qd + lane) * kHhC);
@@ -293,22 +294,73 @@ __global__ void __cluster_dims__(kC, 1, 1) __launch_bounds__(cluster_threads(TP)
     cluster_sync_all(); // every CTA's barriers and zeroed buffers exist before anyone writes remotely
 
     const int F = a.F;
+    // The layer output, off the critical path and shared by the four helper warps: h of one step for NC pairs of tracks
+    // of a half, rebuilt from the digit bytes of this CTA's own tile (the exact value the recurrence continues with)
+    // and split into the fp16 (hi, lo) planes the next GEMM reads.  A track's 64 units are one 128-byte row per plane;
+    // lane (kk = 4 (lane % 16), sub = lane / 16) owns 4 units of track 2 c + sub of the half, two tracks per store.
+    auto write_h = [&](int hstep, int whalf, uint32_t parity, int c0, auto nc_tag) {
+        constexpr int NC = decltype(nc_tag)::value;
+        const uint32_t wkk = 4u * (lane & 15), sub = lane >> 4;
+        const int t = dir == 0 ? hstep : F - 1 - hstep;
+        const uint8_t *tile = smem + kBOff + ((whalf * 2) + parity) * kBBuf + r * kBTile;
+        uint32_t dg[NC][3];
+#pragma unroll
+        for (int c = 0; c < NC; ++c)
+#pragma unroll
+            for (int i = 0; i < 3; ++i)
+            {
+                const uint32_t n = (uint32_t)(TP * i + 2 * (c0 + c)) + sub;
+                dg[c][i] = *reinterpret_cast<const uint32_t *>(tile + n * 64u + ((((wkk >> 4) ^ (n >> 1)) & 3u) << 4) + (wkk & 15u));
+            }
+#pragma unroll
+        for (int c = 0; c < NC; ++c)
+        {
+            float hv[4];
+            __half hi[4], lo[4];
+#pragma unroll
+            for (int e = 0; e < 4; ++e)
+            {
+                // byte e of each digit word, sign-extended (PRMT with the sign-replicate selector)
+                const uint32_t sel = (uint32_t)e | ((8u | e) << 4) | ((8u | e) << 8) | ((8u | e) << 12);
+                const int v = (sext_byte(dg[c][0], sel) << 14) + (sext_byte(dg[c][1], sel) << 7) + sext_byte(dg[c][2], sel);
+                hv[e] = (float)v * (1.0f / 1048576.0f);
+                split_half(hv[e], hi[e], lo[e]);
+            }
+            const int trk = trk0 + whalf * TP + 2 * (c0 + c) + (int)sub;
+            if (trk < a.n_tracks)
+            {
+                const long o = (long)target * a.out_target_stride + ((long)trk * F + t) * a.ldo + a.col_offset + dir * kHhC + kUnits * r + (int)wkk;
+                __half2 ph[2] = {__halves2half2(hi[0], hi[1]), __halves2half2(hi[2], hi[3])};
+                __half2 pl[2] = {__halves2half2(lo[0], lo[1]), __halves2half2(lo[2], lo[3])};
+                *reinterpret_cast<uint2 *>(a.out_hi + o) = *reinterpret_cast<uint2 *>(ph);
+                *reinterpret_cast<uint2 *>(a.out_lo + o) = *reinterpret_cast<uint2 *>(pl);
+                if (a.out_f32)
+                    *reinterpret_cast<float4 *>(a.out_f32 + (long)target * a.out_f32_target_stride + ((long)trk * F + t) * (2 * kHhC) + dir * kHhC +
+                                                kUnits * r + (int)wkk) = make_float4(hv[0], hv[1], hv[2], hv[3]);
+            }
+        }
+    };
+    // pairs of tracks (chunks) per half: [0, kWc) shipper warp, [kWc, 2 kWc) MMA warp, the rest split over the sum warps
+    constexpr int kWc = TP / 8, kWs = TP / 4 / NSW;
+    using WcTag = std::integral_constant<int, kWc>;
+    using WsTag = std::integral_constant<int, kWs>;
     if (warp < NE)
     {
         // ================= epilogue warps =================
-        const int w8 = warp & 7, jq0 = (warp >> 3) * NQW; // first track quad of this warp
-        const int qd = w8 & 3, hh = w8 >> 2, q = lane >> 2, g = lane & 3;
-        const uint32_t kk = (uint32_t)(32 * hh + 8 * qd + q); // hidden unit of this quad inside the CTA
+        // TMEM lane (= gate row of the MMA) 8*gate + unit' inside each 32-lane quadrant: the 16x256b load shape then
+        // hands thread (unit' = lane / 4, cp = lane % 4) all four gates of its unit for the tracks
+        // 8 (e / 2) + 2 cp + (e % 2), e < NT, and all three digits: no exchange between lanes is needed.
+        const int qd = warp & 3, hh = warp >> 2, up = lane >> 2, cp = lane & 3;
+        const uint32_t kk = (uint32_t)(32 * hh + 8 * qd + up); // hidden unit of this thread inside the CTA
         const int k = kUnits * r + (int)kk;
         const float scale = a.whh_scale[target][dir];
-        // per-lane activation constants: gate 2 (g) is tanh, gates 0,1,3 (i,f,o) are sigmoids
-        const float actA = (g == 2) ? -2.0f : 1.0f, actB = (g == 2) ? 2.885390081777927f : -1.4426950408889634f,
-                    actC = (g == 2) ? 1.0f : 0.0f;
+        const float s13 = scale * (1.0f / 8192.0f), s20 = scale * (1.0f / 1048576.0f);
         const uint32_t t_lane = tmem_base + ((uint32_t)(32 * qd) << 16);
         const int ldx = 8 * kHhC;
-        const float *xrow = a.xproj + (long)target * a.xproj_target_stride + (long)dir * 4 * kHhC + 4 * k + g; // gate-interleaved
+        const float *xrow = a.xproj + (long)target * a.xproj_target_stride + (long)dir * 4 * kHhC + 4 * k; // 4 gates of unit k
         const long trk_x = (long)F * ldx; // floats between tracks in xproj
         const long st_base = ((long)target * 2 + dir) * kHhC + k;
+        auto trk_of = [&](int e) { return 8 * (e >> 1) + 2 * cp + (e & 1); };
 
         // After an epilogue thread has written its digits of a half: make them visible to the async proxy and
         // ARRIVE (non-blocking) on the half's named barrier; the shipper warp waits there and ships the tile.
@@ -319,23 +371,18 @@ __global__ void __cluster_dims__(kC, 1, 1) __launch_bounds__(cluster_threads(TP)
             else
                 asm volatile("bar.arrive 2, %0;" ::"n"(kBarCount) : "memory");
         };
-
-        // input projection of one step for this warp's tracks of a half.  The per-track addresses are a dependent
-        // chain on purpose (the empty asm keeps the compiler from hoisting loop-invariant 64-bit offsets
-        // into registers, which spilled the hot loop).
-        auto load_xp = [&](float(&dst)[4 * NQW], int tb, int tt) {
-            const float *pt = xrow + (long)tt * ldx + (long)(tb + 4 * jq0) * trk_x;
-            const int nv = a.n_tracks - tb - 4 * jq0;
+        // input projection (4 gates) of one step for this thread's tracks of a half
+        auto load_xp = [&](float4(&dst)[NT], int tb, int tt) {
 #pragma unroll
-            for (int j = 0; j < 4 * NQW; ++j)
+            for (int e = 0; e < NT; ++e)
             {
-                dst[j] = (j < nv) ? __ldg(pt) : 0.f;
-                pt += trk_x;
-                asm volatile("" : "+l"(pt));
+                const int trk = tb + trk_of(e);
+                dst[e] = trk < a.n_tracks ? __ldg(reinterpret_cast<const float4 *>(xrow + (long)tt * ldx + (long)trk * trk_x)) : make_float4(0.f, 0.f, 0.f, 0.f);
             }
         };
 
-        float c[2][NQW], hlast[2][NQW], xp[2][4 * NQW];
+        float c[2][NT], hlast[2][NT];
+        float4 xp[2][NT];
 #pragma unroll
         for (int half = 0; half < 2; ++half)
         {
@@ -343,14 +390,13 @@ __global__ void __cluster_dims__(kC, 1, 1) __launch_bounds__(cluster_threads(TP)
                 break;
             const int tb = trk0 + half * TP;
 #pragma unroll
-            for (int jw = 0; jw < NQW; ++jw)
+            for (int e = 0; e < NT; ++e)
             {
-                const int jc = jq0 + jw;
-                const int trk = min(tb + 4 * jc + g, a.n_tracks - 1); // padded tracks mirror a real one, never stored
+                const int trk = min(tb + trk_of(e), a.n_tracks - 1); // padded tracks mirror a real one, never stored
                 const long so = (long)trk * a.state_track_stride + st_base;
-                c[half][jw] = a.c_state[so];
-                hlast[half][jw] = a.h_state[so];
-                publish_digits(hlast[half][jw], g, jc, sB + (uint32_t)(half * 2) * kBBuf + (uint32_t)r * kBTile, kk);
+                c[half][e] = a.c_state[so];
+                hlast[half][e] = a.h_state[so];
+                publish_digits<TP>(hlast[half][e], (uint32_t)trk_of(e), sB + (uint32_t)(half * 2) * kBBuf + (uint32_t)r * kBTile, kk);
             }
             load_xp(xp[half], tb, dir == 0 ? 0 : F - 1);
             publish_tile(half);
@@ -375,80 +421,59 @@ __global__ void __cluster_dims__(kC, 1, 1) __launch_bounds__(cluster_threads(TP)
                 const bool dbg = (step == 200 && threadIdx.x == 0 && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0);
 #endif
                 UMX_DBG_STAMP(half * 4 + 0);
-                // MMAs of this half-step complete, and offset * sum_k h_k per track written by the MMA warp
+                // MMAs of this half-step complete, and offset * sum_k h_k per track written by the sum warps
                 mbar_wait(mma_done0 + 8u * half, (uint32_t)(step & 1));
                 tc_fence_after();
                 UMX_DBG_STAMP(half * 4 + 1);
-                // G track quads at a time, written stage by stage so that their dependent chains (TMEM load ->
-                // activations -> quad transpose -> cell update -> digits) interleave instead of running back to back
+                // D[s][.]: 16-lane half s of the quadrant = gates 2s (lanes 0..7) and 2s + 1 (lanes 8..15); column
+                // group j of 8 = digit (8 j) / TP, tracks (8 j) % TP + 2 cp + {0,1}
+                uint32_t D[2][N / 2];
 #pragma unroll
-                for (int jw0 = 0; jw0 < NQW; jw0 += G)
+                for (int sgh = 0; sgh < 2; ++sgh)
                 {
-                    uint32_t d[G][16];
-                    float4 os4[G];
-#pragma unroll
-                    for (int u = 0; u < G; ++u)
+                    const uint32_t ta = t_lane + ((uint32_t)(16 * sgh) << 16) + (uint32_t)(half * 128 + hh * 64);
+                    if (TP == 16)
                     {
-                        if (UMX_LSTM_SKIP & 1)
-                        {
-#pragma unroll
-                            for (int e = 0; e < 16; ++e)
-                                d[u][e] = (uint32_t)(step + e);
-                        }
-                        else
-                            tmem_ld16(t_lane + half * 128 + hh * 64 + 12 * (jq0 + jw0 + u), d[u]);
-                        os4[u] = ld_shared_f32x4(sS + (uint32_t)(half * 64 + (jq0 + jw0 + u) * 16));
+                        tmem_ld_16x256b_x4(ta, &D[sgh][0]);
+                        tmem_ld_16x256b_x2(ta + 32, &D[sgh][16]);
                     }
-                    tc_wait_ld();
-                    float act[G][4];
-#pragma unroll
-                    for (int u = 0; u < G; ++u)
+                    else
                     {
-                        const float os[4] = {os4[u].x, os4[u].y, os4[u].z, os4[u].w};
-#pragma unroll
-                        for (int jj = 0; jj < 4; ++jj)
-                        {
-                            const float dot = combine_digits(d[u][3 * jj], d[u][3 * jj + 1], d[u][3 * jj + 2]);
-                            const float pre = xp[half][4 * (jw0 + u) + jj] + fmaf(scale, dot, os[jj]); // lstm.cpp:132-140
-                            act[u][jj] = act_rcp(pre, actA, actB, actC);
-                        }
+                        tmem_ld_16x256b_x2(ta, &D[sgh][0]);
+                        tmem_ld_16x256b_x1(ta + 16, &D[sgh][8]);
                     }
-                    // 4x4 transpose inside the quad: afterwards lane g holds the four gates of track 4*jc + g
-                    const bool b0 = g & 1, b1 = g & 2;
-                    float keepA[G], keepB[G], recvA[G], recvB[G], v2[G], v3[G], hn[G];
-#pragma unroll
-                    for (int u = 0; u < G; ++u)
-                    {
-                        keepA[u] = b0 ? act[u][1] : act[u][0];
-                        keepB[u] = b0 ? act[u][3] : act[u][2];
-                        recvA[u] = __shfl_xor_sync(0xffffffffu, b0 ? act[u][0] : act[u][1], 1);
-                        recvB[u] = __shfl_xor_sync(0xffffffffu, b0 ? act[u][2] : act[u][3], 1);
-                    }
-#pragma unroll
-                    for (int u = 0; u < G; ++u)
-                    {
-                        v2[u] = __shfl_xor_sync(0xffffffffu, b1 ? keepA[u] : keepB[u], 2); // gate g^2
-                        v3[u] = __shfl_xor_sync(0xffffffffu, b1 ? recvA[u] : recvB[u], 2); // gate g^3
-                    }
-#pragma unroll
-                    for (int u = 0; u < G; ++u)
-                    {
-                        const float v0 = b1 ? keepB[u] : keepA[u], v1 = b1 ? recvB[u] : recvA[u]; // gates g, g^1 of track g
-                        // the value with gate label x sits at index g ^ x
-                        const float w0 = b0 ? v1 : v0, w1 = b0 ? v0 : v1, w2 = b0 ? v3[u] : v2[u], w3 = b0 ? v2[u] : v3[u];
-                        const float i_t = b1 ? w2 : w0, f_t = b1 ? w3 : w1, g_t = b1 ? w0 : w2, o_t = b1 ? w1 : w3;
-                        c[half][jw0 + u] = fmaf(f_t, c[half][jw0 + u], i_t * g_t); // lstm.cpp:152-154
-                        hn[u] = o_t * tanh_fast(c[half][jw0 + u]);                 // lstm.cpp:155
-                        hlast[half][jw0 + u] = hn[u];
-                    }
-#pragma unroll
-                    for (int u = 0; u < G; ++u)
-                        if (!(UMX_LSTM_SKIP & 2))
-                            publish_digits(hn[u], g, jq0 + jw0 + u, tile_out, kk);
                 }
+                float os[NT];
+#pragma unroll
+                for (int e2 = 0; e2 < NT / 2; ++e2)
+                {
+                    float2 v;
+                    asm volatile("ld.shared.v2.f32 {%0, %1}, [%2];" : "=f"(v.x), "=f"(v.y) : "r"(sS + (uint32_t)(half * 64 + (8 * e2 + 2 * cp) * 4)) : "memory");
+                    os[2 * e2] = v.x;
+                    os[2 * e2 + 1] = v.y;
+                }
+                tc_wait_ld();
+                float hn[NT];
+#pragma unroll
+                for (int e = 0; e < NT; ++e)
+                {
+                    // register of (gate, digit dg) of track e: group j = dg * (TP / 8) + e / 2, element e % 2
+                    auto Dv = [&](int gate, int dg) { return D[gate >> 1][4 * (dg * (TP / 8) + (e >> 1)) + 2 * (gate & 1) + (e & 1)]; };
+                    const float xg[4] = {xp[half][e].x, xp[half][e].y, xp[half][e].z, xp[half][e].w};
+                    float pre[4];
+#pragma unroll
+                    for (int gate = 0; gate < 4; ++gate)
+                        pre[gate] = gate_pre(Dv(gate, 0), Dv(gate, 1), Dv(gate, 2), s13, s20, xg[gate] + os[e]); // lstm.cpp:132-140
+                    const float i_t = sigmoid_fast(pre[0]), f_t = sigmoid_fast(pre[1]), g_t = tanh_fast(pre[2]), o_t = sigmoid_fast(pre[3]);
+                    c[half][e] = fmaf(f_t, c[half][e], i_t * g_t); // lstm.cpp:152-154
+                    hn[e] = o_t * tanh_fast(c[half][e]);           // lstm.cpp:155
+                    hlast[half][e] = hn[e];
+                }
+#pragma unroll
+                for (int e = 0; e < NT; ++e)
+                    publish_digits<TP>(hn[e], (uint32_t)trk_of(e), tile_out, kk);
                 // next step's input projection for this half: in flight while the other half is processed
-                if (!(UMX_LSTM_SKIP & 8))
-                    load_xp(xp[half], tb, tn);
+                load_xp(xp[half], tb, tn);
                 UMX_DBG_STAMP(half * 4 + 2);
                 publish_tile(half);
                 UMX_DBG_STAMP(half * 4 + 3);
@@ -464,14 +489,14 @@ __global__ void __cluster_dims__(kC, 1, 1) __launch_bounds__(cluster_threads(TP)
             if (half >= n_halves)
                 break;
 #pragma unroll
-            for (int jw = 0; jw < NQW; ++jw)
+            for (int e = 0; e < NT; ++e)
             {
-                const int trk = trk0 + half * TP + 4 * (jq0 + jw) + g;
+                const int trk = trk0 + half * TP + trk_of(e);
                 if (trk < a.n_tracks)
                 {
                     const long so = (long)trk * a.state_track_stride + st_base;
-                    a.h_state[so] = hlast[half][jw];
-                    a.c_state[so] = c[half][jw];
+                    a.h_state[so] = hlast[half][e];
+                    a.c_state[so] = c[half][e];
                 }
             }
         }
@@ -501,6 +526,8 @@ __global__ void __cluster_dims__(kC, 1, 1) __launch_bounds__(cluster_threads(TP)
                     else
                         bulk_copy_to_peer(peer_b + slot * kBBuf, sB + slot * kBBuf + (uint32_t)r * kBTile, kTileBytes, peer_bar + 8u * slot);
                 }
+                if (step >= 0)
+                    write_h(step, half, pn, 0, WcTag{}); // its share of the h just shipped
             }
         }
     }
@@ -525,7 +552,10 @@ __global__ void __cluster_dims__(kC, 1, 1) __launch_bounds__(cluster_threads(TP)
                     mbar_arrive_expect_tx(hfull0 + 8 * slot, kStepBytes); // the 7 peers' bulk copies complete this phase
                 wait_cluster(hfull0 + 8 * slot, (uint32_t)((step >> 1) & 1));
                 if (step == F)
+                {
+                    write_h(step - 1, half, p, kWc, WcTag{});
                     continue; // nothing left to compute: the bytes of the final publish have landed
+                }
                 tc_fence_after();
                 UMX_DBG_STAMP(dbo + 1);
                 const uint32_t b_lo = b_lo0 + slot * (kBBuf >> 4);
@@ -541,28 +571,22 @@ __global__ void __cluster_dims__(kC, 1, 1) __launch_bounds__(cluster_threads(TP)
                 }
                 __syncwarp();
                 UMX_DBG_STAMP(dbo + 2);
+                if (step >= 1)
+                    write_h(step - 1, half, p, kWc, WcTag{}); // its share of the previous step's h (own tile of this buffer)
             }
         }
     }
     else if (warp < NE + 2 + NSW)
     {
         // ================= sum warps: offset * sum_k h_k per track from the digit bytes of the 8 tiles =================
-        // (exactly the h the MMAs see).  Lane l sums the 16-byte chunk l of every 512-byte round, i.e. a quarter of
-        // row 8 j + l / 4; warp sw takes the rounds of its half of the tracks.
+        // (exactly the h the MMAs see).  A 512-byte round of a tile is 8 rows; lane l sums the 16-byte chunk l of a
+        // round, i.e. a quarter of row 8 j + l / 4.  Warp sw takes the three rounds (one per digit) of the tracks
+        // kTrk sw + l / 4, so one quad of lanes ends up with the three digit sums of one track.
         const int sw = warp - (NE + 2);
-        constexpr int kRounds = N / 8 / NSW;
+        constexpr int kTrk = TP / NSW; // tracks of this warp (8)
+        static_assert(kTrk == 8, "one round of rows per digit and sum warp");
         const float offset = a.whh_offset[target][dir];
-        // digit weight of the rows this lane sums (row n = 8 j + lane / 4, digit n % 3), folded with the offset
-        float wdig[kRounds];
-#pragma unroll
-        for (int j = 0; j < kRounds; ++j)
-        {
-            const int dg = (8 * (sw * kRounds + j) + (lane >> 2)) % 3;
-            wdig[j] = offset * (dg == 0 ? 1.0f / 64.0f : dg == 1 ? 1.0f / 8192.0f : 1.0f / 1048576.0f);
-        }
-        constexpr int kTrk = TP / NSW; // tracks of this warp
-        const uint32_t kk = 4u * (lane & 15), sub = lane >> 4; // the writer part: lane owns 4 units of every second track
-        const long trk_o = (long)F * a.ldo;
+        const float w0 = offset * (1.0f / 64.0f), w1 = offset * (1.0f / 8192.0f), w2 = offset * (1.0f / 1048576.0f);
         for (int step = 0; step <= F; ++step) // the extra round only writes out the last h
         {
             const uint32_t p = (uint32_t)(step & 1);
@@ -574,86 +598,51 @@ __global__ void __cluster_dims__(kC, 1, 1) __launch_bounds__(cluster_threads(TP)
                 const int dbo = 8 + (step - 200) * 8 + half * 4;
 #endif
                 wait_cluster(hfull0 + 8 * slot, (uint32_t)((step >> 1) & 1));
+#ifdef UMX_LSTM_TIMING
+                if (dbg)
+                    g_lstm_dbg[28 + (step - 200) * 2 + half] = clock64();
+#endif
                 if (step < F)
                 {
-                int acc[kRounds];
+                    int acc[3] = {0, 0, 0};
+                    // plain loads (the barrier wait above orders them): all 24 in flight before the first dp4a
+                    const uint4 *tl = reinterpret_cast<const uint4 *>(smem + kBOff + slot * kBBuf + sw * 512) + lane;
+                    uint4 v[3][kC];
 #pragma unroll
-                for (int j = 0; j < kRounds; ++j)
-                    acc[j] = 0;
-                const uint32_t tl = sB + slot * kBBuf + (uint32_t)(sw * kRounds * 512) + (uint32_t)lane * 16u;
+                    for (int dg = 0; dg < 3; ++dg)
 #pragma unroll
-                for (int src = 0; src < kC; ++src)
+                        for (int src = 0; src < kC; ++src)
+                            v[dg][src] = tl[(src * kBTile + dg * NSW * 512) / 16]; // rows TP*dg + 8 sw ..
 #pragma unroll
-                    for (int j = 0; j < kRounds; ++j)
+                    for (int dg = 0; dg < 3; ++dg)
                     {
-                        const uint4 v = ld_shared_u32x4(tl + (uint32_t)(src * kBTile + j * 512));
-                        acc[j] = __dp4a((int)v.x, 0x01010101, acc[j]);
-                        acc[j] = __dp4a((int)v.y, 0x01010101, acc[j]);
-                        acc[j] = __dp4a((int)v.z, 0x01010101, acc[j]);
-                        acc[j] = __dp4a((int)v.w, 0x01010101, acc[j]);
-                    }
-                const uint32_t scr = sS + 128u + (uint32_t)half * 256u + (uint32_t)(sw * kRounds * 8) * 4u; // offset * 2^e(n) * sum of row n
+                        int a4[4] = {0, 0, 0, 0};
 #pragma unroll
-                for (int j = 0; j < kRounds; ++j)
-                {
-                    int v = acc[j];
-                    v += __shfl_xor_sync(0xffffffffu, v, 1);
-                    v += __shfl_xor_sync(0xffffffffu, v, 2);
+                        for (int src = 0; src < kC; ++src)
+                        {
+                            a4[0] = __dp4a((int)v[dg][src].x, 0x01010101, a4[0]);
+                            a4[1] = __dp4a((int)v[dg][src].y, 0x01010101, a4[1]);
+                            a4[2] = __dp4a((int)v[dg][src].z, 0x01010101, a4[2]);
+                            a4[3] = __dp4a((int)v[dg][src].w, 0x01010101, a4[3]);
+                        }
+                        acc[dg] = (a4[0] + a4[1]) + (a4[2] + a4[3]);
+                    }
+#pragma unroll
+                    for (int dg = 0; dg < 3; ++dg)
+                    {
+                        acc[dg] += __shfl_xor_sync(0xffffffffu, acc[dg], 1);
+                        acc[dg] += __shfl_xor_sync(0xffffffffu, acc[dg], 2);
+                    }
                     if ((lane & 3) == 0)
-                        st_shared_f32(scr + (uint32_t)(8 * j + (lane >> 2)) * 4u, (float)v * wdig[j]);
+                        st_shared_f32(sS + (uint32_t)(half * 64 + (sw * kTrk + (lane >> 2)) * 4),
+                                      fmaf((float)acc[0], w0, fmaf((float)acc[1], w1, (float)acc[2] * w2)));
+                    __syncwarp();
+                    UMX_DBG_STAMP(dbo + 3);
+                    if (lane == 0)
+                        mbar_arrive(mma_done0 + 8u * half); // release: the epilogue's wait acquires the sums
                 }
-                __syncwarp();
-                if (lane < kTrk)
-                    st_shared_f32(sS + (uint32_t)(half * 64 + (sw * kTrk + lane) * 4),
-                                  ld_shared_f32(scr + 12u * lane) + ld_shared_f32(scr + 12u * lane + 4u) + ld_shared_f32(scr + 12u * lane + 8u));
-                __syncwarp();
-                UMX_DBG_STAMP(dbo + 3);
-                if (lane == 0)
-                    mbar_arrive(mma_done0 + 8u * half); // release: the epilogue's wait acquires the sums
-                }
-                if (step == 0)
-                    continue;
-                // Off the critical path: h of the PREVIOUS step (this CTA's own tile of the buffer just completed) goes
-                // out as the layer output, rebuilt from its digits (the exact value the recurrence continues with) and
-                // split into the fp16 (hi, lo) planes the next GEMM reads; a track's 64 units are one 128-byte row
-                // per plane, two tracks per store instruction.
-                const int t = dir == 0 ? step - 1 : F - step;
-                const int tb = trk0 + half * TP + sw * kTrk + sub;
-                const uint8_t *tile = smem + kBOff + slot * kBBuf + r * kBTile;
-                const long o = (long)target * a.out_target_stride + ((long)tb * F + t) * a.ldo + a.col_offset + dir * kHhC + kUnits * r + (int)kk;
-                uint32_t dg[kTrk / 2][3];
-#pragma unroll
-                for (int it = 0; it < kTrk / 2; ++it)
-#pragma unroll
-                    for (int i = 0; i < 3; ++i)
-                    {
-                        const uint32_t n = 3u * (uint32_t)(sw * kTrk + 2 * it + sub) + i;
-                        dg[it][i] = *reinterpret_cast<const uint32_t *>(tile + n * 64u + ((((kk >> 4) ^ (n >> 1)) & 3u) << 4) + (kk & 15u));
-                    }
-#pragma unroll
-                for (int it = 0; it < kTrk / 2; ++it)
-                {
-                    float hv[4];
-                    __half hi[4], lo[4];
-#pragma unroll
-                    for (int e = 0; e < 4; ++e)
-                    {
-                        const int v = ((int)(int8_t)(dg[it][0] >> (8 * e)) << 14) + ((int)(int8_t)(dg[it][1] >> (8 * e)) << 7) + (int)(int8_t)(dg[it][2] >> (8 * e));
-                        hv[e] = (float)v * (1.0f / 1048576.0f);
-                        split_half(hv[e], hi[e], lo[e]);
-                    }
-                    if (tb + 2 * it < a.n_tracks)
-                    {
-                        const long oo = o + (long)(2 * it) * trk_o;
-                        __half2 ph[2] = {__halves2half2(hi[0], hi[1]), __halves2half2(hi[2], hi[3])};
-                        __half2 pl[2] = {__halves2half2(lo[0], lo[1]), __halves2half2(lo[2], lo[3])};
-                        *reinterpret_cast<uint2 *>(a.out_hi + oo) = *reinterpret_cast<uint2 *>(ph);
-                        *reinterpret_cast<uint2 *>(a.out_lo + oo) = *reinterpret_cast<uint2 *>(pl);
-                        if (a.out_f32)
-                            *reinterpret_cast<float4 *>(a.out_f32 + (long)target * a.out_f32_target_stride + ((long)(tb + 2 * it) * F + t) * (2 * kHhC) +
-                                                        dir * kHhC + kUnits * r + (int)kk) = make_float4(hv[0], hv[1], hv[2], hv[3]);
-                    }
-                }
+                if (step >= 1)
+                    write_h(step - 1, half, p, 2 * kWc + sw * kWs, WsTag{}); // its share of the previous step's h
 #ifdef UMX_LSTM_TIMING
                 if (dbg)
                     g_lstm_dbg[24 + (step - 200) * 2 + half] = clock64();
@@ -672,7 +661,7 @@ __global__ void __cluster_dims__(kC, 1, 1) __launch_bounds__(cluster_threads(TP)
     }
 }
 
-// byte o of the image: CTA r, row half h, row m = 4*unit' + gate, k: plain rows of 512 bytes (one per TMEM lane)
+// byte o of the image: CTA r, row half h, TMEM lane m, k: plain rows of 512 bytes (one per TMEM lane)
 __global__ void whh_image_kernel(const uint8_t *__restrict__ q, uint8_t *__restrict__ img)
 {
     const long o = (long)blockIdx.x * blockDim.x + threadIdx.x;
@@ -681,7 +670,7 @@ __global__ void whh_image_kernel(const uint8_t *__restrict__ q, uint8_t *__restr
     const int r = (int)(o / kABytes);
     const int rem = (int)(o % kABytes);
     const int h = rem / (128 * kHhC), m = (rem / kHhC) & 127, k = rem % kHhC;
-    const int up = m >> 2, g = m & 3;
+    const int qd = m >> 5, g = (m >> 3) & 3, up = 8 * qd + (m & 7); // lane 8*gate + unit' inside each 32-lane quadrant
     const int row = g * kHhC + kUnits * r + 32 * h + up;
     img[o] = q[(long)row * kHhC + k];
 }
@@ -698,7 +687,7 @@ int launch_tp(const ClusterArgs &P, int groups, cudaStream_t st)
         attr_set[dev & 63] = true;
     }
     dim3 grid(kC, 2 * P.a.target_count, groups);
-    lstm_cluster_kernel<TP><<<grid, cluster_threads(TP), kSmemBytes, st>>>(P);
+    lstm_cluster_kernel<TP><<<grid, kThreads, kSmemBytes, st>>>(P);
     UMX_CUDA_OK(cudaGetLastError());
 #ifdef UMX_LSTM_TIMING
     if (getenv("UMX_LSTM_DEBUG"))
@@ -715,9 +704,9 @@ int launch_tp(const ClusterArgs &P, int groups, cudaStream_t st)
             fprintf(stderr, "\n");
         }
         fprintf(stderr, "lstm_cluster<%d> step 200 (cycles rel. to epilogue X wait begin)\n  epi X: done %+lld computed %+lld shipped %+lld | epi Y: wait %+lld done %+lld computed %+lld shipped %+lld\n"
-                        "  mma200 X: wait %+lld hfull %+lld issued %+lld sums %+lld | Y: wait %+lld hfull %+lld issued %+lld sums %+lld\n  mma201 X: wait %+lld hfull %+lld issued %+lld sums %+lld | Y: wait %+lld hfull %+lld issued %+lld sums %+lld\n  writer done: %+lld %+lld %+lld %+lld\n",
+                        "  mma200 X: wait %+lld hfull %+lld issued %+lld sums %+lld | Y: wait %+lld hfull %+lld issued %+lld sums %+lld\n  mma201 X: wait %+lld hfull %+lld issued %+lld sums %+lld | Y: wait %+lld hfull %+lld issued %+lld sums %+lld\n  writer done: %+lld %+lld %+lld %+lld | sum warp woke: %+lld %+lld %+lld %+lld\n",
                 TP, h[1] - h[0], h[2] - h[0], h[3] - h[0], h[4] - h[0], h[5] - h[0], h[6] - h[0], h[7] - h[0], h[8] - h[0], h[9] - h[0], h[10] - h[0], h[11] - h[0],
-                h[12] - h[0], h[13] - h[0], h[14] - h[0], h[15] - h[0], h[16] - h[0], h[17] - h[0], h[18] - h[0], h[19] - h[0], h[20] - h[0], h[21] - h[0], h[22] - h[0], h[23] - h[0], h[24] - h[0], h[25] - h[0], h[26] - h[0], h[27] - h[0]);
+                h[12] - h[0], h[13] - h[0], h[14] - h[0], h[15] - h[0], h[16] - h[0], h[17] - h[0], h[18] - h[0], h[19] - h[0], h[20] - h[0], h[21] - h[0], h[22] - h[0], h[23] - h[0], h[24] - h[0], h[25] - h[0], h[26] - h[0], h[27] - h[0], h[28] - h[0], h[29] - h[0], h[30] - h[0], h[31] - h[0]);
     }
 #endif
     return 0;
@@ -741,7 +730,7 @@ int lstm_cluster_max_active()
     int n = 0;
     cudaLaunchConfig_t cfg{};
     cfg.gridDim = dim3(kC, 64, 1);
-    cfg.blockDim = dim3(cluster_threads(16));
+    cfg.blockDim = dim3(kThreads);
     cfg.dynamicSmemBytes = kSmemBytes;
     cudaLaunchAttribute at[1];
     at[0].id = cudaLaunchAttributeClusterDimension;
@@ -768,12 +757,8 @@ int launch_lstm_cluster(const LstmLayerArgs &a, const uint8_t *const (*img)[2], 
     // a cluster takes up to 32 tracks as two ping-pong halves of TP tracks each
     const int groups = ceil_div(a.n_tracks, kMaxTracks);
     const int per = std::min(a.n_tracks, kMaxTracks);
-    if (per <= 4)
-        return launch_tp<4>(P, groups, st); // one half of 4
-    if (per <= 8)
-        return launch_tp<4>(P, groups, st); // two halves of 4
     if (per <= 16)
-        return launch_tp<8>(P, groups, st); // two halves of 8
+        return launch_tp<8>(P, groups, st); // one or two halves of 8
     return launch_tp<16>(P, groups, st);
 }
 
