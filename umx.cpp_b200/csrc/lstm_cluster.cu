@@ -46,12 +46,13 @@ constexpr int kABytes = 256 * kHhC;               // this CTA's 256 gate rows x 
 constexpr int kBTile = 48 * 64;                   // one source CTA's tile: up to 48 (track, digit) rows x 64 units
 constexpr int kBBuf = kC * kBTile;                // one (half, parity) h buffer: 24 KB
 constexpr int kBOff = 0;                          // [half 2][parity 2][8 source CTAs][48 rows][64 B], 64-byte swizzle
-constexpr int kSOff = kBOff + 4 * kBBuf;          // offset * sum_k h_k: [half 2][16 tracks] f32, then 48 floats of scratch per half
-constexpr int kBarOff = kSOff + 2 * 64 + 2 * 256;
-constexpr int kSmemBytes = kBarOff + 64;
+constexpr int kSOff = kBOff + 4 * kBBuf;          // offset * sum_k h_k: [half 2][16 tracks] f32
+constexpr int kPOff = kSOff + 2 * 64;             // its per-CTA partial sums: [half 2][parity 2][8 source CTAs][16 tracks] f32
+constexpr int kPBuf = kC * 64;
+constexpr int kBarOff = kPOff + 4 * kPBuf;
+constexpr int kSmemBytes = kBarOff + 96;
 static_assert(kSmemBytes <= 232448, "dynamic shared memory budget of one CTA exceeded");
-// 8 epilogue warps (one per TMEM lane quadrant and row half), 1 MMA warp, 1 shipper warp and 2 warps that sum the
-// digit bytes and write the layer output
+// 8 epilogue warps (one per TMEM lane quadrant and row half), 1 MMA warp, 1 shipper warp and 2 helper warps
 constexpr int kThreads = 32 * 12;
 constexpr uint32_t kTmemCols = 512; // [0,256): accumulators (half*128 + row half*64), [256,512): W_hh (row half*128 + k/4)
 constexpr uint32_t kTmemA = 256;
@@ -242,7 +243,6 @@ __global__ void __cluster_dims__(kC, 1, 1) __launch_bounds__(kThreads, 1) lstm_c
     constexpr int N = (3 * TP + 15) / 16 * 16; // MMA N: rows TP * digit + track of the h operand, padded to a multiple of 16
     constexpr int NT = TP / 4;                 // tracks per half and epilogue thread
     constexpr int NE = 8;                      // epilogue warps; warp NE issues the MMAs, warp NE + 1 ships, NE + 2.. sum
-    constexpr int NSW = TP == 16 ? 2 : 1;      // warps summing the digit bytes (the second one idles for small groups)
     constexpr int kBarCount = 32 * (NE + 1);   // named barrier: the epilogue warps arrive, the shipper waits
     constexpr uint32_t kTileBytes = 64u * N;
     constexpr uint32_t kStepBytes = (kC - 1) * kTileBytes; // the 7 peers' digit tiles
@@ -251,10 +251,10 @@ __global__ void __cluster_dims__(kC, 1, 1) __launch_bounds__(kThreads, 1) lstm_c
         __trap(); // the swizzled operand tiles need the 1024-byte alignment requested above
 
     uint64_t *bars = reinterpret_cast<uint64_t *>(smem + kBarOff);
-    // hfull[half][parity] (4), mma_done[half] (2), then the TMEM base address
-    const uint32_t hfull0 = smem_u32(bars), mma_done0 = smem_u32(bars + 4);
-    uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + 6);
-    const uint32_t sB = smem_u32(smem) + kBOff, sS = smem_u32(smem) + kSOff;
+    // hfull[half][parity] (4), mma_done[half] (2), sfull[half][parity] (4), then the TMEM base address
+    const uint32_t hfull0 = smem_u32(bars), mma_done0 = smem_u32(bars + 4), sfull0 = smem_u32(bars + 6);
+    uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + 10);
+    const uint32_t sB = smem_u32(smem) + kBOff, sS = smem_u32(smem) + kSOff, sP = smem_u32(smem) + kPOff;
 
     // ---- one-time setup: zeroed h buffers, barriers, TMEM, weights into TMEM ----
     {
@@ -266,8 +266,10 @@ __global__ void __cluster_dims__(kC, 1, 1) __launch_bounds__(kThreads, 1) lstm_c
     {
         for (int i = 0; i < 4; ++i)
             mbar_init(hfull0 + 8 * i, 2); // MMA warp (expect_tx of the peers' bytes) + this CTA's own shipper
-        mbar_init(mma_done0, 1 + NSW);    // tcgen05.commit of the MMAs + the sum warps once the offset terms are written
-        mbar_init(mma_done0 + 8, 1 + NSW);
+        mbar_init(mma_done0, 2);          // tcgen05.commit of the MMAs + the sum warp once the offset terms are written
+        mbar_init(mma_done0 + 8, 2);
+        for (int i = 0; i < 4; ++i)
+            mbar_init(sfull0 + 8 * i, 2); // sum warp (expect_tx of the peers' partial sums) + this CTA's own shipper
         fence_barrier_init();
     }
     if (warp == NE)
@@ -340,10 +342,12 @@ __global__ void __cluster_dims__(kC, 1, 1) __launch_bounds__(kThreads, 1) lstm_c
             }
         }
     };
-    // pairs of tracks (chunks) per half: [0, kWc) shipper warp, [kWc, 2 kWc) MMA warp, the rest split over the sum warps
-    constexpr int kWc = TP / 8, kWs = TP / 4 / NSW;
-    using WcTag = std::integral_constant<int, kWc>;
-    using WsTag = std::integral_constant<int, kWs>;
+    // pairs of tracks (chunks) per half: [0, kW0) MMA warp, then kW1 for helper warp 0 (which also adds up the partial
+    // sums) and kW2 for helper warp 1
+    constexpr int kW0 = TP / 8, kW1 = (TP / 2 - kW0) / 2, kW2 = TP / 2 - kW0 - kW1; // MMA warp, helper 0, helper 1
+    using W0Tag = std::integral_constant<int, kW0>;
+    using W1Tag = std::integral_constant<int, kW1>;
+    using W2Tag = std::integral_constant<int, kW2>;
     if (warp < NE)
     {
         // ================= epilogue warps =================
@@ -506,9 +510,17 @@ __global__ void __cluster_dims__(kC, 1, 1) __launch_bounds__(kThreads, 1) lstm_c
         // ================= shipper warp =================
         // Per half-step: wait until the epilogue warps have arrived on the half's named barrier, ship the digit
         // tile to the 7 peers (lanes 0..7, one peer each) and arrive on this CTA's own barrier for the local copy.
+        // Then sum the digit bytes of the tile (dp4a) into this CTA's share of offset * sum_k h_k per track
+        // (W = scale*q + offset: the term the integer MMA cannot carry; exactly the h the MMAs see) and ship those
+        // 64 bytes on a second barrier: they are needed only after the MMAs.
         const bool shipper = lane < kC;
         const uint32_t peer_b = shipper ? mapa(sB + (uint32_t)r * kBTile, (uint32_t)lane) : 0u;
+        const uint32_t peer_p = shipper ? mapa(sP + (uint32_t)r * 64u, (uint32_t)lane) : 0u;
         const uint32_t peer_bar = shipper ? mapa(hfull0, (uint32_t)lane) : 0u;
+        const uint32_t peer_sbar = shipper ? mapa(sfull0, (uint32_t)lane) : 0u;
+        const float offset = a.whh_offset[target][dir];
+        const float w0 = offset * (1.0f / 64.0f), w1 = offset * (1.0f / 8192.0f), w2 = offset * (1.0f / 1048576.0f);
+        constexpr int kRounds = 3 * TP / 8; // 512-byte rounds of 8 rows: lane l holds a quarter of row 8 j + l / 4
         for (int step = -1; step < F; ++step) // step -1 publishes the initial state into parity 0
         {
             const uint32_t pn = (uint32_t)((step + 1) & 1);
@@ -526,8 +538,38 @@ __global__ void __cluster_dims__(kC, 1, 1) __launch_bounds__(kThreads, 1) lstm_c
                     else
                         bulk_copy_to_peer(peer_b + slot * kBBuf, sB + slot * kBBuf + (uint32_t)r * kBTile, kTileBytes, peer_bar + 8u * slot);
                 }
-                if (step >= 0)
-                    write_h(step, half, pn, 0, WcTag{}); // its share of the h just shipped
+                // rows TP * digit + track: round j covers digit (8 j) / TP, tracks (8 j) % TP + l / 4
+                const uint4 *tl = reinterpret_cast<const uint4 *>(smem + kBOff + slot * kBBuf + r * kBTile) + lane;
+                uint4 v[kRounds];
+#pragma unroll
+                for (int j = 0; j < kRounds; ++j)
+                    v[j] = tl[32 * j];
+                int acc[kRounds];
+#pragma unroll
+                for (int j = 0; j < kRounds; ++j)
+                {
+                    acc[j] = __dp4a((int)v[j].x, 0x01010101, __dp4a((int)v[j].y, 0x01010101, 0)) +
+                             __dp4a((int)v[j].z, 0x01010101, __dp4a((int)v[j].w, 0x01010101, 0));
+                    acc[j] += __shfl_xor_sync(0xffffffffu, acc[j], 1);
+                    acc[j] += __shfl_xor_sync(0xffffffffu, acc[j], 2);
+                }
+                const uint32_t s_own = sP + slot * kPBuf + (uint32_t)r * 64u;
+                if ((lane & 3) == 0)
+                {
+#pragma unroll
+                    for (int q = 0; q < TP / 8; ++q) // this lane's tracks: 8 q + l / 4
+                        st_shared_f32(s_own + (uint32_t)(8 * q + (lane >> 2)) * 4u,
+                                      fmaf((float)acc[q], w0, fmaf((float)acc[TP / 8 + q], w1, (float)acc[2 * (TP / 8) + q] * w2)));
+                }
+                asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+                __syncwarp();
+                if (shipper)
+                {
+                    if (lane == r)
+                        mbar_arrive(sfull0 + 8u * slot);
+                    else
+                        bulk_copy_to_peer(peer_p + slot * kPBuf, s_own, 64u, peer_sbar + 8u * slot);
+                }
             }
         }
     }
@@ -553,7 +595,7 @@ __global__ void __cluster_dims__(kC, 1, 1) __launch_bounds__(kThreads, 1) lstm_c
                 wait_cluster(hfull0 + 8 * slot, (uint32_t)((step >> 1) & 1));
                 if (step == F)
                 {
-                    write_h(step - 1, half, p, kWc, WcTag{});
+                    write_h(step - 1, half, p, 0, W0Tag{});
                     continue; // nothing left to compute: the bytes of the final publish have landed
                 }
                 tc_fence_after();
@@ -572,21 +614,16 @@ __global__ void __cluster_dims__(kC, 1, 1) __launch_bounds__(kThreads, 1) lstm_c
                 __syncwarp();
                 UMX_DBG_STAMP(dbo + 2);
                 if (step >= 1)
-                    write_h(step - 1, half, p, kWc, WcTag{}); // its share of the previous step's h (own tile of this buffer)
+                    write_h(step - 1, half, p, 0, W0Tag{}); // its share of the previous step's h (own tile of this buffer)
             }
         }
     }
-    else if (warp < NE + 2 + NSW)
+    else
     {
-        // ================= sum warps: offset * sum_k h_k per track from the digit bytes of the 8 tiles =================
-        // (exactly the h the MMAs see).  A 512-byte round of a tile is 8 rows; lane l sums the 16-byte chunk l of a
-        // round, i.e. a quarter of row 8 j + l / 4.  Warp sw takes the three rounds (one per digit) of the tracks
-        // kTrk sw + l / 4, so one quad of lanes ends up with the three digit sums of one track.
+        // ================= helper warps =================
+        // Warp 0: once the 8 CTAs' partial sums of a half-step have landed, add them up into offset * sum_k h_k per
+        // track for the epilogue.  Both: their share of the layer output.
         const int sw = warp - (NE + 2);
-        constexpr int kTrk = TP / NSW; // tracks of this warp (8)
-        static_assert(kTrk == 8, "one round of rows per digit and sum warp");
-        const float offset = a.whh_offset[target][dir];
-        const float w0 = offset * (1.0f / 64.0f), w1 = offset * (1.0f / 8192.0f), w2 = offset * (1.0f / 1048576.0f);
         for (int step = 0; step <= F; ++step) // the extra round only writes out the last h
         {
             const uint32_t p = (uint32_t)(step & 1);
@@ -597,52 +634,37 @@ __global__ void __cluster_dims__(kC, 1, 1) __launch_bounds__(kThreads, 1) lstm_c
                 const bool dbg = ((step == 200 || step == 201) && sw == 0 && lane == 0 && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0);
                 const int dbo = 8 + (step - 200) * 8 + half * 4;
 #endif
-                wait_cluster(hfull0 + 8 * slot, (uint32_t)((step >> 1) & 1));
-#ifdef UMX_LSTM_TIMING
-                if (dbg)
-                    g_lstm_dbg[28 + (step - 200) * 2 + half] = clock64();
-#endif
-                if (step < F)
+                if (sw == 0)
                 {
-                    int acc[3] = {0, 0, 0};
-                    // plain loads (the barrier wait above orders them): all 24 in flight before the first dp4a
-                    const uint4 *tl = reinterpret_cast<const uint4 *>(smem + kBOff + slot * kBBuf + sw * 512) + lane;
-                    uint4 v[3][kC];
-#pragma unroll
-                    for (int dg = 0; dg < 3; ++dg)
-#pragma unroll
-                        for (int src = 0; src < kC; ++src)
-                            v[dg][src] = tl[(src * kBTile + dg * NSW * 512) / 16]; // rows TP*dg + 8 sw ..
-#pragma unroll
-                    for (int dg = 0; dg < 3; ++dg)
-                    {
-                        int a4[4] = {0, 0, 0, 0};
-#pragma unroll
-                        for (int src = 0; src < kC; ++src)
-                        {
-                            a4[0] = __dp4a((int)v[dg][src].x, 0x01010101, a4[0]);
-                            a4[1] = __dp4a((int)v[dg][src].y, 0x01010101, a4[1]);
-                            a4[2] = __dp4a((int)v[dg][src].z, 0x01010101, a4[2]);
-                            a4[3] = __dp4a((int)v[dg][src].w, 0x01010101, a4[3]);
-                        }
-                        acc[dg] = (a4[0] + a4[1]) + (a4[2] + a4[3]);
-                    }
-#pragma unroll
-                    for (int dg = 0; dg < 3; ++dg)
-                    {
-                        acc[dg] += __shfl_xor_sync(0xffffffffu, acc[dg], 1);
-                        acc[dg] += __shfl_xor_sync(0xffffffffu, acc[dg], 2);
-                    }
-                    if ((lane & 3) == 0)
-                        st_shared_f32(sS + (uint32_t)(half * 64 + (sw * kTrk + (lane >> 2)) * 4),
-                                      fmaf((float)acc[0], w0, fmaf((float)acc[1], w1, (float)acc[2] * w2)));
+                    if (lane == 0)
+                        mbar_arrive_expect_tx(sfull0 + 8 * slot, (kC - 1) * 64u);
+                    wait_cluster(sfull0 + 8 * slot, (uint32_t)((step >> 1) & 1)); // (the round step == F only absorbs the last shipment)
+                }
+                if (sw == 0 && step < F)
+                {
+#ifdef UMX_LSTM_TIMING
+                    if (dbg)
+                        g_lstm_dbg[28 + (step - 200) * 2 + half] = clock64();
+#endif
+                    // lane l: track l % 16, source CTAs 4 (l / 16) .. + 3
+                    const float *ps = reinterpret_cast<const float *>(smem + kPOff + slot * kPBuf) + (lane & 15) + (lane >> 4) * 64;
+                    float tot = (ps[0] + ps[16]) + (ps[32] + ps[48]);
+                    tot += __shfl_xor_sync(0xffffffffu, tot, 16);
+                    if (lane < 16)
+                        st_shared_f32(sS + (uint32_t)(half * 64 + lane * 4), tot);
                     __syncwarp();
                     UMX_DBG_STAMP(dbo + 3);
                     if (lane == 0)
                         mbar_arrive(mma_done0 + 8u * half); // release: the epilogue's wait acquires the sums
                 }
-                if (step >= 1)
-                    write_h(step - 1, half, p, 2 * kWc + sw * kWs, WsTag{}); // its share of the previous step's h
+                if (step == 0)
+                    continue;
+                // h of the previous step sits in this CTA's own tile of the buffer whose barrier completes now
+                wait_cluster(hfull0 + 8 * slot, (uint32_t)((step >> 1) & 1));
+                if (sw == 0)
+                    write_h(step - 1, half, p, kW0, W1Tag{});
+                else
+                    write_h(step - 1, half, p, kW0 + kW1, W2Tag{});
 #ifdef UMX_LSTM_TIMING
                 if (dbg)
                     g_lstm_dbg[24 + (step - 200) * 2 + half] = clock64();
