@@ -130,8 +130,10 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_tc_kernel(const __grid_const
         while (pi + 1 < P.count && tile >= P.p[pi + 1].tile_begin)
             ++pi;
         const int local = tile - P.p[pi].tile_begin;
-        m0 = (local % P.p[pi].m_tiles) * BM; // m fastest: CTAs running together share one B tile
-        n0 = (local / P.p[pi].m_tiles) * BN;
+        // n fastest: the CTAs running together cover a band of ~grid / n_tiles row tiles x all column tiles, so the
+        // activations (the big operand) stream from HBM once while the weights (a few MB) stay in L2
+        n0 = (local % P.p[pi].n_tiles) * BN;
+        m0 = (local / P.p[pi].n_tiles) * BM;
     };
 
     if (warp == 0)
@@ -243,32 +245,20 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_tc_kernel(const __grid_const
             float *__restrict__ of32 = P.p[pi].out_f32;
             __half *__restrict__ ohi = P.p[pi].out_hi;
             __half *__restrict__ olo = P.p[pi].out_lo;
+            const int row0 = m0 + 32 * q;
+            // the rank-1 term's row factors of this thread's 8 rows: loaded once per tile, before waiting for the MMAs
+            float rvv[8];
+#pragma unroll
+            for (int it = 0; it < 8; ++it)
+                rvv[it] = (rowvec && row0 + it * 4 + sub < M) ? __ldg(rowvec + row0 + it * 4 + sub) : 0.f;
             mbar_wait(tfull0 + 8 * acc, acc_phase);
             tc_fence_after();
             const uint32_t taddr = tmem_base + acc * BN + ((uint32_t)(32 * q) << 16);
-            const int row0 = m0 + 32 * q;
 #pragma unroll 1
             for (int ch = 0; ch < BN / 32; ++ch)
             {
-                uint32_t r[32];
-                tmem_ld32(taddr + ch * 32, r);
-                tc_wait_ld();
-                if (ch == BN / 32 - 1)
-                { // everything this warp needs has left TMEM
-                    tc_fence_before();
-                    __syncwarp();
-                    if (lane == 0)
-                        mbar_arrive(tempty0 + 8 * acc);
-                }
+                // per-column constants of this chunk: in flight while the accumulators come out of TMEM
                 const int nc0 = n0 + ch * 32;
-                if (nc0 >= N)
-                    continue;
-#pragma unroll
-                for (int i = 0; i < 8; ++i)
-                    *reinterpret_cast<float4 *>(stage_buf + lane * 36 + 4 * i) =
-                        make_float4(__uint_as_float(r[4 * i]), __uint_as_float(r[4 * i + 1]), __uint_as_float(r[4 * i + 2]),
-                                    __uint_as_float(r[4 * i + 3]));
-                __syncwarp();
                 const int n = nc0 + c4;
                 float al[4], be[4], ga[4];
 #pragma unroll
@@ -279,6 +269,24 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_tc_kernel(const __grid_const
                     be[e] = (beta && ok) ? __ldg(beta + n + e) : 0.f;
                     ga[e] = (rowvec && ok) ? __ldg(gamma + n + e) : 0.f;
                 }
+                uint32_t r[32];
+                tmem_ld32(taddr + ch * 32, r);
+                tc_wait_ld();
+                if (ch == BN / 32 - 1)
+                { // everything this warp needs has left TMEM
+                    tc_fence_before();
+                    __syncwarp();
+                    if (lane == 0)
+                        mbar_arrive(tempty0 + 8 * acc);
+                }
+                if (nc0 >= N)
+                    continue;
+#pragma unroll
+                for (int i = 0; i < 8; ++i)
+                    *reinterpret_cast<float4 *>(stage_buf + lane * 36 + 4 * i) =
+                        make_float4(__uint_as_float(r[4 * i]), __uint_as_float(r[4 * i + 1]), __uint_as_float(r[4 * i + 2]),
+                                    __uint_as_float(r[4 * i + 3]));
+                __syncwarp();
                 const int grp = n / n_group;
                 const long obase = (long)grp * gstride + (n - grp * n_group);
                 const bool full4 = n + 3 < N;
@@ -289,7 +297,7 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_tc_kernel(const __grid_const
                     const int m = row0 + row;
                     const float4 t4 = *reinterpret_cast<const float4 *>(stage_buf + row * 36 + c4);
                     float v[4] = {t4.x, t4.y, t4.z, t4.w};
-                    const float rv = (rowvec && m < M) ? __ldg(rowvec + m) : 0.f;
+                    const float rv = rvv[it];
 #pragma unroll
                     for (int e = 0; e < 4; ++e)
                         v[e] = act_apply(fmaf(v[e], al[e], fmaf(rv, ga[e], be[e])), act);
