@@ -86,6 +86,80 @@ __device__ __forceinline__ uint64_t smem_desc_sw64(uint32_t smem_addr)
            ((uint64_t)4 << 61);
 }
 
+// The rows of one 32-column chunk after the transpose through shared memory: lane (sub, c4) owns columns
+// [c4, c4 + 4) of the rows 4 it + sub.  ACT < 0: activation / outputs / rank-1 term decided at run time.
+struct EpiRows
+{
+    uint32_t stage_buf;
+    int sub, c4, row0, M, N, n, ldo;
+    long obase;
+    float *__restrict__ of32;
+    __half *__restrict__ ohi;
+    __half *__restrict__ olo;
+};
+template <int ACT, bool RV, bool F32, bool HALF>
+__device__ __forceinline__ void epi_rows(const EpiRows &e, const float (&al)[4], const float (&be)[4], const float (&ga)[4],
+                                         const float (&rvv)[8], int act_rt = 0, bool rv_rt = true)
+{
+    const bool full4 = e.n + 3 < e.N;
+#pragma unroll
+    for (int it = 0; it < 8; ++it)
+    {
+        const int row = it * 4 + e.sub;
+        const int m = e.row0 + row;
+        float v[4];
+        asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];"
+                     : "=f"(v[0]), "=f"(v[1]), "=f"(v[2]), "=f"(v[3])
+                     : "r"(e.stage_buf + (uint32_t)(row * 36 + e.c4) * 4u)
+                     : "memory");
+#pragma unroll
+        for (int c = 0; c < 4; ++c)
+        {
+            const float b = (RV && (ACT >= 0 || rv_rt)) ? fmaf(rvv[it], ga[c], be[c]) : be[c];
+            v[c] = fmaf(v[c], al[c], b);
+            if (ACT == kActTanh)
+                v[c] = tanhf(v[c]);
+            else if (ACT == kActRelu)
+                v[c] = fmaxf(v[c], 0.f);
+            else if (ACT < 0)
+                v[c] = act_apply(v[c], act_rt);
+        }
+        if (m >= e.M || e.n >= e.N)
+            continue;
+        const long o = e.obase + (long)m * e.ldo;
+        if (F32 && (ACT >= 0 || e.of32))
+        {
+            if (full4)
+                *reinterpret_cast<float4 *>(e.of32 + o) = make_float4(v[0], v[1], v[2], v[3]);
+            else
+                for (int c = 0; c < 4; ++c)
+                    if (e.n + c < e.N)
+                        e.of32[o + c] = v[c];
+        }
+        if (HALF && (ACT >= 0 || e.ohi))
+        {
+            __half h[4], l[4];
+#pragma unroll
+            for (int c = 0; c < 4; ++c)
+                split_half(v[c], h[c], l[c]);
+            if (full4)
+            {
+                *reinterpret_cast<uint2 *>(e.ohi + o) = make_uint2((uint32_t)__half_as_ushort(h[0]) | ((uint32_t)__half_as_ushort(h[1]) << 16),
+                                                                   (uint32_t)__half_as_ushort(h[2]) | ((uint32_t)__half_as_ushort(h[3]) << 16));
+                *reinterpret_cast<uint2 *>(e.olo + o) = make_uint2((uint32_t)__half_as_ushort(l[0]) | ((uint32_t)__half_as_ushort(l[1]) << 16),
+                                                                   (uint32_t)__half_as_ushort(l[2]) | ((uint32_t)__half_as_ushort(l[3]) << 16));
+            }
+            else
+                for (int c = 0; c < 4; ++c)
+                    if (e.n + c < e.N)
+                    {
+                        e.ohi[o + c] = h[c];
+                        e.olo[o + c] = l[c];
+                    }
+        }
+    }
+}
+
 template <int TERMS>
 __global__ void __launch_bounds__(kThreads, 1) gemm_tc_kernel(const __grid_constant__ TcParams P)
 {
@@ -227,7 +301,9 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_tc_kernel(const __grid_const
         // 128-bit accesses (row pitch 36 floats: conflict-free), so that 8 lanes cover one row's 32 columns
         // and every global store instruction writes four full 128-byte lines.
         const int q = warp & 3; // TMEM lane quadrant this warp may read
-        float *stage_buf = reinterpret_cast<float *>(epi_base + (warp - 2) * kEpiBytesPerWarp);
+        // shared-window address of this warp's transpose tile (explicit ld/st.shared: a generic pointer costs the
+        // long-latency generic path on every access)
+        const uint32_t stage_buf = smem_u32(epi_base + (warp - 2) * kEpiBytesPerWarp);
         const int sub = lane >> 3, c4 = (lane & 7) * 4;
         int acc = 0;
         uint32_t acc_phase = 0;
@@ -251,6 +327,8 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_tc_kernel(const __grid_const
 #pragma unroll
             for (int it = 0; it < 8; ++it)
                 rvv[it] = (rowvec && row0 + it * 4 + sub < M) ? __ldg(rowvec + row0 + it * 4 + sub) : 0.f;
+            // a tile lies inside one output group when the groups are whole tiles (or there is only one)
+            const int grp_tile = n_group >= N ? 0 : (n_group % BN == 0 ? n0 / n_group : -1);
             mbar_wait(tfull0 + 8 * acc, acc_phase);
             tc_fence_after();
             const uint32_t taddr = tmem_base + acc * BN + ((uint32_t)(32 * q) << 16);
@@ -283,61 +361,24 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_tc_kernel(const __grid_const
                     continue;
 #pragma unroll
                 for (int i = 0; i < 8; ++i)
-                    *reinterpret_cast<float4 *>(stage_buf + lane * 36 + 4 * i) =
-                        make_float4(__uint_as_float(r[4 * i]), __uint_as_float(r[4 * i + 1]), __uint_as_float(r[4 * i + 2]),
-                                    __uint_as_float(r[4 * i + 3]));
+                    asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(stage_buf + (uint32_t)(lane * 36 + 4 * i) * 4u), "r"(r[4 * i]),
+                                 "r"(r[4 * i + 1]), "r"(r[4 * i + 2]), "r"(r[4 * i + 3])
+                                 : "memory");
                 __syncwarp();
-                const int grp = n / n_group;
+                const int grp = grp_tile >= 0 ? grp_tile : n / n_group;
                 const long obase = (long)grp * gstride + (n - grp * n_group);
-                const bool full4 = n + 3 < N;
-#pragma unroll
-                for (int it = 0; it < 8; ++it)
-                {
-                    const int row = it * 4 + sub;
-                    const int m = row0 + row;
-                    const float4 t4 = *reinterpret_cast<const float4 *>(stage_buf + row * 36 + c4);
-                    float v[4] = {t4.x, t4.y, t4.z, t4.w};
-                    const float rv = rvv[it];
-#pragma unroll
-                    for (int e = 0; e < 4; ++e)
-                        v[e] = act_apply(fmaf(v[e], al[e], fmaf(rv, ga[e], be[e])), act);
-                    if (m < M && n < N)
-                    {
-                        const long o = obase + (long)m * ldo;
-                        if (of32)
-                        {
-                            if (full4)
-                                *reinterpret_cast<float4 *>(of32 + o) = make_float4(v[0], v[1], v[2], v[3]);
-                            else
-                                for (int e = 0; e < 4; ++e)
-                                    if (n + e < N)
-                                        of32[o + e] = v[e];
-                        }
-                        if (ohi)
-                        {
-                            __half h[4], l[4];
-#pragma unroll
-                            for (int e = 0; e < 4; ++e)
-                                split_half(v[e], h[e], l[e]);
-                            if (full4)
-                            {
-                                *reinterpret_cast<uint2 *>(ohi + o) =
-                                    make_uint2((uint32_t)__half_as_ushort(h[0]) | ((uint32_t)__half_as_ushort(h[1]) << 16),
-                                               (uint32_t)__half_as_ushort(h[2]) | ((uint32_t)__half_as_ushort(h[3]) << 16));
-                                *reinterpret_cast<uint2 *>(olo + o) =
-                                    make_uint2((uint32_t)__half_as_ushort(l[0]) | ((uint32_t)__half_as_ushort(l[1]) << 16),
-                                               (uint32_t)__half_as_ushort(l[2]) | ((uint32_t)__half_as_ushort(l[3]) << 16));
-                            }
-                            else
-                                for (int e = 0; e < 4; ++e)
-                                    if (n + e < N)
-                                    {
-                                        ohi[o + e] = h[e];
-                                        olo[o + e] = l[e];
-                                    }
-                        }
-                    }
-                }
+                const EpiRows er{stage_buf, sub, c4, row0, M, N, n, ldo, obase, of32, ohi, olo};
+                // one specialised, branch-free row loop per epilogue the pipeline uses; anything else takes the generic one
+                if (of32 && !ohi && act == kActNone && rowvec)
+                    epi_rows<kActNone, true, true, false>(er, al, be, ga, rvv);  // W_ih: exact-integer GEMM + rank-1 term
+                else if (of32 && !ohi && act == kActRelu && !rowvec)
+                    epi_rows<kActRelu, false, true, false>(er, al, be, ga, rvv); // fc3
+                else if (!of32 && ohi && act == kActTanh && !rowvec)
+                    epi_rows<kActTanh, false, false, true>(er, al, be, ga, rvv); // fc1
+                else if (!of32 && ohi && act == kActRelu && !rowvec)
+                    epi_rows<kActRelu, false, false, true>(er, al, be, ga, rvv); // fc2
+                else
+                    epi_rows<-1, true, true, true>(er, al, be, ga, rvv, act, rowvec != nullptr);
                 __syncwarp();
             }
             if (++acc == 2)
