@@ -38,8 +38,10 @@ struct Cfg
     static constexpr int kStageBytes = nA * kAPlane + nB * kBPlane;
     static constexpr int kStages = TERMS == 2 ? 6 : 4;
 };
-constexpr int kEpiWarps = 4;
-constexpr int kEpiBytesPerWarp = 32 * 36 * 4; // 32 rows x (32 + 4 pad) floats
+constexpr int kEpiWarps = 8;  // two per TMEM lane quadrant, each takes one half of the tile's columns
+constexpr int kEpiPitch = 20; // floats per row of the transpose tile: 16 columns + 4 pad
+constexpr int kEpiBytesPerWarp = 32 * kEpiPitch * 4;
+constexpr int kEpiChunks = BN / 2 / 16; // 16-column chunks per epilogue warp and tile
 constexpr int kMaxStages = 6;
 constexpr int kSmemBytes = 4 * 49152 + kEpiWarps * kEpiBytesPerWarp + 256 + 1024; // stages + epilogue + barriers + align slack
 constexpr int kThreads = 32 * (2 + kEpiWarps);
@@ -86,8 +88,8 @@ __device__ __forceinline__ uint64_t smem_desc_sw64(uint32_t smem_addr)
            ((uint64_t)4 << 61);
 }
 
-// The rows of one 32-column chunk after the transpose through shared memory: lane (sub, c4) owns columns
-// [c4, c4 + 4) of the rows 4 it + sub.  ACT < 0: activation / outputs / rank-1 term decided at run time.
+// The rows of one 16-column chunk after the transpose through shared memory: lane (sub, c4) owns columns
+// [c4, c4 + 4) of the rows 8 it + sub.  ACT < 0: activation / outputs / rank-1 term decided at run time.
 struct EpiRows
 {
     uint32_t stage_buf;
@@ -99,18 +101,18 @@ struct EpiRows
 };
 template <int ACT, bool RV, bool F32, bool HALF>
 __device__ __forceinline__ void epi_rows(const EpiRows &e, const float (&al)[4], const float (&be)[4], const float (&ga)[4],
-                                         const float (&rvv)[8], int act_rt = 0, bool rv_rt = true)
+                                         const float (&rvv)[4], int act_rt = 0, bool rv_rt = true)
 {
     const bool full4 = e.n + 3 < e.N;
 #pragma unroll
-    for (int it = 0; it < 8; ++it)
+    for (int it = 0; it < 4; ++it)
     {
-        const int row = it * 4 + e.sub;
+        const int row = it * 8 + e.sub;
         const int m = e.row0 + row;
         float v[4];
         asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];"
                      : "=f"(v[0]), "=f"(v[1]), "=f"(v[2]), "=f"(v[3])
-                     : "r"(e.stage_buf + (uint32_t)(row * 36 + e.c4) * 4u)
+                     : "r"(e.stage_buf + (uint32_t)(row * kEpiPitch + e.c4) * 4u)
                      : "memory");
 #pragma unroll
         for (int c = 0; c < 4; ++c)
@@ -248,7 +250,6 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_tc_kernel(const __grid_const
         // ================= MMA issuer =================
         if (lane == 0)
         {
-            constexpr uint32_t idesc = idesc_f16_f32acc(BM, BN);
             int stage = 0;
             uint32_t phase = 0;
             int acc = 0;
@@ -258,6 +259,8 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_tc_kernel(const __grid_const
                 int pi, m0, n0;
                 locate(tile, pi, m0, n0);
                 const int kiters = (P.p[pi].K + BK - 1) / BK;
+                // a ragged last column tile only pays for the columns it has (N of the MMA in steps of 16)
+                const uint32_t idesc = idesc_f16_f32acc(BM, min(BN, (P.p[pi].N - n0 + 15) & ~15));
                 mbar_wait(tempty0 + 8 * acc, acc_phase ^ 1); // epilogue has drained this accumulator
                 tc_fence_after();
                 const uint32_t d_tmem = tmem_base + acc * BN;
@@ -297,14 +300,14 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_tc_kernel(const __grid_const
     else
     {
         // ================= epilogue =================
-        // TMEM lane = output row.  Each 32-column chunk is transposed through a per-warp SMEM tile with
-        // 128-bit accesses (row pitch 36 floats: conflict-free), so that 8 lanes cover one row's 32 columns
-        // and every global store instruction writes four full 128-byte lines.
-        const int q = warp & 3; // TMEM lane quadrant this warp may read
+        // TMEM lane = output row.  Each 16-column chunk is transposed through a per-warp SMEM tile with
+        // 128-bit accesses, so that 4 lanes cover one row's 16 columns and a store instruction writes 8 rows x 64 bytes.
+        const int q = warp & 3;           // TMEM lane quadrant this warp may read
+        const int part = (warp - 2) >> 2; // which half of the tile's columns
         // shared-window address of this warp's transpose tile (explicit ld/st.shared: a generic pointer costs the
         // long-latency generic path on every access)
         const uint32_t stage_buf = smem_u32(epi_base + (warp - 2) * kEpiBytesPerWarp);
-        const int sub = lane >> 3, c4 = (lane & 7) * 4;
+        const int sub = lane >> 2, c4 = (lane & 3) * 4;
         int acc = 0;
         uint32_t acc_phase = 0;
         for (int tile = blockIdx.x; tile < P.total_tiles; tile += gridDim.x)
@@ -323,20 +326,20 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_tc_kernel(const __grid_const
             __half *__restrict__ olo = P.p[pi].out_lo;
             const int row0 = m0 + 32 * q;
             // the rank-1 term's row factors of this thread's 8 rows: loaded once per tile, before waiting for the MMAs
-            float rvv[8];
+            float rvv[4];
 #pragma unroll
-            for (int it = 0; it < 8; ++it)
-                rvv[it] = (rowvec && row0 + it * 4 + sub < M) ? __ldg(rowvec + row0 + it * 4 + sub) : 0.f;
+            for (int it = 0; it < 4; ++it)
+                rvv[it] = (rowvec && row0 + it * 8 + sub < M) ? __ldg(rowvec + row0 + it * 8 + sub) : 0.f;
             // a tile lies inside one output group when the groups are whole tiles (or there is only one)
             const int grp_tile = n_group >= N ? 0 : (n_group % BN == 0 ? n0 / n_group : -1);
             mbar_wait(tfull0 + 8 * acc, acc_phase);
             tc_fence_after();
-            const uint32_t taddr = tmem_base + acc * BN + ((uint32_t)(32 * q) << 16);
+            const uint32_t taddr = tmem_base + acc * BN + part * (BN / 2) + ((uint32_t)(32 * q) << 16);
 #pragma unroll 1
-            for (int ch = 0; ch < BN / 32; ++ch)
+            for (int ch = 0; ch < kEpiChunks; ++ch)
             {
                 // per-column constants of this chunk: in flight while the accumulators come out of TMEM
-                const int nc0 = n0 + ch * 32;
+                const int nc0 = n0 + part * (BN / 2) + ch * 16;
                 const int n = nc0 + c4;
                 float al[4], be[4], ga[4];
 #pragma unroll
@@ -347,10 +350,10 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_tc_kernel(const __grid_const
                     be[e] = (beta && ok) ? __ldg(beta + n + e) : 0.f;
                     ga[e] = (rowvec && ok) ? __ldg(gamma + n + e) : 0.f;
                 }
-                uint32_t r[32];
-                tmem_ld32(taddr + ch * 32, r);
+                uint32_t r[16];
+                tmem_ld16(taddr + ch * 16, r);
                 tc_wait_ld();
-                if (ch == BN / 32 - 1)
+                if (ch == kEpiChunks - 1)
                 { // everything this warp needs has left TMEM
                     tc_fence_before();
                     __syncwarp();
@@ -360,8 +363,8 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_tc_kernel(const __grid_const
                 if (nc0 >= N)
                     continue;
 #pragma unroll
-                for (int i = 0; i < 8; ++i)
-                    asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(stage_buf + (uint32_t)(lane * 36 + 4 * i) * 4u), "r"(r[4 * i]),
+                for (int i = 0; i < 4; ++i)
+                    asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(stage_buf + (uint32_t)(lane * kEpiPitch + 4 * i) * 4u), "r"(r[4 * i]),
                                  "r"(r[4 * i + 1]), "r"(r[4 * i + 2]), "r"(r[4 * i + 3])
                                  : "memory");
                 __syncwarp();
