@@ -190,6 +190,10 @@ __device__ __forceinline__ float tri_weight(int k, int n_buf)
     return (float)tri / (float)(n_buf / 2);
 }
 
+// cos / sin of k pi / 8
+__device__ constexpr float kCos8[16] = {1.0f, 0.923879533f, 0.707106781f, 0.382683432f, 0.0f, -0.382683432f, -0.707106781f, -0.923879533f, -1.0f, -0.923879533f, -0.707106781f, -0.382683432f, 0.0f, 0.382683432f, 0.707106781f, 0.923879533f};
+__device__ constexpr float kSin8[16] = {0.0f, 0.382683432f, 0.707106781f, 0.923879533f, 1.0f, 0.923879533f, 0.707106781f, 0.382683432f, 0.0f, -0.382683432f, -0.707106781f, -0.923879533f, -1.0f, -0.923879533f, -0.707106781f, -0.382683432f};
+
 __global__ void __launch_bounds__(256, 3) istft_kernel(const float2 *__restrict__ stems, long stem_stride, int F,
                                                     int frames_per_cta, const IstftTrack *__restrict__ tracks,
                                                     int n_buf, int stem_begin)
@@ -213,11 +217,24 @@ __global__ void __launch_bounds__(256, 3) istft_kernel(const float2 *__restrict_
     for (int i = t; i < 4096; i += 256)
         ring[i] = make_float2(0.f, 0.f);
 
+    // interior frames (every sample covered by 4 frames): the window-sum-square of the periodic Hann at hop N/4 is 1.5, so
+    // the scale win[n] / 4096 / (wss + 1e-8) is KS * (1 - cos(theta_t + k pi/8)), n = t + 256 k: two FMAs on this
+    // thread's (cos, sin)(theta_t) instead of a table load per sample (agrees with the table to a few ulp)
+    const float2 tw_t = g_tw[t]; // (cos, -sin)(2 pi t / 4096)
+    constexpr float KS = 0.5f / (4096.0f * (1.5f + 1e-8f));
+
     float2 r[16];
     for (int f = f_first; f < f1; ++f)
     {
         const float2 *yL = base + ((long)trk * F + f) * 2 * kBins;
         const float2 *yR = yL + kBins;
+        if (f + 1 < f1)
+        { // the next frame's 257 lines on their way into L2 while this one is transformed
+            const char *nx = reinterpret_cast<const char *>(yL + 2 * kBins);
+            asm volatile("prefetch.global.L2 [%0];" ::"l"(nx + 128 * t));
+            if (t == 0)
+                asm volatile("prefetch.global.L2 [%0];" ::"l"(nx + 128 * 256));
+        }
 #pragma unroll
         for (int a = 0; a < 16; ++a)
         {
@@ -252,7 +269,9 @@ __global__ void __launch_bounds__(256, 3) istft_kernel(const float2 *__restrict_
             const int n = t + 256 * k;
             float sc;
             if (interior)
-                sc = __ldg(&g_istft_scale[n]);
+            {
+                sc = fmaf(tw_t.x, -KS * kCos8[k], fmaf(tw_t.y, -KS * kSin8[k], KS)); // KS (1 - (cos t cos k - sin t sin k)), tw_t.y = -sin
+            }
             else
                 sc = __ldg(&g_win[n]) * (1.0f / (float)kNfft) / (wss_at(f, n, F, g_win) + 1e-8f);
             const float cL = r[k].x * sc;
