@@ -46,6 +46,14 @@ ALGO = {
 }
 
 
+# dram__bytes_read.sum + dram__bytes_write.sum per launch of the stage's kernels, from ncu captures of one 32-track
+# segment batch (profiles/r01_ncu_gemm_launch_metrics.csv: fc1, 3 x W_ih, fc2, fc3; profiles/r01_ncu_full_*.txt)
+TRAFFIC_32 = {
+    "gemm": (4.26e9 + 3 * 6.84e9 + 4.10e9 + 6.97e9) / 6,  # algorithmic: 2.33, 6.77, 4.06, 6.78 GB
+    "istft": 16.4e9,                                       # algorithmic 13.6 GB (spectra in, accumulators read+written)
+}
+
+
 def peaks():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(p):
@@ -265,7 +273,8 @@ def main():
         if top:
             r = per_stage[top]
             roofline = {"kernel": top, "bound": r["bound"], "achieved": r["achieved"], "peak": r["peak"], "unit": r["unit"],
-                        "frac": r["frac"], "traffic": None, "peak_source": pk["src"],
+                        "frac": r["frac"], "traffic": TRAFFIC_32.get(top) if T == 32 else None,
+                        "traffic_unit": "DRAM bytes per launch (ncu, 32-track segment batch; see profiles/)", "peak_source": pk["src"],
                         "share_of_step": r["ms_per_step"] / ms}
         out = {
             "metric": "audio-sec demixed/sec (UMX-L, 4 stems, 44.1kHz stereo)", "value": value, "unit": "audio-s/s",

@@ -53,7 +53,12 @@ constexpr int kBarOff = kPOff + 4 * kPBuf;
 constexpr int kSmemBytes = kBarOff + 96;
 static_assert(kSmemBytes <= 232448, "dynamic shared memory budget of one CTA exceeded");
 // 8 epilogue warps (one per TMEM lane quadrant and row half), 1 MMA warp, 1 shipper warp and 2 helper warps
-constexpr int kThreads = 32 * 12;
+#ifndef UMX_LSTM_EPI_GROUPS
+#define UMX_LSTM_EPI_GROUPS 1
+#endif
+// epilogue warp groups: each group of 8 warps takes 1 / EW of a half's tracks (16-track halves only)
+__host__ __device__ constexpr int epi_groups(int tp) { return tp == 16 ? UMX_LSTM_EPI_GROUPS : 1; }
+__host__ __device__ constexpr int cluster_threads(int tp) { return 32 * (8 * epi_groups(tp) + 4); }
 constexpr uint32_t kTmemCols = 512; // [0,256): accumulators (half*128 + row half*64), [256,512): W_hh (row half*128 + k/4)
 constexpr uint32_t kTmemA = 256;
 
@@ -228,7 +233,7 @@ __device__ __forceinline__ void publish_digits(float h, uint32_t trk, uint32_t t
 }
 
 template <int TP> // tracks per half: 8 or 16
-__global__ void __cluster_dims__(kC, 1, 1) __launch_bounds__(kThreads, 1) lstm_cluster_kernel(const ClusterArgs P)
+__global__ void __cluster_dims__(kC, 1, 1) __launch_bounds__(cluster_threads(TP), 1) lstm_cluster_kernel(const ClusterArgs P)
 {
     extern __shared__ __align__(1024) uint8_t smem[];
     const LstmLayerArgs &a = P.a;
@@ -241,8 +246,11 @@ __global__ void __cluster_dims__(kC, 1, 1) __launch_bounds__(kThreads, 1) lstm_c
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     static_assert(TP == 8 || TP == 16, "tracks per half");
     constexpr int N = (3 * TP + 15) / 16 * 16; // MMA N: rows TP * digit + track of the h operand, padded to a multiple of 16
-    constexpr int NT = TP / 4;                 // tracks per half and epilogue thread
-    constexpr int NE = 8;                      // epilogue warps; warp NE issues the MMAs, warp NE + 1 ships, NE + 2.. sum
+    constexpr int EW = epi_groups(TP);         // epilogue warp groups
+    constexpr int NT = TP / 4 / EW;            // tracks per half and epilogue thread
+    constexpr int GPD = TP / 8 / EW;           // 8-column groups per digit this thread reads
+    constexpr int NE = 8 * EW;                 // epilogue warps; warp NE issues the MMAs, warp NE + 1 ships, NE + 2.. help
+    constexpr int kThreads = cluster_threads(TP);
     constexpr int kBarCount = 32 * (NE + 1);   // named barrier: the epilogue warps arrive, the shipper waits
     constexpr uint32_t kTileBytes = 64u * N;
     constexpr uint32_t kStepBytes = (kC - 1) * kTileBytes; // the 7 peers' digit tiles
@@ -354,7 +362,7 @@ __global__ void __cluster_dims__(kC, 1, 1) __launch_bounds__(kThreads, 1) lstm_c
         // TMEM lane (= gate row of the MMA) 8*gate + unit' inside each 32-lane quadrant: the 16x256b load shape then
         // hands thread (unit' = lane / 4, cp = lane % 4) all four gates of its unit for the tracks
         // 8 (e / 2) + 2 cp + (e % 2), e < NT, and all three digits: no exchange between lanes is needed.
-        const int qd = warp & 3, hh = warp >> 2, up = lane >> 2, cp = lane & 3;
+        const int qd = warp & 3, hh = (warp >> 2) & 1, jh = warp >> 3, up = lane >> 2, cp = lane & 3;
         const uint32_t kk = (uint32_t)(32 * hh + 8 * qd + up); // hidden unit of this thread inside the CTA
         const int k = kUnits * r + (int)kk;
         const float scale = a.whh_scale[target][dir];
@@ -364,7 +372,7 @@ __global__ void __cluster_dims__(kC, 1, 1) __launch_bounds__(kThreads, 1) lstm_c
         const float *xrow = a.xproj + (long)target * a.xproj_target_stride + (long)dir * 4 * kHhC + 4 * k; // 4 gates of unit k
         const long trk_x = (long)F * ldx; // floats between tracks in xproj
         const long st_base = ((long)target * 2 + dir) * kHhC + k;
-        auto trk_of = [&](int e) { return 8 * (e >> 1) + 2 * cp + (e & 1); };
+        auto trk_of = [&](int e) { return 8 * ((jh * NT + e) >> 1) + 2 * cp + (e & 1); }; // NT is even
 
         // After an epilogue thread has written its digits of a half: make them visible to the async proxy and
         // ARRIVE (non-blocking) on the half's named barrier; the shipper warp waits there and ships the tile.
@@ -431,15 +439,21 @@ __global__ void __cluster_dims__(kC, 1, 1) __launch_bounds__(kThreads, 1) lstm_c
                 UMX_DBG_STAMP(half * 4 + 1);
                 // D[s][.]: 16-lane half s of the quadrant = gates 2s (lanes 0..7) and 2s + 1 (lanes 8..15); column
                 // group j of 8 = digit (8 j) / TP, tracks (8 j) % TP + 2 cp + {0,1}
-                uint32_t D[2][N / 2];
+                uint32_t D[2][16 * GPD];
 #pragma unroll
                 for (int sgh = 0; sgh < 2; ++sgh)
                 {
                     const uint32_t ta = t_lane + ((uint32_t)(16 * sgh) << 16) + (uint32_t)(half * 128 + hh * 64);
-                    if (TP == 16)
+                    if (TP == 16 && EW == 1)
                     {
                         tmem_ld_16x256b_x4(ta, &D[sgh][0]);
                         tmem_ld_16x256b_x2(ta + 32, &D[sgh][16]);
+                    }
+                    else if (TP == 16)
+                    { // this warp group's 8 tracks: group 2 dg + jh of every digit
+#pragma unroll
+                        for (int dg = 0; dg < 3; ++dg)
+                            tmem_ld_16x256b_x1(ta + 8 * (2 * dg + jh), &D[sgh][4 * dg]);
                     }
                     else
                     {
@@ -452,7 +466,7 @@ __global__ void __cluster_dims__(kC, 1, 1) __launch_bounds__(kThreads, 1) lstm_c
                 for (int e2 = 0; e2 < NT / 2; ++e2)
                 {
                     float2 v;
-                    asm volatile("ld.shared.v2.f32 {%0, %1}, [%2];" : "=f"(v.x), "=f"(v.y) : "r"(sS + (uint32_t)(half * 64 + (8 * e2 + 2 * cp) * 4)) : "memory");
+                    asm volatile("ld.shared.v2.f32 {%0, %1}, [%2];" : "=f"(v.x), "=f"(v.y) : "r"(sS + (uint32_t)(half * 64 + (8 * (jh * (NT / 2) + e2) + 2 * cp) * 4)) : "memory");
                     os[2 * e2] = v.x;
                     os[2 * e2 + 1] = v.y;
                 }
@@ -461,8 +475,8 @@ __global__ void __cluster_dims__(kC, 1, 1) __launch_bounds__(kThreads, 1) lstm_c
 #pragma unroll
                 for (int e = 0; e < NT; ++e)
                 {
-                    // register of (gate, digit dg) of track e: group j = dg * (TP / 8) + e / 2, element e % 2
-                    auto Dv = [&](int gate, int dg) { return D[gate >> 1][4 * (dg * (TP / 8) + (e >> 1)) + 2 * (gate & 1) + (e & 1)]; };
+                    // register of (gate, digit dg) of track e: loaded group dg * GPD + e / 2, element e % 2
+                    auto Dv = [&](int gate, int dg) { return D[gate >> 1][4 * (dg * GPD + (e >> 1)) + 2 * (gate & 1) + (e & 1)]; };
                     const float xg[4] = {xp[half][e].x, xp[half][e].y, xp[half][e].z, xp[half][e].w};
                     float pre[4];
 #pragma unroll
@@ -709,7 +723,7 @@ int launch_tp(const ClusterArgs &P, int groups, cudaStream_t st)
         attr_set[dev & 63] = true;
     }
     dim3 grid(kC, 2 * P.a.target_count, groups);
-    lstm_cluster_kernel<TP><<<grid, kThreads, kSmemBytes, st>>>(P);
+    lstm_cluster_kernel<TP><<<grid, cluster_threads(TP), kSmemBytes, st>>>(P);
     UMX_CUDA_OK(cudaGetLastError());
 #ifdef UMX_LSTM_TIMING
     if (getenv("UMX_LSTM_DEBUG"))
@@ -752,7 +766,7 @@ int lstm_cluster_max_active()
     int n = 0;
     cudaLaunchConfig_t cfg{};
     cfg.gridDim = dim3(kC, 64, 1);
-    cfg.blockDim = dim3(kThreads);
+    cfg.blockDim = dim3(cluster_threads(16));
     cfg.dynamicSmemBytes = kSmemBytes;
     cudaLaunchAttribute at[1];
     at[0].id = cudaLaunchAttributeClusterDimension;
