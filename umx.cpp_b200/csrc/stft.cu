@@ -330,7 +330,11 @@ __global__ void finalize_kernel(const FinalizeTrack *__restrict__ tracks, int sh
     const long p = i + shift;
     // segments s with s*stride <= p < s*stride + chunk_len(s), added in increasing s
     float sw = 0.f;
-    const long s_hi = p / stride;
+    // one 64-bit division per block (uniform), not per thread: the block's 256 positions span at most two segments' starts
+    const long p0 = tk.i_begin + (long)blockIdx.x * blockDim.x + shift;
+    const long s0 = p0 / stride;
+    const long rem = p - s0 * stride;
+    const long s_hi = rem < stride ? s0 : (rem < 2L * stride ? s0 + 1 : p / stride);
     for (long sgm = (s_hi > 0 ? s_hi - 1 : 0); sgm <= s_hi; ++sgm)
     {
         const long off = sgm * stride;
