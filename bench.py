@@ -170,6 +170,7 @@ def main():
     ap.add_argument("--track-seconds", type=float, default=180.0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--gemm-terms", type=int, default=0)
+    ap.add_argument("--pipeline", type=int, default=-1, help="session option: post stage of segment s on a second stream under the network of s+1")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
@@ -199,6 +200,8 @@ def main():
     sess = umx.Session(model, max_tracks=T, n_buf=SEG)
     if args.gemm_terms:
         sess.set_option("gemm_terms", args.gemm_terms)
+    if args.pipeline >= 0:
+        sess.set_option("pipeline", args.pipeline)
     stream = torch.cuda.current_stream()
     sess.set_stream(stream.cuda_stream)
     sess.set_profiling(True)

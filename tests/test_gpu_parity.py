@@ -192,6 +192,24 @@ def test_demix_multi_segment_multi_track(umx, gemm_impl, terms):
     assert np.abs(again - got[0]).max() < 1e-6
 
 
+@pytest.mark.parametrize("mode", [1, 2])  # 2 is the default
+def test_demix_pipeline_modes_identical(umx, mode):
+    """Session option "pipeline": the post stage on a second stream (1) or in slots under the next segment's
+    recurrences (2) must give bit-identical stems to the in-order schedule, through host and device paths."""
+    hidden, n_buf = 64, 16384
+    gm = umx.load_umx_model(synth.make_ggml(hidden=hidden, seed=78))
+    tracks = [synth.make_audio(n, 30 + i) for i, n in enumerate((70000, 41000, 9000))]
+    ref_sess = umx.Session(gm, 3, n_buf)
+    ref_sess.set_option("pipeline", 0)
+    want = ref_sess.demix(tracks, shift_offset=4033)
+    sess = umx.Session(gm, 3, n_buf)
+    sess.set_option("pipeline", mode)
+    for _ in range(2):
+        got = sess.demix(tracks, shift_offset=4033)
+        for g, w in zip(got, want):
+            assert np.array_equal(g, w)
+
+
 def test_demix_shift_offsets_and_trim(umx, small):
     gm, om = small
     n_buf = 8192

@@ -292,7 +292,7 @@ int umx_cuda_session_set_option(umx_cuda_session *s, const char *name, int value
     }
     else if (n == "pipeline")
     {
-        UMX_CHECK(value == 0 || value == 1, "pipeline must be 0 or 1");
+        UMX_CHECK(value >= 0 && value <= 2, "pipeline must be 0, 1 or 2");
         s->s->pipeline = value;
     }
     else if (n == "lstm_impl")

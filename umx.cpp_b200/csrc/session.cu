@@ -222,6 +222,54 @@ static int run_gemm(Session *s, const GemmBatch &b, int terms = 0)
     return launch_gemm_tc(b, terms ? terms : s->gemm_terms, s->st);
 }
 
+static cudaEvent_t take_event(Session *s, size_t &cursor)
+{
+    if (cursor == s->ev_pool.size())
+    {
+        cudaEvent_t e;
+        cudaEventCreateWithFlags(&e, cudaEventDisableTiming);
+        s->ev_pool.push_back(e);
+    }
+    return s->ev_pool[cursor++];
+}
+
+static int session_back_part(Session *s, int seg, int n_tracks, int part);
+
+// One part of the deferred post stage (option "pipeline" = 2) on st_post, starting when the main stream reaches this point.
+static int slot_run_next(Session *s)
+{
+    Session::SlotJob &j = s->slot;
+    if (j.seg < 0 || j.next > 2)
+        return 0;
+    cudaEvent_t e = take_event(s, s->ev_cursor);
+    UMX_CUDA_OK(cudaEventRecord(e, s->st));
+    UMX_CUDA_OK(cudaStreamWaitEvent(s->st_post, e, 0));
+    cudaStream_t keep_st = s->st;
+    float2 *keep_spec = s->spec;
+    float *keep_mask = s->mask, *keep_maxabs = s->maxabs;
+    s->st = s->st_post;
+    s->spec = j.spec;
+    s->mask = j.mask;
+    s->maxabs = j.maxabs;
+    int rc = session_back_part(s, j.seg, j.n_tracks, j.next);
+    if (!rc && j.next == 2)
+    {
+        {
+            StageScope sc(s, "finalize");
+            s->launches++;
+            rc = launch_finalize(j.fin, j.n_tracks, j.max_range, j.shift, s->n_buf, j.stride, s->tp_nt, s->st, s->tp_t0);
+        }
+        if (!rc && cudaEventRecord(j.done, s->st) != cudaSuccess)
+            rc = -1;
+    }
+    s->st = keep_st;
+    s->spec = keep_spec;
+    s->mask = keep_mask;
+    s->maxabs = keep_maxabs;
+    ++j.next;
+    return rc;
+}
+
 int session_lstm(Session *s, int n_tracks, int target_begin, int target_count, bool want_f32)
 {
     const int H = s->H, Hh = s->Hh;
@@ -262,6 +310,8 @@ int session_lstm(Session *s, int n_tracks, int target_begin, int target_count, b
             if (int rc = run_gemm(s, b, std::min(s->gemm_terms, 2))) // no weight lo plane: at most hi*q + lo*q
                 return rc;
         }
+        if (int rc = slot_run_next(s)) // a part of the previous segment's post stage shares the GPU with this recurrence
+            return rc;
         StageScope sc(s, "lstm");
         LstmLayerArgs a{};
         for (int t = 0; t < kTargets; ++t)
@@ -414,9 +464,11 @@ int session_front(Session *s, int seg, int n_tracks)
     return 0;
 }
 
-int session_back(Session *s, int seg, int n_tracks)
+// part 0: Wiener-EM; parts 1 and 2: iSTFT + overlap-add of the first / second half of this rank's stems
+static int session_back_part(Session *s, int seg, int n_tracks, int part)
 {
     const IstftTrack *dis = s->d_istft + (size_t)seg * s->T;
+    if (part == 0)
     {
         StageScope sc(s, "wiener");
         WienerArgs w{};
@@ -436,15 +488,22 @@ int session_back(Session *s, int seg, int n_tracks)
         w.stem_begin = s->tp_t0;
         w.stem_count = s->tp_nt;
         s->launches += 3;
-        if (int rc = launch_wiener(w, s->st))
-            return rc;
+        return launch_wiener(w, s->st);
     }
-    {
-        StageScope sc(s, "istft");
-        s->launches++;
-        if (int rc = launch_istft(s->stems, s->Mcap * 2 * kBins, s->tp_nt, dis, n_tracks, s->n_buf, s->st, s->tp_t0))
+    const int n1 = (s->tp_nt + 1) / 2;
+    const int begin = part == 1 ? s->tp_t0 : s->tp_t0 + n1, count = part == 1 ? n1 : s->tp_nt - n1;
+    if (count <= 0)
+        return 0;
+    StageScope sc(s, "istft");
+    s->launches++;
+    return launch_istft(s->stems, s->Mcap * 2 * kBins, count, dis, n_tracks, s->n_buf, s->st, begin);
+}
+
+int session_back(Session *s, int seg, int n_tracks)
+{
+    for (int part = 0; part < 3; ++part)
+        if (int rc = session_back_part(s, seg, n_tracks, part))
             return rc;
-    }
     return 0;
 }
 
@@ -497,17 +556,6 @@ int session_infer_segment(Session *s, const float *audio, int n, float *out)
 
 // ---- shift_inference + split_inference (umx.cpp:99-295) ------------------------------------------------
 static int stride_of(int n_buf) { return (int)((1 - 0.25f) * n_buf); } // umx.cpp:180
-
-static cudaEvent_t take_event(Session *s, size_t &cursor)
-{
-    if (cursor == s->ev_pool.size())
-    {
-        cudaEvent_t e;
-        cudaEventCreateWithFlags(&e, cudaEventDisableTiming);
-        s->ev_pool.push_back(e);
-    }
-    return s->ev_pool[cursor++];
-}
 
 int session_demix_device(Session *s, const float *const *d_audio, const int64_t *n_samples, int n_tracks,
                          int shift_offset, float *const *d_out, const float *const *host_in, float *const *host_out)
@@ -562,9 +610,12 @@ int session_demix_device(Session *s, const float *const *d_audio, const int64_t 
     UMX_CUDA_OK(cudaMemcpyAsync(s->d_final, hf.data(), sizeof(FinalizeTrack) * hf.size(), cudaMemcpyHostToDevice, s->st));
     UMX_CUDA_OK(cudaStreamSynchronize(s->st)); // hs/hi/hf are pageable host vectors
 
-    size_t ev = 0;
+    size_t &ev = s->ev_cursor;
+    ev = 0;
+    s->slot = Session::SlotJob{};
     std::vector<long> copied_in(n_tracks, 0);
     const bool pipelined = s->pipeline != 0 && max_segs > 1;
+    const bool slotted = s->pipeline == 2 && max_segs > 1;
     cudaStream_t main_st = s->st;
     std::vector<cudaEvent_t> back_done(max_segs);
     if (pipelined)
@@ -573,6 +624,23 @@ int session_demix_device(Session *s, const float *const *d_audio, const int64_t 
         UMX_CUDA_OK(cudaEventRecord(e, main_st));
         UMX_CUDA_OK(cudaStreamWaitEvent(s->st_post, e, 0));
     }
+    // ship the finished range of every stem of a segment (after its finalize) while later segments compute
+    auto ship_out = [&](int seg) -> int {
+        UMX_CUDA_OK(cudaStreamWaitEvent(s->st_out, back_done[seg], 0));
+        for (int i = 0; i < n_tracks; ++i)
+        {
+            const FinalizeTrack &f = hf[(size_t)seg * s->T + i];
+            if (f.i_end <= f.i_begin)
+                continue;
+            for (int stem = s->tp_t0; stem < s->tp_t0 + s->tp_nt; ++stem)
+            {
+                const size_t o = 2 * ((size_t)stem * n_samples[i] + f.i_begin);
+                UMX_CUDA_OK(cudaMemcpyAsync(host_out[i] + o, d_out[i] + o, sizeof(float2) * (size_t)(f.i_end - f.i_begin),
+                                            cudaMemcpyDeviceToHost, s->st_out));
+            }
+        }
+        return 0;
+    };
     for (int sg = 0; sg < max_segs; ++sg) // sequential: h/c stream from segment to segment
     {
         if (host_in)
@@ -601,6 +669,34 @@ int session_demix_device(Session *s, const float *const *d_audio, const int64_t 
             UMX_CUDA_OK(cudaStreamWaitEvent(main_st, back_done[sg - 2], 0)); // buffer b is free again
         if (int rc = session_front(s, sg, n_tracks))
             return rc;
+        if (slotted)
+        {
+            // whatever is left of the previous segment's post stage (all of it was started under this segment's recurrences
+            // unless the network has fewer than three of them), then its finished ranges can leave for the host
+            while (s->slot.seg >= 0 && s->slot.next <= 2)
+                if (int rc = slot_run_next(s))
+                    return rc;
+            if (s->slot.seg >= 0 && host_out)
+                if (int rc = ship_out(s->slot.seg))
+                    return rc;
+            s->slot = Session::SlotJob{};
+            back_done[sg] = take_event(s, ev);
+            if (sg + 1 < max_segs)
+            { // defer this segment's post stage: its parts start with the recurrences of segment sg + 1
+                s->slot.seg = sg;
+                s->slot.n_tracks = n_tracks;
+                s->slot.next = 0;
+                s->slot.fin = s->d_final + (size_t)sg * s->T;
+                s->slot.max_range = max_range[sg];
+                s->slot.shift = shift_offset;
+                s->slot.stride = stride;
+                s->slot.spec = s->spec;
+                s->slot.mask = s->mask;
+                s->slot.maxabs = s->maxabs;
+                s->slot.done = back_done[sg];
+                continue;
+            }
+        }
         if (pipelined)
         {
             cudaEvent_t e = take_event(s, ev);
@@ -619,24 +715,12 @@ int session_demix_device(Session *s, const float *const *d_audio, const int64_t 
         s->st = main_st;
         if (rc_back)
             return rc_back;
-        back_done[sg] = take_event(s, ev);
+        if (!slotted)
+            back_done[sg] = take_event(s, ev);
         UMX_CUDA_OK(cudaEventRecord(back_done[sg], back_st));
         if (host_out)
-        { // ship the finished range of every stem while the next segment computes
-            UMX_CUDA_OK(cudaStreamWaitEvent(s->st_out, back_done[sg], 0));
-            for (int i = 0; i < n_tracks; ++i)
-            {
-                const FinalizeTrack &f = hf[(size_t)sg * s->T + i];
-                if (f.i_end <= f.i_begin)
-                    continue;
-                for (int stem = s->tp_t0; stem < s->tp_t0 + s->tp_nt; ++stem)
-                {
-                    const size_t o = 2 * ((size_t)stem * n_samples[i] + f.i_begin);
-                    UMX_CUDA_OK(cudaMemcpyAsync(host_out[i] + o, d_out[i] + o, sizeof(float2) * (size_t)(f.i_end - f.i_begin),
-                                                cudaMemcpyDeviceToHost, s->st_out));
-                }
-            }
-        }
+            if (int rc = ship_out(sg))
+                return rc;
     }
     if (pipelined) // completion of the caller-visible stream implies completion of the post stage
         UMX_CUDA_OK(cudaStreamWaitEvent(main_st, back_done[max_segs - 1], 0));

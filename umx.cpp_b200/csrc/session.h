@@ -52,8 +52,21 @@ struct Session
     cudaStream_t st_post = nullptr;                 // Wiener/iSTFT/finalize of segment s run here while segment s+1's network runs on st
     float2 *spec_buf[2] = {};                       // spec / mask / maxabs are double-buffered between the two stages
     float *mask_buf[2] = {}, *maxabs_buf[2] = {};
-    int pipeline = 0;                               // option "pipeline": 1 = post stage on its own low-priority stream (measured: no gain, the GPU is power-capped)
+    int pipeline = 2;                               // option "pipeline": 0 = in order, 1 = post stage on its own low-priority stream, 2 (default) = in slots under the next segment's recurrences
     std::vector<cudaEvent_t> ev_pool;
+    size_t ev_cursor = 0;
+    // option "pipeline" = 2: the post stage (Wiener, iSTFT, finalize) of segment s is cut into three parts that start together
+    // with the three recurrence kernels of segment s+1 (which occupy 64 of the 148 SMs) on st_post
+    struct SlotJob
+    {
+        int seg = -1, n_tracks = 0, next = 0;
+        const FinalizeTrack *fin = nullptr;
+        long max_range = 0;
+        int shift = 0, stride = 0;
+        float2 *spec = nullptr;
+        float *mask = nullptr, *maxabs = nullptr;
+        cudaEvent_t done = nullptr;
+    } slot;
 
     // grow-only pools for whole-track demixing
     std::vector<float2 *> acc_pool, in_pool, out_pool;
