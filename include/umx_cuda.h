@@ -140,7 +140,9 @@ int umx_cuda_session_set_stream(umx_cuda_session *s, void *stream);
 /* How many 8-CTA clusters of the recurrence kernel the current device can hold at once (diagnostic). */
 int umx_cuda_lstm_max_active_clusters(void);
 /* Tuning knobs (documented in DESIGN.md): "gemm_terms" 1..3 fp16 split terms per tensor-core GEMM,
- * "gemm_impl" 0 = tcgen05, 1 = SIMT fp32 validation kernel, "lstm_impl" 0 = cluster kernel, 1 = simple. */
+ * "gemm_impl" 0 = tcgen05, 1 = SIMT fp32 validation kernel, "lstm_impl" 0 = cluster kernel, 1 = simple,
+ * "pipeline" 0 = every segment in order on one stream, 1 = Wiener/iSTFT/finalize of a segment on a second stream,
+ * 2 (default) = the same in three parts that start with the next segment's recurrence kernels; results are identical. */
 int umx_cuda_session_set_option(umx_cuda_session *s, const char *name, int value);
 
 #ifdef __cplusplus
