@@ -35,9 +35,9 @@ def test_lstm_forward_cluster_vs_oracle_streaming(umx, umxl):
             assert np.abs(h - st.h[l, d]).max() < 2e-5 and np.abs(c - st.c[l, d]).max() < 1e-4
 
 
-@pytest.mark.parametrize("n_tracks", [1, 3, 8, 16, 19])
+@pytest.mark.parametrize("n_tracks", [1, 3, 8, 16, 19, 32, 35])
 def test_demix_cluster_vs_simple_multi_track(umx, umxl, n_tracks):
-    """Whole pipeline, several tracks in lockstep (one cluster handles up to 16, then a second group)."""
+    """Whole pipeline, several tracks in lockstep (a cluster takes up to 32 tracks as two halves, then a second group starts)."""
     gm, _ = umxl
     fast, slow = umx.Session(gm, n_tracks, N_BUF), umx.Session(gm, n_tracks, N_BUF)
     fast.set_option("lstm_impl", 0)

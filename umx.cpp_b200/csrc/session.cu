@@ -613,6 +613,11 @@ int session_demix_device(Session *s, const float *const *d_audio, const int64_t 
     size_t &ev = s->ev_cursor;
     ev = 0;
     s->slot = Session::SlotJob{};
+    struct SlotGuard // no deferred job may outlive this call, whichever way it returns
+    {
+        Session *s;
+        ~SlotGuard() { s->slot = Session::SlotJob{}; }
+    } slot_guard{s};
     std::vector<long> copied_in(n_tracks, 0);
     const bool pipelined = s->pipeline != 0 && max_segs > 1;
     const bool slotted = s->pipeline == 2 && max_segs > 1;
