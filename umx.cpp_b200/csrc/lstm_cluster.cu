@@ -40,25 +40,19 @@ namespace
 constexpr int kC = 8;            // CTAs per cluster
 constexpr int kHhC = 512;        // hidden units per direction this kernel is built for
 constexpr int kUnits = 64;       // units per CTA
-constexpr int kMaxHalf = 16;     // tracks per half
-constexpr int kMaxTracks = 2 * kMaxHalf; // tracks per cluster
+constexpr int kMaxNG = 4;        // at most four ping-pong groups of tracks per cluster
 constexpr int kABytes = 256 * kHhC;               // this CTA's 256 gate rows x 512 k of W_hh, uint8: 128 KB, held in TMEM
 constexpr int kBTile = 48 * 64;                   // one source CTA's tile: up to 48 (track, digit) rows x 64 units
 constexpr int kBBuf = kC * kBTile;                // one (half, parity) h buffer: 24 KB
 constexpr int kBOff = 0;                          // [half 2][parity 2][8 source CTAs][48 rows][64 B], 64-byte swizzle
-constexpr int kSOff = kBOff + 4 * kBBuf;          // offset * sum_k h_k: [half 2][16 tracks] f32
-constexpr int kPOff = kSOff + 2 * 64;             // its per-CTA partial sums: [half 2][parity 2][8 source CTAs][16 tracks] f32
+constexpr int kSOff = kBOff + 2 * kMaxNG * kBBuf;   // offset * sum_k h_k: [group][16 tracks] f32
+constexpr int kPOff = kSOff + kMaxNG * 64;          // its per-CTA partial sums: [group][parity 2][8 source CTAs][16 tracks] f32
 constexpr int kPBuf = kC * 64;
-constexpr int kBarOff = kPOff + 4 * kPBuf;
-constexpr int kSmemBytes = kBarOff + 96;
+constexpr int kBarOff = kPOff + 2 * kMaxNG * kPBuf;
+constexpr int kSmemBytes = kBarOff + 256;
 static_assert(kSmemBytes <= 232448, "dynamic shared memory budget of one CTA exceeded");
 // 8 epilogue warps (one per TMEM lane quadrant and row half), 1 MMA warp, 1 shipper warp and 2 helper warps
-#ifndef UMX_LSTM_EPI_GROUPS
-#define UMX_LSTM_EPI_GROUPS 1
-#endif
-// epilogue warp groups: each group of 8 warps takes 1 / EW of a half's tracks (16-track halves only)
-__host__ __device__ constexpr int epi_groups(int tp) { return tp == 16 ? UMX_LSTM_EPI_GROUPS : 1; }
-__host__ __device__ constexpr int cluster_threads(int tp) { return 32 * (8 * epi_groups(tp) + 4); }
+constexpr int kThreads = 32 * 12; // 8 epilogue warps, MMA warp, shipper warp, 2 helper warps
 constexpr uint32_t kTmemCols = 512; // [0,256): accumulators (half*128 + row half*64), [256,512): W_hh (row half*128 + k/4)
 constexpr uint32_t kTmemA = 256;
 
@@ -232,25 +226,25 @@ __device__ __forceinline__ void publish_digits(float h, uint32_t trk, uint32_t t
     }
 }
 
-template <int TP> // tracks per half: 8 or 16
-__global__ void __cluster_dims__(kC, 1, 1) __launch_bounds__(cluster_threads(TP), 1) lstm_cluster_kernel(const ClusterArgs P)
+template <int TP, int NG> // tracks per ping-pong group (8 or 16), groups per cluster (2 or 4)
+__global__ void __cluster_dims__(kC, 1, 1) __launch_bounds__(kThreads, 1) lstm_cluster_kernel(const ClusterArgs P)
 {
     extern __shared__ __align__(1024) uint8_t smem[];
     const LstmLayerArgs &a = P.a;
     const int r = blockIdx.x; // rank in cluster (cluster spans x)
     const int target = a.target_begin + blockIdx.y / 2;
     const int dir = blockIdx.y & 1;
-    const int trk0 = blockIdx.z * kMaxTracks;
-    const int n_group = min(2 * TP, a.n_tracks - trk0); // tracks of this cluster
-    const int n_halves = n_group > TP ? 2 : 1;
+    static_assert(NG == 2 || NG == 4, "ping-pong groups");
+    static_assert(NG * ((3 * TP + 15) / 16 * 16) * 2 <= 256, "accumulator columns");
+    const int trk0 = blockIdx.z * (NG * TP);
+    const int n_group = min(NG * TP, a.n_tracks - trk0); // tracks of this cluster
+    const int n_halves = (n_group + TP - 1) / TP;       // ping-pong groups in use ("halves": there were two of them at first)
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     static_assert(TP == 8 || TP == 16, "tracks per half");
     constexpr int N = (3 * TP + 15) / 16 * 16; // MMA N: rows TP * digit + track of the h operand, padded to a multiple of 16
-    constexpr int EW = epi_groups(TP);         // epilogue warp groups
-    constexpr int NT = TP / 4 / EW;            // tracks per half and epilogue thread
-    constexpr int GPD = TP / 8 / EW;           // 8-column groups per digit this thread reads
-    constexpr int NE = 8 * EW;                 // epilogue warps; warp NE issues the MMAs, warp NE + 1 ships, NE + 2.. help
-    constexpr int kThreads = cluster_threads(TP);
+    constexpr int NT = TP / 4;                 // tracks per group and epilogue thread
+    constexpr int GPD = TP / 8;                // 8-column groups per digit
+    constexpr int NE = 8;                      // epilogue warps; warp NE issues the MMAs, warp NE + 1 ships, NE + 2.. help
     constexpr int kBarCount = 32 * (NE + 1);   // named barrier: the epilogue warps arrive, the shipper waits
     constexpr uint32_t kTileBytes = 64u * N;
     constexpr uint32_t kStepBytes = (kC - 1) * kTileBytes; // the 7 peers' digit tiles
@@ -259,9 +253,10 @@ __global__ void __cluster_dims__(kC, 1, 1) __launch_bounds__(cluster_threads(TP)
         __trap(); // the swizzled operand tiles need the 1024-byte alignment requested above
 
     uint64_t *bars = reinterpret_cast<uint64_t *>(smem + kBarOff);
-    // hfull[half][parity] (4), mma_done[half] (2), sfull[half][parity] (4), then the TMEM base address
-    const uint32_t hfull0 = smem_u32(bars), mma_done0 = smem_u32(bars + 4), sfull0 = smem_u32(bars + 6);
-    uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + 10);
+    // hfull[half][parity] (2 NG), mma_done[half] (NG), sfull[half][parity] (2 NG), then the TMEM base address
+    const uint32_t hfull0 = smem_u32(bars), mma_done0 = smem_u32(bars + 2 * NG), sfull0 = smem_u32(bars + 3 * NG);
+    uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + 5 * NG);
+    constexpr uint32_t kDCols = 256 / NG; // accumulator columns of one group: row half h2 at + kDCols / 2
     const uint32_t sB = smem_u32(smem) + kBOff, sS = smem_u32(smem) + kSOff, sP = smem_u32(smem) + kPOff;
 
     // ---- one-time setup: zeroed h buffers, barriers, TMEM, weights into TMEM ----
@@ -272,11 +267,11 @@ __global__ void __cluster_dims__(kC, 1, 1) __launch_bounds__(cluster_threads(TP)
     }
     if (threadIdx.x == 0)
     {
-        for (int i = 0; i < 4; ++i)
+        for (int i = 0; i < 2 * NG; ++i)
             mbar_init(hfull0 + 8 * i, 2); // MMA warp (expect_tx of the peers' bytes) + this CTA's own shipper
-        mbar_init(mma_done0, 2);          // tcgen05.commit of the MMAs + the sum warp once the offset terms are written
-        mbar_init(mma_done0 + 8, 2);
-        for (int i = 0; i < 4; ++i)
+        for (int i = 0; i < NG; ++i)
+            mbar_init(mma_done0 + 8 * i, 2); // tcgen05.commit of the MMAs + the sum warp once the offset terms are written
+        for (int i = 0; i < 2 * NG; ++i)
             mbar_init(sfull0 + 8 * i, 2); // sum warp (expect_tx of the peers' partial sums) + this CTA's own shipper
         fence_barrier_init();
     }
@@ -362,7 +357,7 @@ __global__ void __cluster_dims__(kC, 1, 1) __launch_bounds__(cluster_threads(TP)
         // TMEM lane (= gate row of the MMA) 8*gate + unit' inside each 32-lane quadrant: the 16x256b load shape then
         // hands thread (unit' = lane / 4, cp = lane % 4) all four gates of its unit for the tracks
         // 8 (e / 2) + 2 cp + (e % 2), e < NT, and all three digits: no exchange between lanes is needed.
-        const int qd = warp & 3, hh = (warp >> 2) & 1, jh = warp >> 3, up = lane >> 2, cp = lane & 3;
+        const int qd = warp & 3, hh = warp >> 2, up = lane >> 2, cp = lane & 3;
         const uint32_t kk = (uint32_t)(32 * hh + 8 * qd + up); // hidden unit of this thread inside the CTA
         const int k = kUnits * r + (int)kk;
         const float scale = a.whh_scale[target][dir];
@@ -372,16 +367,13 @@ __global__ void __cluster_dims__(kC, 1, 1) __launch_bounds__(cluster_threads(TP)
         const float *xrow = a.xproj + (long)target * a.xproj_target_stride + (long)dir * 4 * kHhC + 4 * k; // 4 gates of unit k
         const long trk_x = (long)F * ldx; // floats between tracks in xproj
         const long st_base = ((long)target * 2 + dir) * kHhC + k;
-        auto trk_of = [&](int e) { return 8 * ((jh * NT + e) >> 1) + 2 * cp + (e & 1); }; // NT is even
+        auto trk_of = [&](int e) { return 8 * (e >> 1) + 2 * cp + (e & 1); };
 
         // After an epilogue thread has written its digits of a half: make them visible to the async proxy and
         // ARRIVE (non-blocking) on the half's named barrier; the shipper warp waits there and ships the tile.
         auto publish_tile = [&](int half) {
             asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-            if (half == 0)
-                asm volatile("bar.arrive 1, %0;" ::"n"(kBarCount) : "memory");
-            else
-                asm volatile("bar.arrive 2, %0;" ::"n"(kBarCount) : "memory");
+            asm volatile("bar.arrive %0, %1;" ::"r"(1 + half), "n"(kBarCount) : "memory");
         };
         // input projection (4 gates) of one step for this thread's tracks of a half
         auto load_xp = [&](float4(&dst)[NT], int tb, int tt) {
@@ -393,10 +385,10 @@ __global__ void __cluster_dims__(kC, 1, 1) __launch_bounds__(cluster_threads(TP)
             }
         };
 
-        float c[2][NT], hlast[2][NT];
-        float4 xp[2][NT];
+        float c[NG][NT], hlast[NG][NT];
+        float4 xp[NG][NT];
 #pragma unroll
-        for (int half = 0; half < 2; ++half)
+        for (int half = 0; half < NG; ++half)
         {
             if (half >= n_halves)
                 break;
@@ -422,7 +414,7 @@ __global__ void __cluster_dims__(kC, 1, 1) __launch_bounds__(cluster_threads(TP)
             const int tn = dir == 0 ? min(step + 1, F - 1) : max(F - 2 - step, 0);
             const uint32_t pn = (uint32_t)(step & 1) ^ 1u;
 #pragma unroll
-            for (int half = 0; half < 2; ++half)
+            for (int half = 0; half < NG; ++half)
             {
                 if (half >= n_halves)
                     break;
@@ -430,7 +422,7 @@ __global__ void __cluster_dims__(kC, 1, 1) __launch_bounds__(cluster_threads(TP)
                 const uint32_t tile_out = sB + ((uint32_t)(half * 2) + pn) * kBBuf + (uint32_t)r * kBTile;
 
 #ifdef UMX_LSTM_TIMING
-                const bool dbg = (step == 200 && threadIdx.x == 0 && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0);
+                const bool dbg = (half < 2 && step == 200 && threadIdx.x == 0 && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0);
 #endif
                 UMX_DBG_STAMP(half * 4 + 0);
                 // MMAs of this half-step complete, and offset * sum_k h_k per track written by the sum warps
@@ -443,17 +435,11 @@ __global__ void __cluster_dims__(kC, 1, 1) __launch_bounds__(cluster_threads(TP)
 #pragma unroll
                 for (int sgh = 0; sgh < 2; ++sgh)
                 {
-                    const uint32_t ta = t_lane + ((uint32_t)(16 * sgh) << 16) + (uint32_t)(half * 128 + hh * 64);
-                    if (TP == 16 && EW == 1)
+                    const uint32_t ta = t_lane + ((uint32_t)(16 * sgh) << 16) + (uint32_t)half * kDCols + (uint32_t)hh * (kDCols / 2);
+                    if (TP == 16)
                     {
                         tmem_ld_16x256b_x4(ta, &D[sgh][0]);
                         tmem_ld_16x256b_x2(ta + 32, &D[sgh][16]);
-                    }
-                    else if (TP == 16)
-                    { // this warp group's 8 tracks: group 2 dg + jh of every digit
-#pragma unroll
-                        for (int dg = 0; dg < 3; ++dg)
-                            tmem_ld_16x256b_x1(ta + 8 * (2 * dg + jh), &D[sgh][4 * dg]);
                     }
                     else
                     {
@@ -466,7 +452,7 @@ __global__ void __cluster_dims__(kC, 1, 1) __launch_bounds__(cluster_threads(TP)
                 for (int e2 = 0; e2 < NT / 2; ++e2)
                 {
                     float2 v;
-                    asm volatile("ld.shared.v2.f32 {%0, %1}, [%2];" : "=f"(v.x), "=f"(v.y) : "r"(sS + (uint32_t)(half * 64 + (8 * (jh * (NT / 2) + e2) + 2 * cp) * 4)) : "memory");
+                    asm volatile("ld.shared.v2.f32 {%0, %1}, [%2];" : "=f"(v.x), "=f"(v.y) : "r"(sS + (uint32_t)(half * 64 + (8 * e2 + 2 * cp) * 4)) : "memory");
                     os[2 * e2] = v.x;
                     os[2 * e2 + 1] = v.y;
                 }
@@ -502,7 +488,7 @@ __global__ void __cluster_dims__(kC, 1, 1) __launch_bounds__(cluster_threads(TP)
             g_lstm_loop[(blockIdx.x + 8 * (blockIdx.y + 8 * blockIdx.z)) & 255] = clock64() - loop_t0;
 #endif
 #pragma unroll
-        for (int half = 0; half < 2; ++half)
+        for (int half = 0; half < NG; ++half)
         {
             if (half >= n_halves)
                 break;
@@ -540,10 +526,7 @@ __global__ void __cluster_dims__(kC, 1, 1) __launch_bounds__(cluster_threads(TP)
             const uint32_t pn = (uint32_t)((step + 1) & 1);
             for (int half = 0; half < n_halves; ++half)
             {
-                if (half == 0)
-                    asm volatile("bar.sync 1, %0;" ::"n"(kBarCount) : "memory");
-                else
-                    asm volatile("bar.sync 2, %0;" ::"n"(kBarCount) : "memory");
+                asm volatile("bar.sync %0, %1;" ::"r"(1 + half), "n"(kBarCount) : "memory");
                 const uint32_t slot = (uint32_t)(half * 2) + pn;
                 if (shipper)
                 {
@@ -600,7 +583,7 @@ __global__ void __cluster_dims__(kC, 1, 1) __launch_bounds__(cluster_threads(TP)
             {
                 const uint32_t slot = (uint32_t)(half * 2) + p;
 #ifdef UMX_LSTM_TIMING
-                const bool dbg = ((step == 200 || step == 201) && lane == 0 && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0);
+                const bool dbg = (half < 2 && (step == 200 || step == 201) && lane == 0 && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0);
                 const int dbo = 8 + (step - 200) * 8 + half * 4;
 #endif
                 UMX_DBG_STAMP(dbo + 0);
@@ -621,7 +604,7 @@ __global__ void __cluster_dims__(kC, 1, 1) __launch_bounds__(cluster_threads(TP)
                     for (int h2 = 0; h2 < 2; ++h2)
 #pragma unroll
                         for (int ks = 0; ks < 16; ++ks) // 32 bytes (K = 32) per MMA; B = the tile of source CTA ks / 2
-                            mma_i8_ts(tmem_base + half * 128 + h2 * 64, tmem_base + kTmemA + h2 * 128 + 8 * ks,
+                            mma_i8_ts(tmem_base + half * kDCols + h2 * (kDCols / 2), tmem_base + kTmemA + h2 * 128 + 8 * ks,
                                       b_lo + (((ks >> 1) * kBTile) >> 4) + 2 * (ks & 1), b_hi, idesc, ks != 0);
                     tc_commit(mma_done0 + 8u * half);
                 }
@@ -645,7 +628,7 @@ __global__ void __cluster_dims__(kC, 1, 1) __launch_bounds__(cluster_threads(TP)
             {
                 const uint32_t slot = (uint32_t)(half * 2) + p;
 #ifdef UMX_LSTM_TIMING
-                const bool dbg = ((step == 200 || step == 201) && sw == 0 && lane == 0 && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0);
+                const bool dbg = (half < 2 && (step == 200 || step == 201) && sw == 0 && lane == 0 && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0);
                 const int dbo = 8 + (step - 200) * 8 + half * 4;
 #endif
                 if (sw == 0)
@@ -711,19 +694,20 @@ __global__ void whh_image_kernel(const uint8_t *__restrict__ q, uint8_t *__restr
     img[o] = q[(long)row * kHhC + k];
 }
 
-template <int TP>
-int launch_tp(const ClusterArgs &P, int groups, cudaStream_t st)
+template <int TP, int NG>
+int launch_tp(const ClusterArgs &P, cudaStream_t st)
 {
+    const int groups = ceil_div(P.a.n_tracks, TP * NG); // clusters per (target, direction)
     static bool attr_set[64] = {};
     int dev = 0;
     UMX_CUDA_OK(cudaGetDevice(&dev));
     if (!attr_set[dev & 63])
     {
-        UMX_CUDA_OK(cudaFuncSetAttribute(lstm_cluster_kernel<TP>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
+        UMX_CUDA_OK(cudaFuncSetAttribute(lstm_cluster_kernel<TP, NG>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
         attr_set[dev & 63] = true;
     }
     dim3 grid(kC, 2 * P.a.target_count, groups);
-    lstm_cluster_kernel<TP><<<grid, cluster_threads(TP), kSmemBytes, st>>>(P);
+    lstm_cluster_kernel<TP, NG><<<grid, kThreads, kSmemBytes, st>>>(P);
     UMX_CUDA_OK(cudaGetLastError());
 #ifdef UMX_LSTM_TIMING
     if (getenv("UMX_LSTM_DEBUG"))
@@ -739,9 +723,9 @@ int launch_tp(const ClusterArgs &P, int groups, cudaStream_t st)
                 fprintf(stderr, " [%lld..%lld]", lp[8 * cl] / P.a.F, lp[8 * cl + 7] / P.a.F);
             fprintf(stderr, "\n");
         }
-        fprintf(stderr, "lstm_cluster<%d> step 200 (cycles rel. to epilogue X wait begin)\n  epi X: done %+lld computed %+lld shipped %+lld | epi Y: wait %+lld done %+lld computed %+lld shipped %+lld\n"
+        fprintf(stderr, "lstm_cluster<%d,%d> step 200 (cycles rel. to epilogue X wait begin)\n  epi X: done %+lld computed %+lld shipped %+lld | epi Y: wait %+lld done %+lld computed %+lld shipped %+lld\n"
                         "  mma200 X: wait %+lld hfull %+lld issued %+lld sums %+lld | Y: wait %+lld hfull %+lld issued %+lld sums %+lld\n  mma201 X: wait %+lld hfull %+lld issued %+lld sums %+lld | Y: wait %+lld hfull %+lld issued %+lld sums %+lld\n  writer done: %+lld %+lld %+lld %+lld | sum warp woke: %+lld %+lld %+lld %+lld\n",
-                TP, h[1] - h[0], h[2] - h[0], h[3] - h[0], h[4] - h[0], h[5] - h[0], h[6] - h[0], h[7] - h[0], h[8] - h[0], h[9] - h[0], h[10] - h[0], h[11] - h[0],
+                TP, NG, h[1] - h[0], h[2] - h[0], h[3] - h[0], h[4] - h[0], h[5] - h[0], h[6] - h[0], h[7] - h[0], h[8] - h[0], h[9] - h[0], h[10] - h[0], h[11] - h[0],
                 h[12] - h[0], h[13] - h[0], h[14] - h[0], h[15] - h[0], h[16] - h[0], h[17] - h[0], h[18] - h[0], h[19] - h[0], h[20] - h[0], h[21] - h[0], h[22] - h[0], h[23] - h[0], h[24] - h[0], h[25] - h[0], h[26] - h[0], h[27] - h[0], h[28] - h[0], h[29] - h[0], h[30] - h[0], h[31] - h[0]);
     }
 #endif
@@ -766,7 +750,7 @@ int lstm_cluster_max_active()
     int n = 0;
     cudaLaunchConfig_t cfg{};
     cfg.gridDim = dim3(kC, 64, 1);
-    cfg.blockDim = dim3(cluster_threads(16));
+    cfg.blockDim = dim3(kThreads);
     cfg.dynamicSmemBytes = kSmemBytes;
     cudaLaunchAttribute at[1];
     at[0].id = cudaLaunchAttributeClusterDimension;
@@ -775,9 +759,9 @@ int lstm_cluster_max_active()
     at[0].val.clusterDim.z = 1;
     cfg.attrs = at;
     cfg.numAttrs = 1;
-    if (cudaFuncSetAttribute(lstm_cluster_kernel<16>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes) != cudaSuccess)
+    if (cudaFuncSetAttribute(lstm_cluster_kernel<16, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes) != cudaSuccess)
         return 0;
-    if (cudaOccupancyMaxActiveClusters(&n, lstm_cluster_kernel<16>, &cfg) != cudaSuccess)
+    if (cudaOccupancyMaxActiveClusters(&n, lstm_cluster_kernel<16, 2>, &cfg) != cudaSuccess)
         return 0;
     return n;
 }
@@ -790,12 +774,12 @@ int launch_lstm_cluster(const LstmLayerArgs &a, const uint8_t *const (*img)[2], 
     for (int t = 0; t < kTargets; ++t)
         for (int d = 0; d < 2; ++d)
             P.img[t][d] = img[t][d];
-    // a cluster takes up to 32 tracks as two ping-pong halves of TP tracks each
-    const int groups = ceil_div(a.n_tracks, kMaxTracks);
-    const int per = std::min(a.n_tracks, kMaxTracks);
-    if (per <= 16)
-        return launch_tp<8>(P, groups, st); // one or two halves of 8
-    return launch_tp<16>(P, groups, st);
+    // a cluster takes up to 32 tracks as two ping-pong groups: one group's MMAs and exchange run while the other's gates
+    // are computed.  (Four groups of 8 — lstm_cluster_kernel<16, 2> — shorten the chain of a group but double the MMAs,
+    // bulk copies and barrier traffic per step: measured 116 ms against 92 ms per bench step.)
+    if (a.n_tracks <= 16)
+        return launch_tp<8, 2>(P, st); // one or two groups of 8
+    return launch_tp<16, 2>(P, st);
 }
 
 } // namespace umx
