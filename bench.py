@@ -288,7 +288,10 @@ def main():
                                    f"tracks per GPU sharded with no collective (configs[3]: 256 x 3 min at 8 GPUs), "
                                    f"60 s segments, streaming LSTM, Wiener-EM",
                        "tracks_per_gpu": T, "segments_per_track": segs, "weights": "synthetic UMX-L u8/u16 ggml (seed 1234)",
-                       "l2": "inputs and intermediates per step are far larger than L2 (>1 GB per track-segment)"},
+                       "l2": "inputs and intermediates per step are far larger than L2 (>1 GB per track-segment)",
+                       "schedule": ("in order on one stream" if args.pipeline == 0 else
+                                    "Wiener/iSTFT/finalize of segment s run on a second stream under the recurrence kernels of "
+                                    "segment s+1, so the per-stage times overlap and add up to more than the step")},
             "e2e": {"value": e2e_value, "unit": "audio-s/s", "h2d_bytes_per_step": T * n * 8, "d2h_bytes_per_step": T * n * 32,
                     "steps": k_e2e, "checksum": checksum},
             "gpu_launches": launches, "clocks": clocks, "roofline": roofline, "stages": per_stage,
