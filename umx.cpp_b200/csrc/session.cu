@@ -252,15 +252,41 @@ static int slot_run_next(Session *s)
     s->mask = j.mask;
     s->maxabs = j.maxabs;
     int rc = session_back_part(s, j.seg, j.n_tracks, j.next);
-    if (!rc && j.next == 2)
-    {
+    if (!rc && j.next >= 1)
+    { // the stems whose overlap-add this part completed: normalise / trim them and, for host-buffer calls, send them off
+        const int n1 = (s->tp_nt + 1) / 2;
+        const int begin = j.next == 1 ? s->tp_t0 : s->tp_t0 + n1, count = j.next == 1 ? n1 : s->tp_nt - n1;
+        if (count > 0)
         {
             StageScope sc(s, "finalize");
             s->launches++;
-            rc = launch_finalize(j.fin, j.n_tracks, j.max_range, j.shift, s->n_buf, j.stride, s->tp_nt, s->st, s->tp_t0);
+            rc = launch_finalize(j.fin, j.n_tracks, j.max_range, j.shift, s->n_buf, j.stride, count, s->st, begin);
         }
-        if (!rc && cudaEventRecord(j.done, s->st) != cudaSuccess)
+        if (!rc && j.next == 2 && cudaEventRecord(j.done, s->st) != cudaSuccess)
             rc = -1;
+        if (!rc && j.host_out && count > 0)
+        {
+            cudaEvent_t e2 = take_event(s, s->ev_cursor);
+            if (cudaEventRecord(e2, s->st) != cudaSuccess || cudaStreamWaitEvent(s->st_out, e2, 0) != cudaSuccess)
+                rc = -1;
+            for (int i = 0; !rc && i < j.n_tracks; ++i)
+            {
+                const FinalizeTrack &f = j.fin_host[i];
+                if (f.i_end <= f.i_begin)
+                    continue;
+                for (int stem = begin; stem < begin + count; ++stem)
+                {
+                    const size_t o = 2 * ((size_t)stem * j.n_samples[i] + f.i_begin);
+                    if (cudaMemcpyAsync(j.host_out[i] + o, j.d_out[i] + o, sizeof(float2) * (size_t)(f.i_end - f.i_begin),
+                                        cudaMemcpyDeviceToHost, s->st_out) != cudaSuccess)
+                    {
+                        set_error("umx_cuda_demix: device-to-host copy failed");
+                        rc = -1;
+                        break;
+                    }
+                }
+            }
+        }
     }
     s->st = keep_st;
     s->spec = keep_spec;
@@ -681,9 +707,6 @@ int session_demix_device(Session *s, const float *const *d_audio, const int64_t 
             while (s->slot.seg >= 0 && s->slot.next <= 2)
                 if (int rc = slot_run_next(s))
                     return rc;
-            if (s->slot.seg >= 0 && host_out)
-                if (int rc = ship_out(s->slot.seg))
-                    return rc;
             s->slot = Session::SlotJob{};
             back_done[sg] = take_event(s, ev);
             if (sg + 1 < max_segs)
@@ -699,6 +722,10 @@ int session_demix_device(Session *s, const float *const *d_audio, const int64_t 
                 s->slot.mask = s->mask;
                 s->slot.maxabs = s->maxabs;
                 s->slot.done = back_done[sg];
+                s->slot.fin_host = hf.data() + (size_t)sg * s->T;
+                s->slot.host_out = host_out;
+                s->slot.d_out = d_out;
+                s->slot.n_samples = n_samples;
                 continue;
             }
         }

@@ -66,6 +66,11 @@ struct Session
         float2 *spec = nullptr;
         float *mask = nullptr, *maxabs = nullptr;
         cudaEvent_t done = nullptr;
+        // host-buffer calls: each half of the stems leaves for the host as soon as its iSTFT part and finalize are queued
+        const FinalizeTrack *fin_host = nullptr; // host copy of fin
+        float *const *host_out = nullptr;
+        float *const *d_out = nullptr;
+        const int64_t *n_samples = nullptr;
     } slot;
 
     // grow-only pools for whole-track demixing
