@@ -271,12 +271,21 @@ def main():
             ach = work * units / (t_ms / 1e3) / (1e9 if bound == "hbm" else 1e12)
             per_stage[k] = {"bound": bound, "ms_per_step": t_ms, "achieved": ach, "peak": pk[bound],
                             "unit": "GB/s" if bound == "hbm" else "TFLOP/s", "frac": ach / pk[bound]}
+        if "gemm" in per_stage:
+            # MMA work actually issued: every fp16 split pass counts (fc1/fc2/fc3: `terms` passes, W_ih: min(terms, 2) on the
+            # exact integers); SURVEY 8(d) asks for both the algorithmic and the issued utilisation of the tensor pipe
+            terms = args.gemm_terms if args.gemm_terms else 3
+            issued = 4 * ((15.74e9 + 10.84e9 + 21.69e9) * terms + 65.03e9 * min(terms, 2))
+            g = per_stage["gemm"]
+            g["achieved_issued"] = issued * units / (g["ms_per_step"] / 1e3) / 1e12
+            g["frac_issued"] = g["achieved_issued"] / pk["tensor"]
         top = max(per_stage, key=lambda k: per_stage[k]["ms_per_step"]) if per_stage else None
         roofline = None
         if top:
             r = per_stage[top]
             roofline = {"kernel": top, "bound": r["bound"], "achieved": r["achieved"], "peak": r["peak"], "unit": r["unit"],
-                        "frac": r["frac"], "traffic": TRAFFIC_32.get(top) if T == 32 else None,
+                        "frac": r["frac"], "achieved_issued": r.get("achieved_issued"), "frac_issued": r.get("frac_issued"),
+                        "traffic": TRAFFIC_32.get(top) if T == 32 else None,
                         "traffic_unit": "DRAM bytes per launch (ncu, 32-track segment batch; see profiles/)", "peak_source": pk["src"],
                         "share_of_step": r["ms_per_step"] / ms}
         out = {
