@@ -1,15 +1,18 @@
 // Tensor-core GEMM for the dense layers of the network (reference: the Eigen GEMMs at
 // src/inference.cpp:86,127,143 and the W_ih x_t half of src/lstm.cpp:132-136, for ALL frames at once).
 //
-//   C[m,n] = act(alpha[n] * sum_k A[m,k] B[n,k] + beta[n])
+//   C[m,n] = act(alpha[n] * sum_k A[m,k] B[n,k] + rowvec[m] * gamma[n] + beta[n])
 //
-// sm_100a design: persistent CTAs (one per SM), 128x256 output tiles, fp16 operands staged by TMA
-// (cp.async.bulk.tensor, 128-byte swizzle) through a 4-stage mbarrier ring, tcgen05.mma (M128 N256 K16,
-// one issuing thread) accumulating in fp32 in TMEM, two accumulator buffers (2 x 256 TMEM columns) so
-// the epilogue of tile i overlaps the MMAs of tile i+1.  Warp roles: 0 = TMA producer, 1 = MMA issuer
-// (+ TMEM alloc), 2..5 = epilogue (tcgen05.ld -> BN/bias/activation -> fp32 or fp16 hi/lo stores).
+// sm_100a design: persistent CTAs (one per SM), 128x256 output tiles walked column-fastest (the CTAs running together
+// share a band of row tiles, so the activations stream from HBM once and the weights stay in L2), fp16 operands
+// staged by TMA (cp.async.bulk.tensor, 64/128-byte swizzle) through a 4..6-stage mbarrier ring, tcgen05.mma
+// (M128 N<=256 K16, one issuing thread) accumulating in fp32 in TMEM, two accumulator buffers (2 x 256 TMEM columns)
+// so the epilogue of tile i overlaps the MMAs of tile i+1.  Warp roles: 0 = TMA producer, 1 = MMA issuer
+// (+ TMEM alloc), 2..9 = epilogue, two warps per TMEM lane quadrant (tcgen05.ld -> SMEM transpose in 16-column
+// chunks -> BN/bias/activation -> fp32 or fp16 hi/lo stores), with one branch-free row loop per epilogue kind.
 // Precision: every operand is a (hi, lo) fp16 pair; `terms` selects hi*hi [+ lo*hi [+ hi*lo]] into the
-// same accumulator, i.e. 1, 2 or 3 MMA passes per k-block ("GEMM precision").
+// same accumulator, i.e. 1, 2 or 3 MMA passes per k-block ("GEMM precision").  The W_ih GEMM passes the
+// centred quantised integers as a single exact plane and folds the dequantisation offset in as the rank-1 term.
 #include "common.cuh"
 #include "kernels.cuh"
 #include "tc_common.cuh"
