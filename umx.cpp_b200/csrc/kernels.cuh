@@ -144,6 +144,7 @@ struct WienerArgs
     int F;
     int n_tracks;
     int stem_begin, stem_count; // stems whose output is written (all 4 unless target-parallel)
+    const IstftTrack *chunks; // optional, per track: only the frames its chunk's iSTFT will read are filtered (apply pass)
 };
 constexpr int kWienerChunks = 19;
 int launch_wiener(const WienerArgs &a, cudaStream_t st);

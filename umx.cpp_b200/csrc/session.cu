@@ -513,6 +513,7 @@ static int session_back_part(Session *s, int seg, int n_tracks, int part)
         w.n_tracks = n_tracks;
         w.stem_begin = s->tp_t0;
         w.stem_count = s->tp_nt;
+        w.chunks = dis;
         s->launches += 3;
         return launch_wiener(w, s->st);
     }

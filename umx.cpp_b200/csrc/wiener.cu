@@ -136,7 +136,15 @@ __global__ void __launch_bounds__(256) wiener_apply_kernel(const WienerArgs a)
     const int trk = blockIdx.z;
     if (b >= kBins)
         return;
-    const int f_begin = blockIdx.y * kWienerApplyFrames, f_end = min(a.F, f_begin + kWienerApplyFrames);
+    int f_lim = a.F;
+    if (a.chunks)
+    { // the stems are only read by the iSTFT of this track's chunk: frames beyond it are never used (see istft_kernel)
+        const int nw = a.chunks[trk].n_wave;
+        f_lim = min(a.F, (nw > 0 ? nw + kPad + kHop - 1 : 0) / kHop);
+    }
+    const int f_begin = blockIdx.y * kWienerApplyFrames, f_end = min(f_lim, f_begin + kWienerApplyFrames);
+    if (f_begin >= f_end)
+        return;
     const float ma = wiener_max_abs(a.maxabs, trk);
     const float inv_ma = 1.0f / ma;
     const float reg = sqrtf(kWienerEps); // wiener.cpp:155-163
