@@ -15,6 +15,14 @@ constexpr int kNfft = 4096;
 constexpr int kHop = 1024;
 constexpr int kBins = kNfft / 2 + 1;      // 2049
 constexpr int kPad = kNfft / 2;           // 2048
+// Frames of an F-frame window that can reach one of the first n_wave samples: sample i sits at padded position i + kPad and
+// frame f covers [kHop f, kHop f + kNfft).  Every later frame of a zero-extended chunk has an all-zero spectrum (so it adds
+// nothing to the Wiener statistics whatever the network says there) and is never emitted: the post-network stages skip it.
+__host__ __device__ inline int frames_reaching(int n_wave, int F)
+{
+    const int f = (n_wave > 0 ? n_wave + kPad + kHop - 1 : 0) / kHop;
+    return f < F ? f : F;
+}
 constexpr int kBinsCropped = 1487;        // src/inference.cpp:41-55 (16 kHz bandwidth)
 constexpr int kFc1In = 2 * kBinsCropped;  // 2974
 constexpr int kFc1InPad = 2976;           // row pitch of the fc1 A operand (16-byte aligned rows)

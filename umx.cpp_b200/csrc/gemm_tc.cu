@@ -65,7 +65,8 @@ struct TcProblem
     int n_group;
     long group_stride;
     int m_tiles, n_tiles, tile_begin; // tiles [tile_begin, tile_begin + m_tiles*n_tiles)
-    int pad_;
+    int rows_per_track;               // with chunks: rows are (track, frame); see GemmProblem
+    const IstftTrack *chunks;
 };
 
 struct alignas(64) TcParams
@@ -214,6 +215,23 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_tc_kernel(const __grid_const
         n0 = (local % P.p[pi].n_tiles) * BN;
         m0 = (local / P.p[pi].n_tiles) * BM;
     };
+    // A row tile none of whose rows is a frame that reaches its track's chunk is not computed (all three warp roles skip
+    // the same tiles, so their pipeline counters stay in step).
+    auto needed = [&](int pi, int m0) -> bool {
+        const IstftTrack *ch = P.p[pi].chunks;
+        if (!ch)
+            return true;
+        const int F = P.p[pi].rows_per_track;
+        const int t0 = m0 / F, f0 = m0 - t0 * F;
+        if (f0 < frames_reaching(ch[t0].n_wave, F))
+            return true;
+        const int t1 = (min(m0 + BM, P.p[pi].M) - 1) / F;
+        for (int t = t0 + 1; t <= t1; ++t) // later tracks start inside this tile at frame 0
+            if (ch[t].n_wave > 0)
+                return true;
+        return false;
+    };
+
 
     if (warp == 0)
     {
@@ -226,6 +244,8 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_tc_kernel(const __grid_const
             {
                 int pi, m0, n0;
                 locate(tile, pi, m0, n0);
+                if (!needed(pi, m0))
+                    continue;
                 const int kblocks = (P.p[pi].K + BK - 1) / BK;
                 for (int kb = 0; kb < kblocks; ++kb)
                 {
@@ -261,6 +281,8 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_tc_kernel(const __grid_const
             {
                 int pi, m0, n0;
                 locate(tile, pi, m0, n0);
+                if (!needed(pi, m0))
+                    continue;
                 const int kiters = (P.p[pi].K + BK - 1) / BK;
                 // a ragged last column tile only pays for the columns it has (N of the MMA in steps of 16)
                 const uint32_t idesc = idesc_f16_f32acc(BM, min(BN, (P.p[pi].N - n0 + 15) & ~15));
@@ -317,6 +339,8 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_tc_kernel(const __grid_const
         {
             int pi, m0, n0;
             locate(tile, pi, m0, n0);
+            if (!needed(pi, m0))
+                continue;
             // hoist the problem description into registers once per tile
             const int M = P.p[pi].M, N = P.p[pi].N, ldo = P.p[pi].ldo, act = P.p[pi].act, n_group = P.p[pi].n_group;
             const long gstride = P.p[pi].group_stride;
@@ -483,6 +507,9 @@ int launch_gemm_tc(const GemmBatch &batch, int terms, cudaStream_t st)
         p.ldo = g.ldo;
         p.n_group = g.n_group;
         p.group_stride = g.group_stride;
+        p.chunks = g.chunks;
+        p.rows_per_track = g.rows_per_track;
+        UMX_CHECK(!g.chunks || g.rows_per_track > 0, "gemm_tc: rows_per_track missing");
         p.m_tiles = ceil_div(g.M, BM);
         p.n_tiles = ceil_div(g.N, BN);
         p.tile_begin = tiles;

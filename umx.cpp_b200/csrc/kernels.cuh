@@ -82,6 +82,10 @@ struct GemmProblem
     int ldo;
     int n_group;
     long group_stride;
+    // optional: rows are (track, frame) with rows_per_track frames per track; only the frames reaching the track's chunk are
+    // needed (frames_reaching), row tiles without such a row are skipped by the tensor-core kernel
+    const IstftTrack *chunks;
+    int rows_per_track;
 };
 
 constexpr int kMaxGemmProblems = 4;
@@ -144,7 +148,7 @@ struct WienerArgs
     int F;
     int n_tracks;
     int stem_begin, stem_count; // stems whose output is written (all 4 unless target-parallel)
-    const IstftTrack *chunks; // optional, per track: only the frames its chunk's iSTFT will read are filtered (apply pass)
+    const IstftTrack *chunks; // optional, per track: only the frames that reach its chunk are reduced and filtered
 };
 constexpr int kWienerChunks = 19;
 int launch_wiener(const WienerArgs &a, cudaStream_t st);

@@ -435,6 +435,8 @@ int session_network(Session *s, int n_tracks)
             p.act = kActRelu;
             p.alpha = m->t[t].fc2_alpha;
             p.beta = m->t[t].fc2_beta;
+            p.chunks = s->cur_chunks;
+            p.rows_per_track = s->F;
             p.out_hi = s->fc2_h + (size_t)t * Mc * H;
             p.out_lo = s->fc2_l + (size_t)t * Mc * H;
             p.ldo = H;
@@ -458,6 +460,8 @@ int session_network(Session *s, int n_tracks)
             p.act = kActRelu;
             p.alpha = m->t[t].fc3_alpha;
             p.beta = m->t[t].fc3_beta;
+            p.chunks = s->cur_chunks;
+            p.rows_per_track = s->F;
             p.out_f32 = s->mask + (size_t)t * Mc * kMaskLd;
             p.ldo = kMaskLd;
             p.n_group = kMaskLd;
@@ -479,8 +483,11 @@ int session_front(Session *s, int seg, int n_tracks)
         if (int rc = launch_stft(dst, n_tracks, s->n_buf, s->spec, s->xh, s->xl, s->maxabs, s->st))
             return rc;
     }
-    if (int rc = session_network(s, n_tracks))
-        return rc;
+    s->cur_chunks = s->d_istft + (size_t)seg * s->T;
+    const int rc_net = session_network(s, n_tracks);
+    s->cur_chunks = nullptr;
+    if (rc_net)
+        return rc_net;
     if (s->tp_world > 1)
     { // the one exchange step of the target-parallel mode: every rank needs all four sources' masks
         StageScope sc(s, "allgather");

@@ -212,7 +212,7 @@ __global__ void __launch_bounds__(256, 3) istft_kernel(const float2 *__restrict_
     // frames that reach an emitted sample: sample i sits at padded position i + 2048, frame f covers [1024 f, 1024 f + 4096).
     // The reference always transforms the whole 60 s window and drops what lies beyond the chunk (src/dsp.cpp:203-205); a
     // short last chunk (or a track with no chunk in this segment) needs only its first few frames.
-    const int f_need = min(F, (tk.n_wave > 0 ? tk.n_wave + kPad + kHop - 1 : 0) / kHop);
+    const int f_need = frames_reaching(tk.n_wave, F);
     if (f0 >= f_need)
         return;
     const int f1 = min(f_need, f0 + frames_per_cta);

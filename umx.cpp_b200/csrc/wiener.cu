@@ -71,7 +71,9 @@ __global__ void __launch_bounds__(256) wiener_reduce_kernel(const WienerArgs a)
     if (b >= kBins)
         return;
     const int fc = (a.F + kWienerChunks - 1) / kWienerChunks;
-    const int f_begin = chunk * fc, f_end = min(a.F, f_begin + fc);
+    // frames beyond the chunk have an all-zero mixture spectrum: exactly zero terms in every sum (and the masks there are not computed)
+    const int f_lim = a.chunks ? frames_reaching(a.chunks[trk].n_wave, a.F) : a.F;
+    const int f_begin = chunk * fc, f_end = min(f_lim, f_begin + fc);
     const float ma = 1.0f / wiener_max_abs(a.maxabs, trk); // reciprocal: see initial_estimate
     float acc[kWienerQ];
 #pragma unroll
@@ -136,12 +138,8 @@ __global__ void __launch_bounds__(256) wiener_apply_kernel(const WienerArgs a)
     const int trk = blockIdx.z;
     if (b >= kBins)
         return;
-    int f_lim = a.F;
-    if (a.chunks)
-    { // the stems are only read by the iSTFT of this track's chunk: frames beyond it are never used (see istft_kernel)
-        const int nw = a.chunks[trk].n_wave;
-        f_lim = min(a.F, (nw > 0 ? nw + kPad + kHop - 1 : 0) / kHop);
-    }
+    // the stems are only read by the iSTFT of this track's chunk: frames beyond it are never used (see istft_kernel)
+    const int f_lim = a.chunks ? frames_reaching(a.chunks[trk].n_wave, a.F) : a.F;
     const int f_begin = blockIdx.y * kWienerApplyFrames, f_end = min(f_lim, f_begin + kWienerApplyFrames);
     if (f_begin >= f_end)
         return;
