@@ -70,3 +70,20 @@ def test_lockstep_tracks_are_independent_and_deterministic(umx):
     for x, y in zip(batch_a, batch_b):
         assert np.array_equal(x, y)
     assert np.array_equal(batch_a[2], alone)
+
+
+@pytest.mark.parametrize("hidden,n_buf", [(1024, 65536), (64, 16384)])
+def test_skipping_frames_beyond_the_chunk_changes_nothing(umx, hidden, n_buf):
+    """The reference runs every frame of the zero-extended 60 s window; here the frames beyond a chunk are computed once (first
+    layer) or not at all (after the network).  Option skip_zero_frames=0 runs them all: the stems must be identical bits.
+    Ragged lockstep batch: short last chunks, and tracks that run out of segments early."""
+    gm = umx.load_umx_model(synth.make_ggml(hidden=hidden, seed=1234))
+    tracks = [synth.make_audio(n, 70 + i) for i, n in enumerate((3 * n_buf + 900, n_buf // 3, 2 * n_buf + n_buf // 2, 5000))]
+    outs = []
+    for skip in (1, 0):
+        sess = umx.Session(gm, len(tracks), n_buf)
+        sess.set_option("skip_zero_frames", skip)
+        outs.append(sess.demix(tracks))
+    for x, y in zip(*outs):
+        assert np.isfinite(x).all()
+        assert np.array_equal(x, y)

@@ -295,6 +295,11 @@ int umx_cuda_session_set_option(umx_cuda_session *s, const char *name, int value
         UMX_CHECK(value >= 0 && value <= 2, "pipeline must be 0, 1 or 2");
         s->s->pipeline = value;
     }
+    else if (n == "skip_zero_frames")
+    {
+        UMX_CHECK(value == 0 || value == 1, "skip_zero_frames must be 0 or 1");
+        s->s->skip_zero_frames = value;
+    }
     else if (n == "lstm_impl")
     {
         UMX_CHECK(value == 0 || value == 1, "lstm_impl must be 0 (cluster) or 1 (simple)");

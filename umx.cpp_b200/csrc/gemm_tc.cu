@@ -66,6 +66,7 @@ struct TcProblem
     long group_stride;
     int m_tiles, n_tiles, tile_begin; // tiles [tile_begin, tile_begin + m_tiles*n_tiles)
     int rows_per_track;               // with chunks: rows are (track, frame); see GemmProblem
+    int extra_rows;
     const IstftTrack *chunks;
 };
 
@@ -223,11 +224,11 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_tc_kernel(const __grid_const
             return true;
         const int F = P.p[pi].rows_per_track;
         const int t0 = m0 / F, f0 = m0 - t0 * F;
-        if (f0 < frames_reaching(ch[t0].n_wave, F))
+        if (f0 < frames_reaching(ch[t0].n_wave, F) + P.p[pi].extra_rows)
             return true;
         const int t1 = (min(m0 + BM, P.p[pi].M) - 1) / F;
         for (int t = t0 + 1; t <= t1; ++t) // later tracks start inside this tile at frame 0
-            if (ch[t].n_wave > 0)
+            if (ch[t].n_wave > 0 || P.p[pi].extra_rows)
                 return true;
         return false;
     };
@@ -509,6 +510,7 @@ int launch_gemm_tc(const GemmBatch &batch, int terms, cudaStream_t st)
         p.group_stride = g.group_stride;
         p.chunks = g.chunks;
         p.rows_per_track = g.rows_per_track;
+        p.extra_rows = g.extra_rows;
         UMX_CHECK(!g.chunks || g.rows_per_track > 0, "gemm_tc: rows_per_track missing");
         p.m_tiles = ceil_div(g.M, BM);
         p.n_tiles = ceil_div(g.N, BN);

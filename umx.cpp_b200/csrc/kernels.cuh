@@ -35,8 +35,9 @@ struct FinalizeTrack
 constexpr int kIstftFramesPerCta = 32; // + 3 halo frames recomputed per CTA
 
 int init_fft_tables(int device);
+// skip_zero: frames beyond the first all-zero one of a short chunk are not computed (nothing downstream reads them)
 int launch_stft(const StftTrack *d_tracks, int n_tracks, int n_buf, float2 *spec, __half *xh, __half *xl,
-                float *maxabs, cudaStream_t st);
+                float *maxabs, cudaStream_t st, int skip_zero = 0);
 int launch_istft(const float2 *stems, long stem_stride, int n_stems, const IstftTrack *d_tracks, int n_tracks,
                  int n_buf, cudaStream_t st, int stem_begin = 0);
 int launch_finalize(const FinalizeTrack *d_tracks, int n_tracks, long max_range, int shift, int n_buf, int stride, int n_stems,
@@ -86,6 +87,7 @@ struct GemmProblem
     // needed (frames_reaching), row tiles without such a row are skipped by the tensor-core kernel
     const IstftTrack *chunks;
     int rows_per_track;
+    int extra_rows; // 1: also the first all-zero frame (its row stands for every later one, see LstmLayerArgs::chunks)
 };
 
 constexpr int kMaxGemmProblems = 4;
@@ -122,6 +124,9 @@ struct LstmLayerArgs
     int Hh;                // hidden units per direction
     int n_tracks;
     int target_begin, target_count;
+    // optional (first layer): frames >= z = frames_reaching(chunk) have an all-zero spectrum, hence identical fc1 outputs and
+    // identical input projections; only row z of xproj is computed and every later step reads it
+    const IstftTrack *chunks;
 };
 int launch_lstm_simple(const LstmLayerArgs &a, cudaStream_t st);
 // lstm_cluster.cu: W_hh resident in SMEM across a cluster of 8 CTAs, tcgen05 kind::i8 (Hh == 512 only)

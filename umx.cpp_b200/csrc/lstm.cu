@@ -35,11 +35,13 @@ __global__ void lstm_simple_kernel(const LstmLayerArgs a)
 
     const float *xp = a.xproj + (long)target * a.xproj_target_stride + (long)dir * 4 * Hh + 4 * u; // gate-interleaved
     const int ldx = 8 * Hh;
+    // first layer of a short chunk: frames from the first all-zero one on share one computed row of xproj (LstmLayerArgs::chunks)
+    const int t_z = a.chunks ? frames_reaching(a.chunks[trk].n_wave, a.F) : a.F;
     for (int step = 0; step < a.F; ++step)
     {
         const int t = dir == 0 ? step : a.F - 1 - step;
         const long row = (long)trk * a.F + t;
-        const float *x = xp + row * ldx;
+        const float *x = xp + ((long)trk * a.F + min(t, t_z)) * ldx;
         const float4 xg = *reinterpret_cast<const float4 *>(x);
         const float gi = xg.x, gf = xg.y, gg = xg.z, go = xg.w;
         float ai = 0.f, af = 0.f, ag = 0.f, ao = 0.f;

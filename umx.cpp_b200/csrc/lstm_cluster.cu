@@ -381,7 +381,10 @@ __global__ void __cluster_dims__(kC, 1, 1) __launch_bounds__(kThreads, 1) lstm_c
             for (int e = 0; e < NT; ++e)
             {
                 const int trk = tb + trk_of(e);
-                dst[e] = trk < a.n_tracks ? __ldg(reinterpret_cast<const float4 *>(xrow + (long)tt * ldx + (long)trk * trk_x)) : make_float4(0.f, 0.f, 0.f, 0.f);
+                // first layer of a short chunk: every frame from the first all-zero one on has the same input projection,
+                // and only that one row was computed
+                const int te = (a.chunks && trk < a.n_tracks) ? min(tt, frames_reaching(__ldg(&a.chunks[trk].n_wave), F)) : tt;
+                dst[e] = trk < a.n_tracks ? __ldg(reinterpret_cast<const float4 *>(xrow + (long)te * ldx + (long)trk * trk_x)) : make_float4(0.f, 0.f, 0.f, 0.f);
             }
         };
 

@@ -324,6 +324,12 @@ int session_lstm(Session *s, int n_tracks, int target_begin, int target_count, b
                 p.N = 4 * H;
                 p.K = H;
                 p.act = kActNone;
+                if (l == 0)
+                { // the first all-zero frame's input projection stands for all later ones (LstmLayerArgs::chunks)
+                    p.chunks = s->cur_chunks;
+                    p.rows_per_track = s->F;
+                    p.extra_rows = 1;
+                }
                 p.alpha = m->t[t].wih_alpha[l];
                 p.gamma = m->t[t].wih_gamma[l];
                 p.rowvec = s->rowsum + (size_t)t * Mc;
@@ -375,6 +381,7 @@ int session_lstm(Session *s, int n_tracks, int target_begin, int target_count, b
         a.n_tracks = n_tracks;
         a.target_begin = target_begin;
         a.target_count = target_count;
+        a.chunks = l == 0 ? s->cur_chunks : nullptr;
         s->launches++;
         if (s->lstm_impl == 0 && lstm_cluster_supported(Hh))
         {
@@ -408,6 +415,9 @@ int session_network(Session *s, int n_tracks)
         p.N = s->tp_nt * H;
         p.K = kFc1InPad;
         p.act = kActTanh;
+        p.chunks = s->cur_chunks; // all-zero frames beyond the chunk: only the first one is computed
+        p.rows_per_track = s->F;
+        p.extra_rows = 1;
         p.alpha = m->fc1_alpha + t0 * H;
         p.beta = m->fc1_beta + t0 * H;
         p.out_hi = s->act_h + t0 * Mc * 2 * H;
@@ -480,10 +490,10 @@ int session_front(Session *s, int seg, int n_tracks)
         StageScope sc(s, "stft");
         UMX_CUDA_OK(cudaMemsetAsync(s->maxabs, 0, sizeof(float) * s->T, s->st));
         s->launches++;
-        if (int rc = launch_stft(dst, n_tracks, s->n_buf, s->spec, s->xh, s->xl, s->maxabs, s->st))
+        if (int rc = launch_stft(dst, n_tracks, s->n_buf, s->spec, s->xh, s->xl, s->maxabs, s->st, s->skip_zero_frames))
             return rc;
     }
-    s->cur_chunks = s->d_istft + (size_t)seg * s->T;
+    s->cur_chunks = s->skip_zero_frames ? s->d_istft + (size_t)seg * s->T : nullptr;
     const int rc_net = session_network(s, n_tracks);
     s->cur_chunks = nullptr;
     if (rc_net)

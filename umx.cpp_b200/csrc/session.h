@@ -45,7 +45,8 @@ struct Session
     float *lstm_f32 = nullptr;               // optional fp32 LSTM output (kernel-level API), [4][Mcap][H]
 
     StftTrack *d_stft = nullptr;   // descriptor arrays [seg_cap][T]
-    const IstftTrack *cur_chunks = nullptr; // chunk descriptors of the segment the network is running for (fc2/fc3 skip frames beyond them)
+    const IstftTrack *cur_chunks = nullptr; // chunk descriptors of the segment the network is running for (frames beyond a chunk are skipped)
+    int skip_zero_frames = 1;               // option "skip_zero_frames": 0 computes every frame of every window like the reference does
     IstftTrack *d_istft = nullptr;
     FinalizeTrack *d_final = nullptr;
     int seg_cap = 0;

@@ -72,7 +72,7 @@ int init_fft_tables(int device)
 // ------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256) stft_kernel(const StftTrack *__restrict__ tracks, int n_buf, int F,
                                                    float2 *__restrict__ spec, __half *__restrict__ xh,
-                                                   __half *__restrict__ xl, float *__restrict__ maxabs)
+                                                   __half *__restrict__ xl, float *__restrict__ maxabs, int skip_zero)
 {
     __shared__ float2 s[kFftSmemFloat2];
     __shared__ float s_red[8];
@@ -80,6 +80,10 @@ __global__ void __launch_bounds__(256) stft_kernel(const StftTrack *__restrict__
     const int f = blockIdx.x;
     const int trk = blockIdx.y;
     const StftTrack tk = tracks[trk];
+    // frames beyond the chunk are all zero (the window is the zero-extended chunk); the first of them is computed and stands
+    // for the rest: nothing downstream reads the others (see frames_reaching and LstmLayerArgs::chunks)
+    if (skip_zero && f > frames_reaching(tk.n_valid, F))
+        return;
 
     float2 r[16];
 #pragma unroll
@@ -408,11 +412,11 @@ __global__ void from_ref_layout_kernel(const T *__restrict__ in, T *__restrict__
 // launchers
 // ------------------------------------------------------------------------------------------------
 int launch_stft(const StftTrack *d_tracks, int n_tracks, int n_buf, float2 *spec, __half *xh, __half *xl,
-                float *maxabs, cudaStream_t st)
+                float *maxabs, cudaStream_t st, int skip_zero)
 {
     const int F = n_buf / kHop + 1;
     dim3 grid(F, n_tracks);
-    stft_kernel<<<grid, 256, 0, st>>>(d_tracks, n_buf, F, spec, xh, xl, maxabs);
+    stft_kernel<<<grid, 256, 0, st>>>(d_tracks, n_buf, F, spec, xh, xl, maxabs, skip_zero);
     UMX_CUDA_OK(cudaGetLastError());
     return 0;
 }
