@@ -263,22 +263,32 @@ def main():
 
     if rank == 0:
         pk = peaks()
-        units = T * segs  # (track, segment) passes per step
+        # Work actually performed per track and step.  The reference runs every frame of every zero-extended 60 s window; the
+        # frames beyond a chunk are computed once (STFT, fc1, first-layer W_ih: fz + 1 of F frames) or not at all (fc2, fc3,
+        # Wiener, iSTFT: fz of F) here, so a short last segment counts for what is really done.
+        plan = umx.segment_plan(n)
+        fz = [min(FRAMES, (ln + 2048 + 1023) // 1024 if ln > 0 else 0) for _, ln in plan]
+        pre = sum(min(FRAMES, z + 1) / FRAMES for z in fz)   # segment-equivalents of the stages before the recurrences
+        post = sum(z / FRAMES for z in fz)                   # ... and after the network
+        gemm_1 = 4 * ((15.74e9 + 65.03e9 / 3) * pre + (65.03e9 * 2 / 3) * segs + (10.84e9 + 21.69e9) * post)
+        work_per_track = {"stft": ALGO["stft"][1] * pre, "istft": ALGO["istft"][1] * post, "wiener": ALGO["wiener"][1] * post,
+                          "gemm": gemm_1, "lstm": ALGO["lstm"][1] * segs}
         per_stage = {}
-        for k, (bound, work) in ALGO.items():
+        for k, (bound, _) in ALGO.items():
             t_ms = stage_ms[k] / args.steps
             if t_ms <= 0:
                 continue
-            ach = work * units / (t_ms / 1e3) / (1e9 if bound == "hbm" else 1e12)
+            ach = work_per_track[k] * T / (t_ms / 1e3) / (1e9 if bound == "hbm" else 1e12)
             per_stage[k] = {"bound": bound, "ms_per_step": t_ms, "achieved": ach, "peak": pk[bound],
                             "unit": "GB/s" if bound == "hbm" else "TFLOP/s", "frac": ach / pk[bound]}
         if "gemm" in per_stage:
             # MMA work actually issued: every fp16 split pass counts (fc1/fc2/fc3: `terms` passes, W_ih: min(terms, 2) on the
             # exact integers); SURVEY 8(d) asks for both the algorithmic and the issued utilisation of the tensor pipe
             terms = args.gemm_terms if args.gemm_terms else 3
-            issued = 4 * ((15.74e9 + 10.84e9 + 21.69e9) * terms + 65.03e9 * min(terms, 2))
+            issued = 4 * (15.74e9 * terms * pre + (65.03e9 / 3) * min(terms, 2) * pre + (65.03e9 * 2 / 3) * min(terms, 2) * segs
+                          + (10.84e9 + 21.69e9) * terms * post)
             g = per_stage["gemm"]
-            g["achieved_issued"] = issued * units / (g["ms_per_step"] / 1e3) / 1e12
+            g["achieved_issued"] = issued * T / (g["ms_per_step"] / 1e3) / 1e12
             g["frac_issued"] = g["achieved_issued"] / pk["tensor"]
         if "lstm" in per_stage:
             # the recurrence is a latency problem: time per dependent step is the figure of merit; the
