@@ -373,17 +373,35 @@ __global__ void __cluster_dims__(kC, 1, 1) __launch_bounds__(kThreads, 1) lstm_c
         // ARRIVE (non-blocking) on the half's named barrier; the shipper warp waits there and ships the tile.
         auto publish_tile = [&](int half) {
             asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-            asm volatile("bar.arrive %0, %1;" ::"r"(1 + half), "n"(kBarCount) : "memory");
+            // (immediate barrier ids: a register id makes ptxas reserve all 16 named barriers and costs a few per cent)
+            if (half == 0)
+                asm volatile("bar.arrive 1, %0;" ::"n"(kBarCount) : "memory");
+            else if (half == 1)
+                asm volatile("bar.arrive 2, %0;" ::"n"(kBarCount) : "memory");
+            else if (half == 2)
+                asm volatile("bar.arrive 3, %0;" ::"n"(kBarCount) : "memory");
+            else
+                asm volatile("bar.arrive 4, %0;" ::"n"(kBarCount) : "memory");
         };
         // input projection (4 gates) of one step for this thread's tracks of a half
-        auto load_xp = [&](float4(&dst)[NT], int tb, int tt) {
+        // first layer of a short chunk: every frame from the first all-zero one on has the same input projection and only
+        // that one row was computed (LstmLayerArgs::chunks); zrow = that frame per track of this thread, F when all rows exist
+        int zrow[NG][NT];
+#pragma unroll
+        for (int half = 0; half < NG; ++half)
+#pragma unroll
+            for (int e = 0; e < NT; ++e)
+            {
+                const int trk = trk0 + half * TP + trk_of(e);
+                zrow[half][e] = (a.chunks && trk < a.n_tracks) ? frames_reaching(a.chunks[trk].n_wave, F) : F;
+            }
+        auto load_xp = [&](float4(&dst)[NT], int half, int tt) {
+            const int tb = trk0 + half * TP;
 #pragma unroll
             for (int e = 0; e < NT; ++e)
             {
                 const int trk = tb + trk_of(e);
-                // first layer of a short chunk: every frame from the first all-zero one on has the same input projection,
-                // and only that one row was computed
-                const int te = (a.chunks && trk < a.n_tracks) ? min(tt, frames_reaching(__ldg(&a.chunks[trk].n_wave), F)) : tt;
+                const int te = min(tt, zrow[half][e]);
                 dst[e] = trk < a.n_tracks ? __ldg(reinterpret_cast<const float4 *>(xrow + (long)te * ldx + (long)trk * trk_x)) : make_float4(0.f, 0.f, 0.f, 0.f);
             }
         };
@@ -405,7 +423,7 @@ __global__ void __cluster_dims__(kC, 1, 1) __launch_bounds__(kThreads, 1) lstm_c
                 hlast[half][e] = a.h_state[so];
                 publish_digits<TP>(hlast[half][e], (uint32_t)trk_of(e), sB + (uint32_t)(half * 2) * kBBuf + (uint32_t)r * kBTile, kk);
             }
-            load_xp(xp[half], tb, dir == 0 ? 0 : F - 1);
+            load_xp(xp[half], half, dir == 0 ? 0 : F - 1);
             publish_tile(half);
         }
 
@@ -421,7 +439,6 @@ __global__ void __cluster_dims__(kC, 1, 1) __launch_bounds__(kThreads, 1) lstm_c
             {
                 if (half >= n_halves)
                     break;
-                const int tb = trk0 + half * TP;
                 const uint32_t tile_out = sB + ((uint32_t)(half * 2) + pn) * kBBuf + (uint32_t)r * kBTile;
 
 #ifdef UMX_LSTM_TIMING
@@ -480,7 +497,7 @@ __global__ void __cluster_dims__(kC, 1, 1) __launch_bounds__(kThreads, 1) lstm_c
                 for (int e = 0; e < NT; ++e)
                     publish_digits<TP>(hn[e], (uint32_t)trk_of(e), tile_out, kk);
                 // next step's input projection for this half: in flight while the other half is processed
-                load_xp(xp[half], tb, tn);
+                load_xp(xp[half], half, tn);
                 UMX_DBG_STAMP(half * 4 + 2);
                 publish_tile(half);
                 UMX_DBG_STAMP(half * 4 + 3);
@@ -529,7 +546,14 @@ __global__ void __cluster_dims__(kC, 1, 1) __launch_bounds__(kThreads, 1) lstm_c
             const uint32_t pn = (uint32_t)((step + 1) & 1);
             for (int half = 0; half < n_halves; ++half)
             {
-                asm volatile("bar.sync %0, %1;" ::"r"(1 + half), "n"(kBarCount) : "memory");
+                if (half == 0)
+                    asm volatile("bar.sync 1, %0;" ::"n"(kBarCount) : "memory");
+                else if (half == 1)
+                    asm volatile("bar.sync 2, %0;" ::"n"(kBarCount) : "memory");
+                else if (half == 2)
+                    asm volatile("bar.sync 3, %0;" ::"n"(kBarCount) : "memory");
+                else
+                    asm volatile("bar.sync 4, %0;" ::"n"(kBarCount) : "memory");
                 const uint32_t slot = (uint32_t)(half * 2) + pn;
                 if (shipper)
                 {
