@@ -296,8 +296,8 @@ def main():
             launches_l = 3 * segs
             per_stage["lstm"]["us_per_dependent_step"] = per_stage["lstm"]["ms_per_step"] * 1e3 / (launches_l * FRAMES)
             per_stage["lstm"]["note"] = "latency-bound: 8-CTA clusters on 64 SMs, one MMA batch + DSMEM exchange per step"
-        # dominant kernel: gemm_tc_kernel (its two instantiations are 45 % of the GPU time in the ncu launch list of this command,
-        # profiles/r01_launches_bench_steps1_summary.txt; the recurrence kernel is 29 %).  Under the default schedule the
+        # dominant kernel: gemm_tc_kernel (its two instantiations are 43 % of the GPU time in the ncu launch list of this command,
+        # profiles/r01_launches_bench_steps1_summary.txt; the recurrence kernel is 34 %).  Under the default schedule the
         # recurrence's stage time is inflated by the post-stage kernels sharing the GPU with it, so it is not picked by time.
         top = "gemm" if "gemm" in per_stage else (max(per_stage, key=lambda k: per_stage[k]["ms_per_step"]) if per_stage else None)
         roofline = None
