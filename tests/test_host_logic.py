@@ -71,3 +71,25 @@ def test_product_does_not_import_oracle():
         if not f.endswith((".cu", ".cuh", ".h", ".cpp")):
             continue
         assert "oracle" not in open(os.path.join(ROOT, "umx.cpp_b200", "csrc", f)).read().lower()
+
+
+def _frames_reaching(n_wave: int, F: int) -> int:
+    """umx.cpp_b200/csrc/common.cuh: frames_reaching (mirrored here; the oracle decides whether the bound is right)."""
+    return min(F, (n_wave + 2048 + 1023) // 1024 if n_wave > 0 else 0)
+
+
+@pytest.mark.parametrize("n_buf,n_wave", [(16384, 1), (16384, 5000), (16384, 6144), (16384, 6145), (16384, 14000),
+                                           (16384, 14336), (16384, 14337), (16384, 16384), (32768, 18017)])
+def test_frames_beyond_a_chunk_are_exactly_zero_in_the_oracle(n_buf, n_wave):
+    """The product skips every frame f >= frames_reaching(chunk length) of a zero-extended window after the network and computes
+    only the first of them before it.  That is only right if the oracle's STFT of such a window is EXACTLY zero there (so the
+    masks cannot matter in the Wiener sums) and the bound is tight."""
+    rng = np.random.default_rng(n_wave)
+    audio = rng.uniform(0.2, 1.0, size=(2, n_wave)).astype(np.float32)  # no zero samples inside the chunk
+    spec = O.stft(audio, n_buf)  # (2, F, 2049), buffers sized for n_buf, chunk zero-extended (SURVEY F4)
+    F = spec.shape[1]
+    fz = _frames_reaching(n_wave, F)
+    assert np.all(spec[:, fz:, :] == 0)
+    # tight up to the window's zero first tap: at most one frame more than strictly necessary is computed
+    last_nonzero = max(f for f in range(F) if np.any(spec[:, f, :] != 0))
+    assert fz - 1 - last_nonzero in (0, 1)
