@@ -9,21 +9,24 @@
 //   * h_{t-1} of all 512 units x tracks sits in each CTA's SMEM as the MMA B operand, written as three
 //     signed base-128 digits per value (h = sum_i d_i 2^(-6-7i), exact to 2^-21), one 64-byte-swizzled
 //     tile per source CTA;
-//   * one elected thread issues tcgen05.mma kind::i8: D[row][3*track+digit] = sum_k q[row][k] d[k]
-//     (uint8 x int8 -> int32, exact) for the two 128-row halves of the CTA's gate rows; meanwhile the rest of
-//     that warp sums the digit bytes of the same tiles (dp4a) into offset * sum_k h_k per track
-//     (W = scale*q + offset), the term the integer MMA cannot carry;
-//   * 8 (or 16) epilogue warps read TMEM (lane = gate row, ordered 4*unit + gate so one quad of lanes holds
-//     the four gates of a unit), add the input projection and the offset term, apply the activations,
-//     transpose inside the quad so each lane owns one (unit, track), update c and h, and write the three
-//     digit bytes of the new h straight into this CTA's own tile; a named barrier later, 8 lanes of the
-//     shipper warp send the tile to the 7 peers with bulk DSMEM copies (cp.async.bulk shared::cta ->
-//     shared::cluster) whose bytes are counted on the peer's mbarrier: async proxy end to end;
-//   * the MMA warp posts expect_tx for the 7 peer tiles, waits, and issues the next step's MMAs.
+//   * one elected thread issues tcgen05.mma kind::i8: D[row][16*digit+track] = sum_k q[row][k] d[k]
+//     (uint8 x int8 -> int32, exact) for the two 128-row halves of the CTA's gate rows;
+//   * offset * sum_k h_k per track (W = scale*q + offset: the term the integer MMA cannot carry) comes from the digit
+//     bytes themselves: the shipper warp sums its CTA's own tile with dp4a and ships the 16 partial sums on a second
+//     mbarrier, a helper warp adds the 8 CTAs' partials while the MMAs run;
+//   * 8 epilogue warps read TMEM with the 16x256b shape.  TMEM lane (gate row) 8*gate + unit' inside each 32-lane
+//     quadrant and B row 16*digit + track make that shape hand thread (unit', c) all four gates and all three digits of
+//     its unit for four tracks: no exchange between lanes.  They add the input projection and the offset term, apply the
+//     activations, update c and h, and write the three digit bytes of the new h straight into this CTA's own tile; a
+//     named barrier later, 8 lanes of the shipper warp send the tile to the 7 peers with bulk DSMEM copies
+//     (cp.async.bulk shared::cta -> shared::cluster) whose bytes are counted on the peer's mbarrier: async proxy end
+//     to end;
+//   * the MMA warp posts expect_tx for the 7 peer tiles, waits, and issues the next step's MMAs;
+//   * the MMA warp and two helper warps rebuild h from the shipped digits and write the layer output (fp16 hi/lo planes
+//     for the next GEMM) off the critical path.
 // There is no cluster-wide barrier in the loop; two h buffers per half alternate by step parity.
 // h / c are loaded from and stored to the session so the state streams across segments (lstm.cpp:160-161).
-// The input projection arrives gate-interleaved (column 4*unit + gate per direction), so a warp's 32 gate
-// rows are one 128-byte line.
+// The input projection arrives gate-interleaved (column 4*unit + gate per direction): one 16-byte load per (unit, track).
 #include "common.cuh"
 #include "kernels.cuh"
 #include "tc_common.cuh"
