@@ -52,3 +52,39 @@ def gtest_rand_waveform() -> np.ndarray:
 
 def load_golden():
     return np.load(GOLDEN)
+
+
+# ---- multi-segment whole-track case: the reference CLI (umx.cpp:26-295) on a 100 s track = 3 segments, the last one short ----
+MS_HIDDEN = 32
+MS_SECONDS = 100
+MS_N = MS_SECONDS * 44100
+MS_GOLDEN = os.path.join(ROOT, "tests", "golden", "ref_cli_multiseg.npz")
+
+
+def multiseg_model_bytes() -> bytes:
+    return synth.make_ggml(hidden=MS_HIDDEN, seed=4321)
+
+
+def multiseg_audio() -> np.ndarray:
+    return synth.make_audio(MS_N, seed=7)
+
+
+def multiseg_indices(n: int = MS_N, shift: int = 4033) -> np.ndarray:
+    """Output samples kept in the golden file: every 499th, plus 256-sample windows around every place where the segment
+    recombination changes regime (start / peak / end of each triangular window, in trimmed output coordinates) and the track ends."""
+    seg, stride = 2646000, 1984500
+    marks = [0, n - 1]
+    for k in range(0, (n + 22050 - shift + stride - 1) // stride):
+        for p in (k * stride, k * stride + seg // 2, k * stride + seg):
+            marks.append(p - shift)
+    idx = set(range(0, n, 499))
+    for m in marks:
+        idx.update(i for i in range(m - 128, m + 128) if 0 <= i < n)
+    return np.array(sorted(idx), dtype=np.int64)
+
+
+def parse_cli_plan(stdout: str):
+    """[(offset, chunk_length)] from the lines the reference prints at umx.cpp:220-222."""
+    import re
+
+    return [(int(a), int(b)) for a, b in re.findall(r"offset: (\d+), chunk shape: \(2, (\d+)\)", stdout)]

@@ -111,3 +111,20 @@ def test_live_against_compiled_reference(tmp_path):
     for t in range(4):
         assert np.array_equal(rm.tensor("fc2_w", t), om.t[t]["fc2.weight"].T)
         assert np.array_equal(rm.tensor("lstm_ih_w", t, 2, 0), om.t[t]["lstm.weight_ih_l2"].T)
+
+
+@pytest.mark.slow
+def test_demix_multisegment_matches_reference_cli():
+    """umx.cpp:99-295 end to end on THREE segments (the last one 459,017 samples): O.demix against the four WAVs the reference's
+    own CLI wrote for the same 100 s track (tests/golden/make_golden_multiseg.py), and the integer segment table against the lines
+    the CLI printed (umx.cpp:220-222).  ~1 minute of numpy."""
+    g = np.load(gi.MS_GOLDEN)
+    L = O.shifted_length(gi.MS_N, O.DEFAULT_SHIFT_OFFSET)
+    assert O.segment_plan(L) == [tuple(int(v) for v in row) for row in g["plan"]]  # bit-exact indexing
+    got = O.demix(O.load_model(gi.multiseg_model_bytes()), gi.multiseg_audio())
+    assert got.shape == (4, 2, gi.MS_N)
+    want = g["stems"]
+    sub = got[:, :, g["idx"]]
+    err = float(np.abs(sub - want).max())
+    sdr = float(10 * np.log10((want.astype(np.float64) ** 2).sum() / ((sub - want).astype(np.float64) ** 2).sum()))
+    assert err < 1e-5 and sdr > 100.0, (err, sdr)
