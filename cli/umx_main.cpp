@@ -119,6 +119,12 @@ bool load_audio(const std::string &path, std::vector<float> &interleaved, size_t
 // write_audio_file (src/dsp.cpp:75-101): float32 stereo 44.1 kHz
 bool write_wav(const std::string &path, const float *interleaved, size_t n)
 {
+    // RIFF sizes are 32-bit: longer than ~3.1 hours of float stereo does not fit a plain WAV
+    if (n > (size_t)(UINT32_MAX - 36) / (2 * sizeof(float)))
+    {
+        std::cerr << "[ERROR] " << path << ": " << n << " samples do not fit a RIFF/WAV file (4 GiB limit)" << std::endl;
+        return false;
+    }
     FILE *f = std::fopen(path.c_str(), "wb");
     if (!f)
         return false;
@@ -138,10 +144,8 @@ bool write_wav(const std::string &path, const float *interleaved, size_t n)
     w16(34, 32);
     std::memcpy(h + 36, "data", 4);
     w32(40, data_bytes);
-    std::fwrite(h, 1, sizeof h, f);
-    std::fwrite(interleaved, 1, data_bytes, f);
-    std::fclose(f);
-    return true;
+    const bool ok = std::fwrite(h, 1, sizeof h, f) == sizeof h && std::fwrite(interleaved, 1, data_bytes, f) == data_bytes;
+    return (std::fclose(f) == 0) && ok;
 }
 } // namespace
 

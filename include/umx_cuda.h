@@ -115,7 +115,9 @@ int umx_cuda_target_mags(umx_cuda_session *s, const float *spec, float *mags);
  * n_tracks > UMX_WIENER_NOALLOC_MAX_TRACKS is rejected.  The first call on each device resolves the
  * array's address: make it before any stream capture.  All calls share the array (its max|X| slots are
  * re-zeroed per call, the rest is overwritten before use), so calls that overlap on the GPU race:
- * serialise them. */
+ * serialise them.  The buffers and the stream must belong to the device that is current at the call (checked);
+ * F <= 1,048,560.  The resolved address is cached per device for the life of the process: after a
+ * cudaDeviceReset the library must be reloaded before this entry point is used again. */
 #define UMX_WIENER_NOALLOC_MAX_TRACKS 2
 int umx_cuda_wiener_noalloc(const float *d_mix, const float *d_mags, int F, int n_tracks, float *d_out, void *stream);
 

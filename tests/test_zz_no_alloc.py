@@ -69,3 +69,39 @@ def test_wiener_noalloc_two_tracks_and_limit(umx):
         umx.wiener_noalloc(d_mix.data_ptr(), d_mags.data_ptr(), F, 3, d_out.data_ptr(), None)
     with pytest.raises(umx.UmxCudaError):
         umx.wiener_noalloc(d_mix.data_ptr(), d_mags.data_ptr(), 0, 1, d_out.data_ptr(), None)
+
+
+def test_wiener_noalloc_own_stream_back_to_back(umx):
+    """Two calls of different sizes queued on the caller's own stream with no host synchronisation between them: the second
+    starts from the first one's scratch contents and is ordered behind it by the stream alone."""
+    torch = pytest.importorskip("torch")
+    dev = torch.device("cuda", 0)
+    st = torch.cuda.Stream(device=dev)
+    cases = [_case(15, 33, 40.0), _case(16, 9, 0.25)]
+    bufs = []
+    for spec, mags in cases:
+        F = spec.shape[1]
+        bufs.append((torch.from_numpy(_internal(spec)).to(dev), torch.from_numpy(_internal(mags)).to(dev),
+                     torch.full((4, F, 2, NB), float("nan"), dtype=torch.complex64, device=dev)))
+    torch.cuda.synchronize()
+    for (spec, _), (d_mix, d_mags, d_out) in zip(cases, bufs):
+        umx.wiener_noalloc(d_mix.data_ptr(), d_mags.data_ptr(), spec.shape[1], 1, d_out.data_ptr(), st.cuda_stream)
+    st.synchronize()
+    for (spec, mags), (_, _, d_out) in zip(cases, bufs):
+        want, _ = umx.wiener_filter(spec, mags)
+        got = np.moveaxis(d_out.cpu().numpy(), -3, -2)
+        assert np.isfinite(got).all() and rel(got, want) < 1e-4
+
+
+def test_wiener_noalloc_rejects_foreign_memory_and_huge_F(umx):
+    torch = pytest.importorskip("torch")
+    dev = torch.device("cuda", 0)
+    spec, mags = _case(17, 4, 1.0)
+    d_mix = torch.from_numpy(_internal(spec)).to(dev)
+    d_mags = torch.from_numpy(_internal(mags)).to(dev)
+    d_out = torch.empty((4, 4, 2, NB), dtype=torch.complex64, device=dev)
+    host = np.zeros(16, np.float32)
+    with pytest.raises(umx.UmxCudaError, match="device memory"):  # a host pointer where a device buffer is expected
+        umx.wiener_noalloc(host.ctypes.data, d_mags.data_ptr(), 4, 1, d_out.data_ptr(), None)
+    with pytest.raises(umx.UmxCudaError, match="1,048,560"):  # rejected before anything is queued
+        umx.wiener_noalloc(d_mix.data_ptr(), d_mags.data_ptr(), 16 * 65535 + 1, 1, d_out.data_ptr(), None)

@@ -4,6 +4,7 @@
 #include <cuda_fp16.h>
 #include <cstdint>
 #include <cstdio>
+#include <mutex>
 #include <string>
 
 namespace umx
@@ -60,6 +61,31 @@ void set_error(const std::string &msg);
             return -2;                                                                        \
         }                                                                                     \
     } while (0)
+
+// One-time set-up per device (cudaFuncSetAttribute, device attributes) that may be reached from several host threads at once:
+// sessions may be driven from different threads (umx_cuda.h).  `done` is only read and written under the mutex.
+struct PerDeviceOnce
+{
+    std::mutex mu;
+    bool done[64] = {};
+    template <typename Fn>
+    int run(Fn &&fn) // fn(dev) returns 0 on success; it runs once per device, later calls only take the lock
+    {
+        int dev = 0;
+        if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64)
+        {
+            set_error("cudaGetDevice failed or device index >= 64");
+            return -1;
+        }
+        std::lock_guard<std::mutex> lk(mu);
+        if (done[dev])
+            return 0;
+        if (int rc = fn(dev))
+            return rc;
+        done[dev] = true;
+        return 0;
+    }
+};
 
 inline int ceil_div(long a, long b) { return (int)((a + b - 1) / b); }
 

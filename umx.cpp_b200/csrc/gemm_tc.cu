@@ -519,19 +519,18 @@ int launch_gemm_tc(const GemmBatch &batch, int terms, cudaStream_t st)
     }
     P.total_tiles = tiles;
 
+    static PerDeviceOnce once;
     static int sm_count[64] = {};
-    static bool attr_set[64] = {};
+    if (int rc = once.run([&](int dev) {
+            UMX_CUDA_OK(cudaFuncSetAttribute(gemm_tc_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
+            UMX_CUDA_OK(cudaFuncSetAttribute(gemm_tc_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
+            UMX_CUDA_OK(cudaFuncSetAttribute(gemm_tc_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
+            UMX_CUDA_OK(cudaDeviceGetAttribute(&sm_count[dev], cudaDevAttrMultiProcessorCount, dev));
+            return 0;
+        }))
+        return rc;
     int dev = 0;
     UMX_CUDA_OK(cudaGetDevice(&dev));
-    dev &= 63;
-    if (!attr_set[dev])
-    {
-        UMX_CUDA_OK(cudaFuncSetAttribute(gemm_tc_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
-        UMX_CUDA_OK(cudaFuncSetAttribute(gemm_tc_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
-        UMX_CUDA_OK(cudaFuncSetAttribute(gemm_tc_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
-        UMX_CUDA_OK(cudaDeviceGetAttribute(&sm_count[dev], cudaDevAttrMultiProcessorCount, dev));
-        attr_set[dev] = true;
-    }
     const int grid = std::min(tiles, sm_count[dev]);
     if (terms == 1)
         gemm_tc_kernel<1><<<grid, kThreads, kSmemBytes, st>>>(P);

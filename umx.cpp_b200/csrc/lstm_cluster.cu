@@ -728,14 +728,12 @@ template <int TP, int NG>
 int launch_tp(const ClusterArgs &P, cudaStream_t st)
 {
     const int groups = ceil_div(P.a.n_tracks, TP * NG); // clusters per (target, direction)
-    static bool attr_set[64] = {};
-    int dev = 0;
-    UMX_CUDA_OK(cudaGetDevice(&dev));
-    if (!attr_set[dev & 63])
-    {
-        UMX_CUDA_OK(cudaFuncSetAttribute(lstm_cluster_kernel<TP, NG>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
-        attr_set[dev & 63] = true;
-    }
+    static PerDeviceOnce once; // one per template instantiation
+    if (int rc = once.run([&](int) {
+            UMX_CUDA_OK(cudaFuncSetAttribute(lstm_cluster_kernel<TP, NG>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
+            return 0;
+        }))
+        return rc;
     dim3 grid(kC, 2 * P.a.target_count, groups);
     lstm_cluster_kernel<TP, NG><<<grid, kThreads, kSmemBytes, st>>>(P);
     UMX_CUDA_OK(cudaGetLastError());

@@ -49,25 +49,73 @@ bool gunzip(const uint8_t *src, size_t n, std::vector<uint8_t> &out)
     return rc == Z_STREAM_END;
 }
 
+// The 43 tensor names of one target, matched EXACTLY (the reference's loader compares whole names too and answers anything
+// else with "failed to load", src/model.cpp:240-546).  kind: what the tensor is; layer/dir only for lstm.* names.
+struct TensorId
+{
+    enum Kind { kUnknown, kInAffine, kOutAffine, kFc1, kFc2, kFc3, kBn12, kBn3, kWih, kWhh, kLstmBias } kind = kUnknown;
+    int layer = 0, dir = 0;
+};
+
+TensorId identify_tensor(const std::string &name)
+{
+    TensorId id;
+    static const char *bn_fields[] = {"weight", "bias", "running_mean", "running_var"};
+    if (name == "input_mean" || name == "input_scale") id.kind = TensorId::kInAffine;
+    else if (name == "output_mean" || name == "output_scale") id.kind = TensorId::kOutAffine;
+    else if (name == "fc1.weight") id.kind = TensorId::kFc1;
+    else if (name == "fc2.weight") id.kind = TensorId::kFc2;
+    else if (name == "fc3.weight") id.kind = TensorId::kFc3;
+    else if (name.size() > 4 && name.compare(0, 2, "bn") == 0 && name[3] == '.' && name[2] >= '1' && name[2] <= '3')
+    {
+        for (const char *f : bn_fields)
+            if (name.compare(4, std::string::npos, f) == 0)
+                id.kind = name[2] == '3' ? TensorId::kBn3 : TensorId::kBn12;
+    }
+    else if (name.compare(0, 5, "lstm.") == 0)
+    { // lstm.{weight_ih,weight_hh,bias_ih,bias_hh}_l{0,1,2}[_reverse]
+        static const struct { const char *stem; TensorId::Kind kind; } stems[] = {
+            {"lstm.weight_ih_l", TensorId::kWih}, {"lstm.weight_hh_l", TensorId::kWhh},
+            {"lstm.bias_ih_l", TensorId::kLstmBias}, {"lstm.bias_hh_l", TensorId::kLstmBias}};
+        for (const auto &st : stems)
+        {
+            const size_t len = std::strlen(st.stem);
+            if (name.compare(0, len, st.stem) != 0 || name.size() <= len)
+                continue;
+            const char digit = name[len];
+            const std::string tail = name.substr(len + 1);
+            if (digit < '0' || digit > '2' || (!tail.empty() && tail != "_reverse"))
+                continue;
+            id.kind = st.kind;
+            id.layer = digit - '0';
+            id.dir = tail.empty() ? 0 : 1;
+        }
+    }
+    return id;
+}
+
 struct Expect
 {
     int d0, d1; // ggml dims (reversed PyTorch shape); d1 == 1 for vectors
 };
 
 // shapes the reference allocates (src/model.cpp:140-186); 0 = unknown tensor name
-Expect expected_shape(const std::string &name, int H)
+Expect expected_shape(const TensorId &id, int H)
 {
-    if (name == "input_mean" || name == "input_scale") return {kBinsCropped, 1};
-    if (name == "output_mean" || name == "output_scale") return {kBins, 1};
-    if (name == "fc1.weight") return {kFc1In, H};
-    if (name.rfind("bn1.", 0) == 0 || name.rfind("bn2.", 0) == 0) return {H, 1};
-    if (name.rfind("bn3.", 0) == 0) return {kFc3Out, 1};
-    if (name == "fc2.weight") return {2 * H, H};
-    if (name == "fc3.weight") return {H, kFc3Out};
-    if (name.rfind("lstm.weight_ih", 0) == 0) return {H, 2 * H};
-    if (name.rfind("lstm.weight_hh", 0) == 0) return {H / 2, 2 * H};
-    if (name.rfind("lstm.bias", 0) == 0) return {2 * H, 1};
-    return {0, 0};
+    switch (id.kind)
+    {
+    case TensorId::kInAffine: return {kBinsCropped, 1};
+    case TensorId::kOutAffine: return {kBins, 1};
+    case TensorId::kFc1: return {kFc1In, H};
+    case TensorId::kBn12: return {H, 1};
+    case TensorId::kBn3: return {kFc3Out, 1};
+    case TensorId::kFc2: return {2 * H, H};
+    case TensorId::kFc3: return {H, kFc3Out};
+    case TensorId::kWih: return {H, 2 * H};
+    case TensorId::kWhh: return {H / 2, 2 * H};
+    case TensorId::kLstmBias: return {2 * H, 1};
+    default: return {0, 0};
+    }
 }
 
 template <typename T>
@@ -186,10 +234,16 @@ int model_create(const void *bytes, size_t n, int device, Model **out)
             set_error("load_umx_model: more than 4 targets in model file");
             return fail(-3);
         }
-        const Expect ex = expected_shape(name, H);
+        const TensorId id = identify_tensor(name);
+        const Expect ex = expected_shape(id, H);
         if (ex.d0 == 0)
         {
             set_error("load_umx_model: failed to load " + name); // src/model.cpp:541-546
+            return fail(-3);
+        }
+        if (m->t[target].f32.count(name))
+        {
+            set_error("load_umx_model: tensor '" + name + "' appears twice in target " + std::to_string(target));
             return fail(-3);
         }
         if (ne[0] != ex.d0 || ne[1] != ex.d1)
@@ -197,8 +251,9 @@ int model_create(const void *bytes, size_t n, int device, Model **out)
             set_error("load_single_matrix: tensor '" + name + "' has wrong size in model file"); // :582-591
             return fail(-3);
         }
-        const bool wide = name.find("bn2") != std::string::npos || name.find("bn3") != std::string::npos ||
-                          name.find("fc2") != std::string::npos || name.find("fc3") != std::string::npos;
+        // u16 payloads: fc2 / fc3 / bn2.* / bn3.* (src/model.cpp:390-539 call load_single_matrix_uint16 for exactly these)
+        const bool wide = id.kind == TensorId::kFc2 || id.kind == TensorId::kFc3 || id.kind == TensorId::kBn3 ||
+                          (id.kind == TensorId::kBn12 && name[2] == '2');
         const long count = (long)ne[0] * ne[1];
         const size_t nbytes = (size_t)count * (wide ? 2 : 1);
         if (pos + nbytes > n)
@@ -242,7 +297,7 @@ int model_create(const void *bytes, size_t n, int device, Model **out)
                 dt.host[i] = std::fmaf((float)q, scale, offset);
             }
         }
-        if (name.rfind("lstm.weight_ih", 0) == 0)
+        if (id.kind == TensorId::kWih)
         { // keep the quantised input weights: the GEMM consumes the exact integers
             uint8_t *q = nullptr;
             if (dev_alloc(m, &q, nbytes))
@@ -250,12 +305,11 @@ int model_create(const void *bytes, size_t n, int device, Model **out)
             if (cudaMemcpy(q, staging, nbytes, cudaMemcpyDeviceToDevice) != cudaSuccess)
                 return fail(-1);
             whh_raw[target][name] = q;
-            const int layer = name[name.find("_l") + 2] - '0';
-            const int dir = name.find("_reverse") != std::string::npos ? 1 : 0;
+            const int layer = id.layer, dir = id.dir; // validated by identify_tensor: layer in 0..2
             m->t[target].wih_scale[layer][dir] = scale;
             m->t[target].wih_offset[layer][dir] = offset;
         }
-        if (name.rfind("lstm.weight_hh", 0) == 0)
+        if (id.kind == TensorId::kWhh)
         { // keep the quantised recurrent weights
             uint8_t *q = nullptr;
             if (dev_alloc(m, &q, nbytes))
@@ -263,8 +317,7 @@ int model_create(const void *bytes, size_t n, int device, Model **out)
             if (cudaMemcpy(q, staging, nbytes, cudaMemcpyDeviceToDevice) != cudaSuccess)
                 return fail(-1);
             whh_raw[target][name] = q;
-            const int layer = name[name.find("_l") + 2] - '0';
-            const int dir = name.find("_reverse") != std::string::npos ? 1 : 0;
+            const int layer = id.layer, dir = id.dir; // validated by identify_tensor: layer in 0..2
             m->t[target].whh_scale[layer][dir] = scale;
             m->t[target].whh_offset[layer][dir] = offset;
         }

@@ -426,15 +426,13 @@ int launch_istft(const float2 *stems, long stem_stride, int n_stems, const Istft
 {
     const int F = n_buf / kHop + 1;
     const int G = kIstftFramesPerCta;
-    static bool attr_set[64] = {};
-    int dev = 0;
-    UMX_CUDA_OK(cudaGetDevice(&dev));
     const size_t smem = sizeof(float2) * (kFftSmemFloat2 + 4096);
-    if (!attr_set[dev & 63])
-    {
-        UMX_CUDA_OK(cudaFuncSetAttribute(istft_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        attr_set[dev & 63] = true;
-    }
+    static PerDeviceOnce once;
+    if (int rc = once.run([&](int) {
+            UMX_CUDA_OK(cudaFuncSetAttribute(istft_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+            return 0;
+        }))
+        return rc;
     dim3 grid(ceil_div(F, G), n_stems, n_tracks);
     istft_kernel<<<grid, 256, smem, st>>>(stems, stem_stride, F, G, d_tracks, n_buf, stem_begin);
     UMX_CUDA_OK(cudaGetLastError());

@@ -329,6 +329,8 @@ extern "C" int umx_cuda_wiener_noalloc(const float *d_mix, const float *d_mags, 
     using namespace umx;
     UMX_CHECK(d_mix && d_mags && d_out, "umx_cuda_wiener_noalloc: null pointer");
     UMX_CHECK(F >= 1, "umx_cuda_wiener_noalloc: F must be >= 1");
+    // the filter pass walks frames in blocks of 16 along grid.y (<= 65535): reject up front, before anything is queued
+    UMX_CHECK(F <= 16 * 65535, "umx_cuda_wiener_noalloc: F must be <= 1,048,560 frames");
     if (n_tracks < 1 || n_tracks > kNoAllocMaxTracks)
     {
         set_error("umx_cuda_wiener_noalloc: n_tracks = " + std::to_string(n_tracks) + " is outside [1, " +
@@ -340,6 +342,35 @@ extern "C" int umx_cuda_wiener_noalloc(const float *d_mix, const float *d_mags, 
     if (int rc = noalloc_scratch(&scratch))
         return rc;
     cudaStream_t st = static_cast<cudaStream_t>(stream);
+    // The scratch array used is the CURRENT device's copy: the caller's buffers and stream must live on that device.
+    // (Queries only; nothing here allocates.)
+    int cur_dev = 0;
+    UMX_CUDA_OK(cudaGetDevice(&cur_dev));
+    for (const void *p : {static_cast<const void *>(d_mix), static_cast<const void *>(d_mags), static_cast<const void *>(d_out)})
+    {
+        cudaPointerAttributes pa{};
+        if (cudaPointerGetAttributes(&pa, p) != cudaSuccess || (pa.type != cudaMemoryTypeDevice && pa.type != cudaMemoryTypeManaged) ||
+            (pa.type == cudaMemoryTypeDevice && pa.device != cur_dev))
+        {
+            cudaGetLastError();
+            set_error("umx_cuda_wiener_noalloc: d_mix, d_mags and d_out must be device memory of the current device (" +
+                      std::to_string(cur_dev) + ")");
+            return -2;
+        }
+    }
+#if CUDART_VERSION >= 12080
+    if (st != nullptr && st != cudaStreamLegacy && st != cudaStreamPerThread)
+    {
+        int st_dev = -1;
+        if (cudaStreamGetDevice(st, &st_dev) == cudaSuccess && st_dev != cur_dev)
+        {
+            set_error("umx_cuda_wiener_noalloc: the stream belongs to device " + std::to_string(st_dev) +
+                      " but device " + std::to_string(cur_dev) + " is current");
+            return -2;
+        }
+        cudaGetLastError();
+    }
+#endif
     const long e = (long)n_tracks * F * 2 * kBins; // elements of one [n_tracks*F][2][2049] tensor
     float *maxabs = scratch + kNaMaxabsOff;
     // the only state that must start at zero: the atomicMax targets
