@@ -46,6 +46,7 @@ constexpr int kEpiPitch = 20; // floats per row of the transpose tile: 16 column
 constexpr int kEpiBytesPerWarp = 32 * kEpiPitch * 4;
 constexpr int kEpiChunks = BN / 2 / 16; // 16-column chunks per epilogue warp and tile
 constexpr int kMaxStages = 6;
+constexpr int kSched = 4; // depth of the tile-index ring between the producer and the MMA / epilogue warps
 constexpr int kSmemBytes = 4 * 49152 + kEpiWarps * kEpiBytesPerWarp + 256 + 1024; // stages + epilogue + barriers + align slack
 constexpr int kThreads = 32 * (2 + kEpiWarps);
 constexpr uint32_t kTmemCols = 512;
@@ -75,6 +76,7 @@ struct alignas(64) TcParams
     CUtensorMap a_hi[kMaxGemmProblems], a_lo[kMaxGemmProblems], b_hi[kMaxGemmProblems], b_lo[kMaxGemmProblems];
     TcProblem p[kMaxGemmProblems];
     int count, total_tiles, terms, pad_;
+    int *tile_counter; // null: tiles blockIdx.x, + gridDim.x, ...; else: tiles drawn from this global counter (zero at launch)
 };
 
 __device__ __forceinline__ float act_apply(float v, int act)
@@ -182,6 +184,10 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_tc_kernel(const __grid_const
     const uint32_t full0 = smem_u32(bars), empty0 = smem_u32(bars + kMaxStages);
     const uint32_t tfull0 = smem_u32(bars + 2 * kMaxStages), tempty0 = smem_u32(bars + 2 * kMaxStages + 2);
     uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + 2 * kMaxStages + 4);
+    // tile schedule: the producer publishes the index of every tile this CTA works on (or -1: no more) through a small ring, so
+    // the tiles may come from a global counter (CTAs that get their SM late, or share the GPU with other kernels, take fewer)
+    const uint32_t sfull0 = smem_u32(bars + 2 * kMaxStages + 5), sempty0 = sfull0 + 8 * kSched;
+    volatile int *sched_tile = reinterpret_cast<volatile int *>(bars + 2 * kMaxStages + 5 + 2 * kSched);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
@@ -196,6 +202,11 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_tc_kernel(const __grid_const
         {
             mbar_init(tfull0 + 8 * i, 1);
             mbar_init(tempty0 + 8 * i, kEpiWarps);
+        }
+        for (int i = 0; i < kSched; ++i)
+        {
+            mbar_init(sfull0 + 8 * i, 1);
+            mbar_init(sempty0 + 8 * i, 1 + kEpiWarps); // the MMA thread and one lane per epilogue warp
         }
         fence_barrier_init();
     }
@@ -241,12 +252,35 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_tc_kernel(const __grid_const
         {
             int stage = 0;
             uint32_t phase = 0;
-            for (int tile = blockIdx.x; tile < P.total_tiles; tile += gridDim.x)
+            int sslot = 0;
+            uint32_t sphase = 0;
+            int *const counter = P.tile_counter;
+            int cand = counter ? atomicAdd(counter, 1) : (int)blockIdx.x;
+            for (;;)
             {
-                int pi, m0, n0;
-                locate(tile, pi, m0, n0);
-                if (!needed(pi, m0))
-                    continue;
+                // next tile that has to be computed (row tiles beyond every chunk are skipped here, once, for all warp roles)
+                int tile = -1, pi = 0, m0 = 0, n0 = 0;
+                while (cand < P.total_tiles)
+                {
+                    locate(cand, pi, m0, n0);
+                    const int c = cand;
+                    cand = counter ? atomicAdd(counter, 1) : cand + (int)gridDim.x; // the next draw is in flight during this tile's loads
+                    if (needed(pi, m0))
+                    {
+                        tile = c;
+                        break;
+                    }
+                }
+                mbar_wait(sempty0 + 8 * sslot, sphase ^ 1);
+                sched_tile[sslot] = tile;
+                mbar_arrive(sfull0 + 8 * sslot);
+                if (++sslot == kSched)
+                {
+                    sslot = 0;
+                    sphase ^= 1;
+                }
+                if (tile < 0)
+                    break;
                 const int kblocks = (P.p[pi].K + BK - 1) / BK;
                 for (int kb = 0; kb < kblocks; ++kb)
                 {
@@ -278,12 +312,22 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_tc_kernel(const __grid_const
             uint32_t phase = 0;
             int acc = 0;
             uint32_t acc_phase = 0;
-            for (int tile = blockIdx.x; tile < P.total_tiles; tile += gridDim.x)
+            int sslot = 0;
+            uint32_t sphase = 0;
+            for (;;)
             {
+                mbar_wait(sfull0 + 8 * sslot, sphase);
+                const int tile = sched_tile[sslot];
+                mbar_arrive(sempty0 + 8 * sslot);
+                if (++sslot == kSched)
+                {
+                    sslot = 0;
+                    sphase ^= 1;
+                }
+                if (tile < 0)
+                    break;
                 int pi, m0, n0;
                 locate(tile, pi, m0, n0);
-                if (!needed(pi, m0))
-                    continue;
                 const int kiters = (P.p[pi].K + BK - 1) / BK;
                 // a ragged last column tile only pays for the columns it has (N of the MMA in steps of 16)
                 const uint32_t idesc = idesc_f16_f32acc(BM, min(BN, (P.p[pi].N - n0 + 15) & ~15));
@@ -336,12 +380,24 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_tc_kernel(const __grid_const
         const int sub = lane >> 2, c4 = (lane & 3) * 4;
         int acc = 0;
         uint32_t acc_phase = 0;
-        for (int tile = blockIdx.x; tile < P.total_tiles; tile += gridDim.x)
+        int sslot = 0;
+        uint32_t sphase = 0;
+        for (;;)
         {
+            mbar_wait(sfull0 + 8 * sslot, sphase);
+            const int tile = sched_tile[sslot];
+            __syncwarp();
+            if (lane == 0)
+                mbar_arrive(sempty0 + 8 * sslot);
+            if (++sslot == kSched)
+            {
+                sslot = 0;
+                sphase ^= 1;
+            }
+            if (tile < 0)
+                break;
             int pi, m0, n0;
             locate(tile, pi, m0, n0);
-            if (!needed(pi, m0))
-                continue;
             // hoist the problem description into registers once per tile
             const int M = P.p[pi].M, N = P.p[pi].N, ldo = P.p[pi].ldo, act = P.p[pi].act, n_group = P.p[pi].n_group;
             const long gstride = P.p[pi].group_stride;
@@ -471,7 +527,7 @@ int make_map(CUtensorMap *map, const __half *ptr, int K, int rows, int ld, int b
 }
 } // namespace
 
-int launch_gemm_tc(const GemmBatch &batch, int terms, cudaStream_t st)
+int launch_gemm_tc(const GemmBatch &batch, int terms, cudaStream_t st, int *tile_counter)
 {
     UMX_CHECK(batch.count >= 1 && batch.count <= kMaxGemmProblems, "gemm_tc: bad problem count");
     UMX_CHECK(terms >= 1 && terms <= 3, "gemm_tc: terms must be 1..3");
@@ -518,6 +574,9 @@ int launch_gemm_tc(const GemmBatch &batch, int terms, cudaStream_t st)
         tiles += p.m_tiles * p.n_tiles;
     }
     P.total_tiles = tiles;
+    P.tile_counter = tile_counter;
+    if (tile_counter) // the queue starts at zero for every launch (stream-ordered, 4 bytes)
+        UMX_CUDA_OK(cudaMemsetAsync(tile_counter, 0, sizeof(int), st));
 
     static PerDeviceOnce once;
     static int sm_count[64] = {};

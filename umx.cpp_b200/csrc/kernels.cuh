@@ -99,7 +99,9 @@ struct GemmBatch
 
 int launch_gemm_simt(const GemmBatch &batch, cudaStream_t st);
 // terms: 1 = A_hi*B_hi ; 2 = + A_lo*B_hi ; 3 = + A_hi*B_lo
-int launch_gemm_tc(const GemmBatch &batch, int terms, cudaStream_t st);
+// tile_counter (optional, device int): tiles are drawn from it at run time instead of the static blockIdx stride, so a launch that
+// shares the GPU with other kernels finishes as soon as the CTAs that did get an SM have worked through all tiles
+int launch_gemm_tc(const GemmBatch &batch, int terms, cudaStream_t st, int *tile_counter = nullptr);
 
 // ---- lstm ----------------------------------------------------------------------------------------
 struct LstmLayerArgs

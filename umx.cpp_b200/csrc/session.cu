@@ -24,41 +24,49 @@ int salloc(Session *s, T **p, size_t count, bool zero = false)
 } // namespace
 
 // ---- measurement -----------------------------------------------------------------------------------
-StageScope::StageScope(Session *s_, const char *stage) : s(s_)
+// Stage timers are CUDA event pairs on the stream the stage is launched to.  The events come from a pool that only grows, so a
+// profiled call creates no events once the pool is warm; with profiling off nothing is recorded at all.
+static cudaEvent_t take_timer_event(Session *s)
+{
+    if (s->timer_cursor == s->timer_pool.size())
+    {
+        cudaEvent_t e;
+        cudaEventCreate(&e);
+        s->timer_pool.push_back(e);
+    }
+    return s->timer_pool[s->timer_cursor++];
+}
+StageScope::StageScope(Session *s_, const char *stage, cudaStream_t st_) : s(s_), st(st_ ? st_ : s_->st)
 {
     if (!s->profiling)
         return;
     StageTimer t;
     t.stage = stage;
-    cudaEventCreate(&t.a);
-    cudaEventCreate(&t.b);
-    cudaEventRecord(t.a, s->st);
+    t.a = take_timer_event(s);
+    t.b = take_timer_event(s);
+    cudaEventRecord(t.a, st);
     s->timers.push_back(t);
     idx = (int)s->timers.size() - 1;
 }
 StageScope::~StageScope()
 {
     if (idx >= 0)
-        cudaEventRecord(s->timers[idx].b, s->st);
+        cudaEventRecord(s->timers[idx].b, st);
 }
 
 void session_begin_profile(Session *s)
 {
     s->launches = 0;
     s->stage_ms.clear();
-    for (auto &t : s->timers)
-    {
-        cudaEventDestroy(t.a);
-        cudaEventDestroy(t.b);
-    }
     s->timers.clear();
+    s->timer_cursor = 0;
 }
 
 int session_end_profile(Session *s)
 {
     if (!s->profiling)
         return 0;
-    UMX_CUDA_OK(cudaStreamSynchronize(s->st));
+    UMX_CUDA_OK(cudaStreamSynchronize(s->st)); // every internal stream has been joined into s->st by the caller
     for (auto &t : s->timers)
     {
         float ms = 0.f;
@@ -91,53 +99,68 @@ int session_create(Model *m, int max_tracks, int n_buf, Session **out)
         session_destroy(s);
         return rc;
     };
-    if (cudaStreamCreateWithFlags(&s->own_st, cudaStreamNonBlocking) != cudaSuccess)
+    // Streams.  Priorities (greatest first): the deepest LSTM layer — oldest segment in flight — then layer 1, layer 0, the
+    // front stage (STFT, fc1), and last the post stage, which is HBM-bound and fills whatever the others leave idle.
+    int prio_lo = 0, prio_hi = 0;
+    cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi);
+    auto prio = [&](int rank_from_top) { return std::min(prio_lo, prio_hi + rank_from_top); };
+    bool ok = cudaStreamCreateWithFlags(&s->own_st, cudaStreamNonBlocking) == cudaSuccess &&
+              cudaStreamCreateWithFlags(&s->st_in, cudaStreamNonBlocking) == cudaSuccess &&
+              cudaStreamCreateWithFlags(&s->st_out, cudaStreamNonBlocking) == cudaSuccess &&
+              cudaStreamCreateWithPriority(&s->st_post, cudaStreamNonBlocking, prio_lo) == cudaSuccess &&
+              cudaStreamCreateWithPriority(&s->st_front, cudaStreamNonBlocking, prio(3)) == cudaSuccess &&
+              cudaStreamCreateWithPriority(&s->st_comm, cudaStreamNonBlocking, prio_hi) == cudaSuccess &&
+              cudaEventCreateWithFlags(&s->desc_copied, cudaEventDisableTiming) == cudaSuccess;
+    for (int l = 0; ok && l < 3; ++l)
+        for (int g = 0; ok && g < kTargets; ++g)
+            ok = cudaStreamCreateWithPriority(&s->st_lane[l][g], cudaStreamNonBlocking, prio(2 - l)) == cudaSuccess;
+    if (!ok)
     {
         set_error("session_create: cudaStreamCreate failed");
         return fail(-1);
     }
     s->st = s->own_st;
-    if (cudaStreamCreateWithFlags(&s->st_in, cudaStreamNonBlocking) != cudaSuccess ||
-        cudaStreamCreateWithFlags(&s->st_out, cudaStreamNonBlocking) != cudaSuccess ||
-        [&] { // lowest priority: the post stage should only take what the network stage leaves idle
-            int lo = 0, hi = 0;
-            cudaDeviceGetStreamPriorityRange(&lo, &hi);
-            return cudaStreamCreateWithPriority(&s->st_post, cudaStreamNonBlocking, lo);
-        }() != cudaSuccess)
-    {
-        set_error("session_create: cudaStreamCreate failed");
-        return fail(-1);
-    }
     int rc = 0;
-    rc |= salloc(s, &s->spec_buf[0], M * 2 * kBins);
-    rc |= salloc(s, &s->spec_buf[1], M * 2 * kBins);
+    for (int i = 0; i < Session::kSpecRing; ++i)
+    {
+        rc |= salloc(s, &s->spec_ring[i], M * 2 * kBins);
+        rc |= salloc(s, &s->maxabs_ring[i], (size_t)s->T, true);
+    }
     rc |= salloc(s, &s->xh, M * kFc1InPad, true); // pad columns stay zero
     rc |= salloc(s, &s->xl, M * kFc1InPad, true);
-    rc |= salloc(s, &s->act_h, 4 * M * 2 * H);
-    rc |= salloc(s, &s->act_l, 4 * M * 2 * H);
-    for (int i = 0; i < 2; ++i)
+    for (int i = 0; i < Session::kActRing; ++i)
     {
-        rc |= salloc(s, &s->lb_h[i], 4 * M * H);
-        rc |= salloc(s, &s->lb_l[i], 4 * M * H);
+        rc |= salloc(s, &s->act_ring_h[i], 4 * M * 2 * H);
+        rc |= salloc(s, &s->act_ring_l[i], 4 * M * 2 * H);
     }
-    rc |= salloc(s, &s->xproj, 4 * M * 4 * H);
-    rc |= salloc(s, &s->rowsum, 4 * M);
+    for (int l = 0; l < 2; ++l)
+        for (int i = 0; i < Session::kLbRing; ++i)
+        {
+            rc |= salloc(s, &s->lb_ring_h[l][i], 4 * M * H);
+            rc |= salloc(s, &s->lb_ring_l[l][i], 4 * M * H);
+        }
+    for (int l = 0; l < 3; ++l)
+    {
+        rc |= salloc(s, &s->xproj_l[l], 4 * M * 4 * H);
+        rc |= salloc(s, &s->rowsum_l[l], 4 * M);
+    }
     rc |= salloc(s, &s->fc2_h, 4 * M * H);
     rc |= salloc(s, &s->fc2_l, 4 * M * H);
-    rc |= salloc(s, &s->mask_buf[0], 4 * M * kMaskLd);
-    rc |= salloc(s, &s->mask_buf[1], 4 * M * kMaskLd);
+    for (int i = 0; i < Session::kMaskRing; ++i)
+        rc |= salloc(s, &s->mask_ring[i], 4 * M * kMaskLd);
     rc |= salloc(s, &s->stems, 4 * M * 2 * kBins);
-    rc |= salloc(s, &s->maxabs_buf[0], (size_t)s->T, true);
-    rc |= salloc(s, &s->maxabs_buf[1], (size_t)s->T, true);
     rc |= salloc(s, &s->partials, (size_t)s->T * kWienerChunks * 20 * kBins);
     rc |= salloc(s, &s->stats, (size_t)s->T * 16 * kBins);
     rc |= salloc(s, &s->h_state, (size_t)s->T * 3 * 8 * s->Hh, true);
     rc |= salloc(s, &s->c_state, (size_t)s->T * 3 * 8 * s->Hh, true);
+    rc |= salloc(s, &s->tile_counters, 16, true);
     if (rc)
         return fail(-1);
-    s->spec = s->spec_buf[0];
-    s->mask = s->mask_buf[0];
-    s->maxabs = s->maxabs_buf[0];
+    s->spec = s->spec_ring[0];
+    s->mask = s->mask_ring[0];
+    s->maxabs = s->maxabs_ring[0];
+    s->act_h = s->act_ring_h[0];
+    s->act_l = s->act_ring_l[0];
     s->acc_pool.assign(s->T, nullptr);
     s->in_pool.assign(s->T, nullptr);
     s->out_pool.assign(s->T, nullptr);
@@ -154,19 +177,26 @@ int ensure_desc_capacity(Session *s, int segs)
 {
     if (segs <= s->seg_cap)
         return 0;
+    UMX_CUDA_OK(cudaDeviceSynchronize()); // nothing may still be reading the old tables
     if (s->d_stft)
         cudaFree(s->d_stft);
     if (s->d_istft)
         cudaFree(s->d_istft);
     if (s->d_final)
         cudaFree(s->d_final);
+    if (s->h_desc)
+        cudaFreeHost(s->h_desc);
     s->d_stft = nullptr;
     s->d_istft = nullptr;
     s->d_final = nullptr;
+    s->h_desc = nullptr;
     s->seg_cap = 0;
-    UMX_CUDA_OK(cudaMalloc(&s->d_stft, sizeof(StftTrack) * (size_t)segs * s->T));
-    UMX_CUDA_OK(cudaMalloc(&s->d_istft, sizeof(IstftTrack) * (size_t)segs * s->T));
-    UMX_CUDA_OK(cudaMalloc(&s->d_final, sizeof(FinalizeTrack) * (size_t)segs * s->T));
+    const size_t n = (size_t)segs * s->T;
+    UMX_CUDA_OK(cudaMalloc(&s->d_stft, sizeof(StftTrack) * n));
+    UMX_CUDA_OK(cudaMalloc(&s->d_istft, sizeof(IstftTrack) * n));
+    UMX_CUDA_OK(cudaMalloc(&s->d_final, sizeof(FinalizeTrack) * n));
+    s->h_desc_bytes = (sizeof(StftTrack) + sizeof(IstftTrack) + sizeof(FinalizeTrack)) * n;
+    UMX_CUDA_OK(cudaMallocHost(&s->h_desc, s->h_desc_bytes));
     s->seg_cap = segs;
     return 0;
 }
@@ -176,8 +206,7 @@ void session_destroy(Session *s)
     if (!s)
         return;
     cudaSetDevice(s->device);
-    if (s->st)
-        cudaStreamSynchronize(s->st);
+    cudaDeviceSynchronize();
     session_begin_profile(s);
     tp_destroy(s);
     for (void *p : s->allocs)
@@ -191,16 +220,21 @@ void session_destroy(Session *s)
     cudaFree(s->d_stft);
     cudaFree(s->d_istft);
     cudaFree(s->d_final);
+    if (s->h_desc)
+        cudaFreeHost(s->h_desc);
     for (auto e : s->ev_pool)
         cudaEventDestroy(e);
-    if (s->st_in)
-        cudaStreamDestroy(s->st_in);
-    if (s->st_out)
-        cudaStreamDestroy(s->st_out);
-    if (s->st_post)
-        cudaStreamDestroy(s->st_post);
-    if (s->own_st)
-        cudaStreamDestroy(s->own_st);
+    for (auto e : s->timer_pool)
+        cudaEventDestroy(e);
+    if (s->desc_copied)
+        cudaEventDestroy(s->desc_copied);
+    for (cudaStream_t st : {s->st_in, s->st_out, s->st_post, s->st_front, s->st_comm, s->own_st})
+        if (st)
+            cudaStreamDestroy(st);
+    for (auto &row : s->st_lane)
+        for (cudaStream_t st : row)
+            if (st)
+                cudaStreamDestroy(st);
     delete s;
 }
 
@@ -214,12 +248,12 @@ int session_reset(Session *s)
 }
 
 // ---- the network (src/inference.cpp:58-186) ------------------------------------------------------------
-static int run_gemm(Session *s, const GemmBatch &b, int terms = 0)
+static int run_gemm(Session *s, const GemmBatch &b, cudaStream_t st, int terms = 0, int *tile_counter = nullptr)
 {
     s->launches++;
     if (s->gemm_impl == 1)
-        return launch_gemm_simt(b, s->st);
-    return launch_gemm_tc(b, terms ? terms : s->gemm_terms, s->st);
+        return launch_gemm_simt(b, st);
+    return launch_gemm_tc(b, terms ? terms : s->gemm_terms, st, tile_counter);
 }
 
 static cudaEvent_t take_event(Session *s, size_t &cursor)
@@ -231,6 +265,210 @@ static cudaEvent_t take_event(Session *s, size_t &cursor)
         s->ev_pool.push_back(e);
     }
     return s->ev_pool[cursor++];
+}
+
+// the buffers the in-order schedules and the kernel-level entry points use: slot 0 of every ring, and the current spec / mask
+static NetView current_view(Session *s)
+{
+    NetView v{};
+    v.spec = s->spec;
+    v.maxabs = s->maxabs;
+    v.mask = s->mask;
+    v.act_h = s->act_ring_h[0];
+    v.act_l = s->act_ring_l[0];
+    for (int l = 0; l < 2; ++l)
+    {
+        v.lb_h[l] = s->lb_ring_h[l][0];
+        v.lb_l[l] = s->lb_ring_l[l][0];
+    }
+    v.chunks = s->cur_chunks;
+    return v;
+}
+
+// fc1 + BN1 + tanh for this rank's targets in one GEMM (inference.cpp:75-99)
+static int net_fc1(Session *s, const NetView &v, int n_tracks, cudaStream_t st, int *tile_counter)
+{
+    const int H = s->H;
+    const long M = (long)n_tracks * s->F, Mc = s->Mcap;
+    Model *m = s->m;
+    StageScope sc(s, "gemm", st);
+    GemmBatch b{};
+    b.count = 1;
+    GemmProblem &p = b.p[0];
+    const size_t t0 = (size_t)s->tp_t0; // target-parallel ranks only compute their own targets' columns
+    p.A = {s->xh, s->xl, kFc1InPad, 0};
+    p.B = {m->fc1_hi + t0 * H * kFc1InPad, m->fc1_lo + t0 * H * kFc1InPad, kFc1InPad, 0};
+    p.M = (int)M;
+    p.N = s->tp_nt * H;
+    p.K = kFc1InPad;
+    p.act = kActTanh;
+    p.chunks = v.chunks; // all-zero frames beyond the chunk: only the first one is computed
+    p.rows_per_track = s->F;
+    p.extra_rows = 1;
+    p.alpha = m->fc1_alpha + t0 * H;
+    p.beta = m->fc1_beta + t0 * H;
+    p.out_hi = v.act_h + t0 * Mc * 2 * H;
+    p.out_lo = v.act_l + t0 * Mc * 2 * H;
+    p.ldo = 2 * H;
+    p.n_group = H;
+    p.group_stride = Mc * 2 * H;
+    return run_gemm(s, b, st, 0, tile_counter);
+}
+
+// W_ih x + b_ih + b_hh of layer l for all frames (the GEMM half of src/lstm.cpp:132-136), targets [t0, t0 + nt)
+static int net_layer_gemm(Session *s, const NetView &v, int l, int n_tracks, int t0, int nt, cudaStream_t st, int *tile_counter)
+{
+    const int H = s->H;
+    const long M = (long)n_tracks * s->F, Mc = s->Mcap;
+    Model *m = s->m;
+    StageScope sc(s, "gemm", st);
+    GemmBatch b{};
+    b.count = nt;
+    for (int i = 0; i < nt; ++i)
+    {
+        const int t = t0 + i;
+        GemmProblem &p = b.p[i];
+        if (l == 0)
+            p.A = {v.act_h + (size_t)t * Mc * 2 * H, v.act_l + (size_t)t * Mc * 2 * H, 2 * H, 0};
+        else
+            p.A = {v.lb_h[l - 1] + (size_t)t * Mc * H, v.lb_l[l - 1] + (size_t)t * Mc * H, H, 0};
+        // W_ih as exact integers (one fp16 plane): x.W = scale*(x.q) + offset*rowsum(x) + bias
+        s->launches++;
+        if (int rc = launch_rowsum(p.A.hi, p.A.lo, M, H, p.A.ld, s->rowsum_l[l] + (size_t)t * Mc, st))
+            return rc;
+        p.B = {m->t[t].wih_q[l], nullptr, H, 0};
+        p.M = (int)M;
+        p.N = 4 * H;
+        p.K = H;
+        p.act = kActNone;
+        if (l == 0)
+        { // the first all-zero frame's input projection stands for all later ones (LstmLayerArgs::chunks)
+            p.chunks = v.chunks;
+            p.rows_per_track = s->F;
+            p.extra_rows = 1;
+        }
+        p.alpha = m->t[t].wih_alpha[l];
+        p.gamma = m->t[t].wih_gamma[l];
+        p.rowvec = s->rowsum_l[l] + (size_t)t * Mc;
+        p.beta = m->t[t].wih_beta[l];
+        p.out_f32 = s->xproj_l[l] + (size_t)t * Mc * 4 * H;
+        p.ldo = 4 * H;
+        p.n_group = 4 * H;
+        p.group_stride = 0;
+    }
+    return run_gemm(s, b, st, std::min(s->gemm_terms, 2), tile_counter); // no weight lo plane: at most hi*q + lo*q
+}
+
+// the recurrence of layer l (src/lstm.cpp:112-174) for targets [t0, t0 + nt); h/c stream on in the session
+static int net_layer_rec(Session *s, const NetView &v, int l, int n_tracks, int t0, int nt, bool want_f32, cudaStream_t st)
+{
+    const int H = s->H, Hh = s->Hh;
+    const long Mc = s->Mcap;
+    Model *m = s->m;
+    StageScope sc(s, "lstm", st);
+    LstmLayerArgs a{};
+    for (int t = 0; t < kTargets; ++t)
+        for (int d = 0; d < 2; ++d)
+        {
+            a.whh_q[t][d] = m->t[t].whh_q[l][d];
+            a.whh_scale[t][d] = m->t[t].whh_scale[l][d];
+            a.whh_offset[t][d] = m->t[t].whh_offset[l][d];
+        }
+    a.xproj = s->xproj_l[l];
+    a.xproj_target_stride = Mc * 4 * H;
+    a.h_state = s->h_state + (size_t)l * 8 * Hh;
+    a.c_state = s->c_state + (size_t)l * 8 * Hh;
+    a.state_track_stride = 3 * 8 * Hh;
+    if (l < 2)
+    {
+        a.out_hi = v.lb_h[l];
+        a.out_lo = v.lb_l[l];
+        a.out_target_stride = Mc * H;
+        a.ldo = H;
+        a.col_offset = 0;
+    }
+    else
+    {
+        a.out_hi = v.act_h;
+        a.out_lo = v.act_l;
+        a.out_target_stride = Mc * 2 * H;
+        a.ldo = 2 * H;
+        a.col_offset = H;
+    }
+    a.out_f32 = (want_f32 && l == 2) ? s->lstm_f32 : nullptr;
+    a.out_f32_target_stride = Mc * H;
+    a.F = s->F;
+    a.Hh = Hh;
+    a.n_tracks = n_tracks;
+    a.target_begin = t0;
+    a.target_count = nt;
+    a.chunks = l == 0 ? v.chunks : nullptr;
+    s->launches++;
+    if (s->lstm_impl == 0)
+    {
+        UMX_CHECK(lstm_cluster_supported(Hh), "the cluster recurrence kernel does not support this hidden size: set option lstm_impl = 1");
+        const uint8_t *img[kTargets][2];
+        for (int t = 0; t < kTargets; ++t)
+            for (int d = 0; d < 2; ++d)
+                img[t][d] = m->t[t].whh_img[l][d];
+        return launch_lstm_cluster(a, img, st);
+    }
+    return launch_lstm_simple(a, st);
+}
+
+// skip concat + fc2 + BN2 + ReLU (inference.cpp:118-140), fc3 + BN3 + output affine + ReLU -> mask (inference.cpp:143-166)
+static int net_head(Session *s, const NetView &v, int n_tracks, int t0, int nt, cudaStream_t st, int *tile_counter)
+{
+    const int H = s->H;
+    const long M = (long)n_tracks * s->F, Mc = s->Mcap;
+    Model *m = s->m;
+    StageScope sc(s, "gemm", st);
+    {
+        GemmBatch b{};
+        b.count = nt;
+        for (int t = t0; t < t0 + nt; ++t)
+        {
+            GemmProblem &p = b.p[t - t0];
+            p.A = {v.act_h + (size_t)t * Mc * 2 * H, v.act_l + (size_t)t * Mc * 2 * H, 2 * H, 0};
+            p.B = {m->t[t].fc2_hi, m->t[t].fc2_lo, 2 * H, 0};
+            p.M = (int)M;
+            p.N = H;
+            p.K = 2 * H;
+            p.act = kActRelu;
+            p.alpha = m->t[t].fc2_alpha;
+            p.beta = m->t[t].fc2_beta;
+            p.chunks = v.chunks;
+            p.rows_per_track = s->F;
+            p.out_hi = s->fc2_h + (size_t)t * Mc * H;
+            p.out_lo = s->fc2_l + (size_t)t * Mc * H;
+            p.ldo = H;
+            p.n_group = H;
+            p.group_stride = 0;
+        }
+        if (int rc = run_gemm(s, b, st, 0, tile_counter))
+            return rc;
+    }
+    GemmBatch b{};
+    b.count = nt;
+    for (int t = t0; t < t0 + nt; ++t)
+    {
+        GemmProblem &p = b.p[t - t0];
+        p.A = {s->fc2_h + (size_t)t * Mc * H, s->fc2_l + (size_t)t * Mc * H, H, 0};
+        p.B = {m->t[t].fc3_hi, m->t[t].fc3_lo, H, 0};
+        p.M = (int)M;
+        p.N = kFc3Out;
+        p.K = H;
+        p.act = kActRelu;
+        p.alpha = m->t[t].fc3_alpha;
+        p.beta = m->t[t].fc3_beta;
+        p.chunks = v.chunks;
+        p.rows_per_track = s->F;
+        p.out_f32 = v.mask + (size_t)t * Mc * kMaskLd;
+        p.ldo = kMaskLd;
+        p.n_group = kMaskLd;
+        p.group_stride = 0;
+    }
+    return run_gemm(s, b, st, 0, tile_counter);
 }
 
 static int session_back_part(Session *s, int seg, int n_tracks, int part);
@@ -274,16 +512,14 @@ static int slot_run_next(Session *s)
                 const FinalizeTrack &f = j.fin_host[i];
                 if (f.i_end <= f.i_begin)
                     continue;
-                for (int stem = begin; stem < begin + count; ++stem)
+                // the finished range of `count` stems of this track in one strided copy
+                const size_t o = 2 * ((size_t)begin * j.n_samples[i] + f.i_begin);
+                if (cudaMemcpy2DAsync(j.host_out[i] + o, sizeof(float2) * (size_t)j.n_samples[i], j.d_out[i] + o,
+                                      sizeof(float2) * (size_t)j.n_samples[i], sizeof(float2) * (size_t)(f.i_end - f.i_begin),
+                                      (size_t)count, cudaMemcpyDeviceToHost, s->st_out) != cudaSuccess)
                 {
-                    const size_t o = 2 * ((size_t)stem * j.n_samples[i] + f.i_begin);
-                    if (cudaMemcpyAsync(j.host_out[i] + o, j.d_out[i] + o, sizeof(float2) * (size_t)(f.i_end - f.i_begin),
-                                        cudaMemcpyDeviceToHost, s->st_out) != cudaSuccess)
-                    {
-                        set_error("umx_cuda_demix: device-to-host copy failed");
-                        rc = -1;
-                        break;
-                    }
+                    set_error("umx_cuda_demix: device-to-host copy failed");
+                    rc = -1;
                 }
             }
         }
@@ -298,101 +534,14 @@ static int slot_run_next(Session *s)
 
 int session_lstm(Session *s, int n_tracks, int target_begin, int target_count, bool want_f32)
 {
-    const int H = s->H, Hh = s->Hh;
-    const long M = (long)n_tracks * s->F, Mc = s->Mcap;
-    Model *m = s->m;
+    const NetView v = current_view(s);
     for (int l = 0; l < 3; ++l)
     {
-        {
-            StageScope sc(s, "gemm");
-            GemmBatch b{};
-            b.count = target_count;
-            for (int i = 0; i < target_count; ++i)
-            {
-                const int t = target_begin + i;
-                GemmProblem &p = b.p[i];
-                if (l == 0)
-                    p.A = {s->act_h + (size_t)t * Mc * 2 * H, s->act_l + (size_t)t * Mc * 2 * H, 2 * H, 0};
-                else
-                    p.A = {s->lb_h[(l - 1) & 1] + (size_t)t * Mc * H, s->lb_l[(l - 1) & 1] + (size_t)t * Mc * H, H, 0};
-                // W_ih as exact integers (one fp16 plane): x.W = scale*(x.q) + offset*rowsum(x) + bias
-                s->launches++;
-                if (int rc = launch_rowsum(p.A.hi, p.A.lo, M, H, p.A.ld, s->rowsum + (size_t)t * Mc, s->st))
-                    return rc;
-                p.B = {m->t[t].wih_q[l], nullptr, H, 0};
-                p.M = (int)M;
-                p.N = 4 * H;
-                p.K = H;
-                p.act = kActNone;
-                if (l == 0)
-                { // the first all-zero frame's input projection stands for all later ones (LstmLayerArgs::chunks)
-                    p.chunks = s->cur_chunks;
-                    p.rows_per_track = s->F;
-                    p.extra_rows = 1;
-                }
-                p.alpha = m->t[t].wih_alpha[l];
-                p.gamma = m->t[t].wih_gamma[l];
-                p.rowvec = s->rowsum + (size_t)t * Mc;
-                p.beta = m->t[t].wih_beta[l];
-                p.out_f32 = s->xproj + (size_t)t * Mc * 4 * H;
-                p.ldo = 4 * H;
-                p.n_group = 4 * H;
-                p.group_stride = 0;
-            }
-            if (int rc = run_gemm(s, b, std::min(s->gemm_terms, 2))) // no weight lo plane: at most hi*q + lo*q
-                return rc;
-        }
+        if (int rc = net_layer_gemm(s, v, l, n_tracks, target_begin, target_count, s->st, nullptr))
+            return rc;
         if (int rc = slot_run_next(s)) // a part of the previous segment's post stage shares the GPU with this recurrence
             return rc;
-        StageScope sc(s, "lstm");
-        LstmLayerArgs a{};
-        for (int t = 0; t < kTargets; ++t)
-            for (int d = 0; d < 2; ++d)
-            {
-                a.whh_q[t][d] = m->t[t].whh_q[l][d];
-                a.whh_scale[t][d] = m->t[t].whh_scale[l][d];
-                a.whh_offset[t][d] = m->t[t].whh_offset[l][d];
-            }
-        a.xproj = s->xproj;
-        a.xproj_target_stride = Mc * 4 * H;
-        a.h_state = s->h_state + (size_t)l * 8 * Hh;
-        a.c_state = s->c_state + (size_t)l * 8 * Hh;
-        a.state_track_stride = 3 * 8 * Hh;
-        if (l < 2)
-        {
-            a.out_hi = s->lb_h[l & 1];
-            a.out_lo = s->lb_l[l & 1];
-            a.out_target_stride = Mc * H;
-            a.ldo = H;
-            a.col_offset = 0;
-        }
-        else
-        {
-            a.out_hi = s->act_h;
-            a.out_lo = s->act_l;
-            a.out_target_stride = Mc * 2 * H;
-            a.ldo = 2 * H;
-            a.col_offset = H;
-        }
-        a.out_f32 = (want_f32 && l == 2) ? s->lstm_f32 : nullptr;
-        a.out_f32_target_stride = Mc * H;
-        a.F = s->F;
-        a.Hh = Hh;
-        a.n_tracks = n_tracks;
-        a.target_begin = target_begin;
-        a.target_count = target_count;
-        a.chunks = l == 0 ? s->cur_chunks : nullptr;
-        s->launches++;
-        if (s->lstm_impl == 0 && lstm_cluster_supported(Hh))
-        {
-            const uint8_t *img[kTargets][2];
-            for (int t = 0; t < kTargets; ++t)
-                for (int d = 0; d < 2; ++d)
-                    img[t][d] = m->t[t].whh_img[l][d];
-            if (int rc = launch_lstm_cluster(a, img, s->st))
-                return rc;
-        }
-        else if (int rc = launch_lstm_simple(a, s->st))
+        if (int rc = net_layer_rec(s, v, l, n_tracks, target_begin, target_count, want_f32, s->st))
             return rc;
     }
     return 0;
@@ -400,99 +549,26 @@ int session_lstm(Session *s, int n_tracks, int target_begin, int target_count, b
 
 int session_network(Session *s, int n_tracks)
 {
-    const int H = s->H;
-    const long M = (long)n_tracks * s->F, Mc = s->Mcap;
-    Model *m = s->m;
-    { // fc1 + BN1 + tanh for all four targets in one GEMM (inference.cpp:75-99)
-        StageScope sc(s, "gemm");
-        GemmBatch b{};
-        b.count = 1;
-        GemmProblem &p = b.p[0];
-        const size_t t0 = (size_t)s->tp_t0; // target-parallel ranks only compute their own targets' columns
-        p.A = {s->xh, s->xl, kFc1InPad, 0};
-        p.B = {m->fc1_hi + t0 * H * kFc1InPad, m->fc1_lo + t0 * H * kFc1InPad, kFc1InPad, 0};
-        p.M = (int)M;
-        p.N = s->tp_nt * H;
-        p.K = kFc1InPad;
-        p.act = kActTanh;
-        p.chunks = s->cur_chunks; // all-zero frames beyond the chunk: only the first one is computed
-        p.rows_per_track = s->F;
-        p.extra_rows = 1;
-        p.alpha = m->fc1_alpha + t0 * H;
-        p.beta = m->fc1_beta + t0 * H;
-        p.out_hi = s->act_h + t0 * Mc * 2 * H;
-        p.out_lo = s->act_l + t0 * Mc * 2 * H;
-        p.ldo = 2 * H;
-        p.n_group = H;
-        p.group_stride = Mc * 2 * H;
-        if (int rc = run_gemm(s, b))
-            return rc;
-    }
+    const NetView v = current_view(s);
+    if (int rc = net_fc1(s, v, n_tracks, s->st, nullptr))
+        return rc;
     if (int rc = session_lstm(s, n_tracks, s->tp_t0, s->tp_nt, false))
         return rc;
-    StageScope sc(s, "gemm");
-    { // skip concat + fc2 + BN2 + ReLU (inference.cpp:118-140)
-        GemmBatch b{};
-        b.count = s->tp_nt;
-        for (int t = s->tp_t0; t < s->tp_t0 + s->tp_nt; ++t)
-        {
-            GemmProblem &p = b.p[t - s->tp_t0];
-            p.A = {s->act_h + (size_t)t * Mc * 2 * H, s->act_l + (size_t)t * Mc * 2 * H, 2 * H, 0};
-            p.B = {m->t[t].fc2_hi, m->t[t].fc2_lo, 2 * H, 0};
-            p.M = (int)M;
-            p.N = H;
-            p.K = 2 * H;
-            p.act = kActRelu;
-            p.alpha = m->t[t].fc2_alpha;
-            p.beta = m->t[t].fc2_beta;
-            p.chunks = s->cur_chunks;
-            p.rows_per_track = s->F;
-            p.out_hi = s->fc2_h + (size_t)t * Mc * H;
-            p.out_lo = s->fc2_l + (size_t)t * Mc * H;
-            p.ldo = H;
-            p.n_group = H;
-            p.group_stride = 0;
-        }
-        if (int rc = run_gemm(s, b))
-            return rc;
-    }
-    { // fc3 + BN3 + output affine + ReLU -> mask (inference.cpp:143-166)
-        GemmBatch b{};
-        b.count = s->tp_nt;
-        for (int t = s->tp_t0; t < s->tp_t0 + s->tp_nt; ++t)
-        {
-            GemmProblem &p = b.p[t - s->tp_t0];
-            p.A = {s->fc2_h + (size_t)t * Mc * H, s->fc2_l + (size_t)t * Mc * H, H, 0};
-            p.B = {m->t[t].fc3_hi, m->t[t].fc3_lo, H, 0};
-            p.M = (int)M;
-            p.N = kFc3Out;
-            p.K = H;
-            p.act = kActRelu;
-            p.alpha = m->t[t].fc3_alpha;
-            p.beta = m->t[t].fc3_beta;
-            p.chunks = s->cur_chunks;
-            p.rows_per_track = s->F;
-            p.out_f32 = s->mask + (size_t)t * Mc * kMaskLd;
-            p.ldo = kMaskLd;
-            p.n_group = kMaskLd;
-            p.group_stride = 0;
-        }
-        if (int rc = run_gemm(s, b))
-            return rc;
-    }
-    return 0;
+    return net_head(s, v, n_tracks, s->tp_t0, s->tp_nt, s->st, nullptr);
+}
+
+static int run_stft(Session *s, int seg, int n_tracks, const NetView &v, cudaStream_t st)
+{
+    StageScope sc(s, "stft", st);
+    UMX_CUDA_OK(cudaMemsetAsync(v.maxabs, 0, sizeof(float) * s->T, st));
+    s->launches++;
+    return launch_stft(s->d_stft + (size_t)seg * s->T, n_tracks, s->n_buf, v.spec, s->xh, s->xl, v.maxabs, st, s->skip_zero_frames);
 }
 
 int session_front(Session *s, int seg, int n_tracks)
 {
-    const StftTrack *dst = s->d_stft + (size_t)seg * s->T;
-    {
-        StageScope sc(s, "stft");
-        UMX_CUDA_OK(cudaMemsetAsync(s->maxabs, 0, sizeof(float) * s->T, s->st));
-        s->launches++;
-        if (int rc = launch_stft(dst, n_tracks, s->n_buf, s->spec, s->xh, s->xl, s->maxabs, s->st, s->skip_zero_frames))
-            return rc;
-    }
+    if (int rc = run_stft(s, seg, n_tracks, current_view(s), s->st))
+        return rc;
     s->cur_chunks = s->skip_zero_frames ? s->d_istft + (size_t)seg * s->T : nullptr;
     const int rc_net = session_network(s, n_tracks);
     s->cur_chunks = nullptr;
@@ -501,10 +577,34 @@ int session_front(Session *s, int seg, int n_tracks)
     if (s->tp_world > 1)
     { // the one exchange step of the target-parallel mode: every rank needs all four sources' masks
         StageScope sc(s, "allgather");
-        if (int rc = tp_allgather_masks(s))
+        if (int rc = tp_allgather_masks(s, s->mask, s->st))
             return rc;
     }
     return 0;
+}
+
+static int run_wiener(Session *s, int seg, int n_tracks, const NetView &v, cudaStream_t st)
+{
+    StageScope sc(s, "wiener", st);
+    WienerArgs w{};
+    w.spec = v.spec;
+    w.mask = v.mask;
+    w.mask_target_stride = s->Mcap * kMaskLd;
+    w.mask_ld = kMaskLd;
+    w.mask_is_mag = 0;
+    w.maxabs = v.maxabs;
+    w.partials = s->partials;
+    w.stats = s->stats;
+    w.out = s->stems;
+    w.out_stem_stride = s->Mcap * 2 * kBins;
+    w.mix_out = nullptr;
+    w.F = s->F;
+    w.n_tracks = n_tracks;
+    w.stem_begin = s->tp_t0;
+    w.stem_count = s->tp_nt;
+    w.chunks = s->d_istft + (size_t)seg * s->T;
+    s->launches += 3;
+    return launch_wiener(w, st);
 }
 
 // part 0: Wiener-EM; parts 1 and 2: iSTFT + overlap-add of the first / second half of this rank's stems
@@ -512,28 +612,7 @@ static int session_back_part(Session *s, int seg, int n_tracks, int part)
 {
     const IstftTrack *dis = s->d_istft + (size_t)seg * s->T;
     if (part == 0)
-    {
-        StageScope sc(s, "wiener");
-        WienerArgs w{};
-        w.spec = s->spec;
-        w.mask = s->mask;
-        w.mask_target_stride = s->Mcap * kMaskLd;
-        w.mask_ld = kMaskLd;
-        w.mask_is_mag = 0;
-        w.maxabs = s->maxabs;
-        w.partials = s->partials;
-        w.stats = s->stats;
-        w.out = s->stems;
-        w.out_stem_stride = s->Mcap * 2 * kBins;
-        w.mix_out = nullptr;
-        w.F = s->F;
-        w.n_tracks = n_tracks;
-        w.stem_begin = s->tp_t0;
-        w.stem_count = s->tp_nt;
-        w.chunks = dis;
-        s->launches += 3;
-        return launch_wiener(w, s->st);
-    }
+        return run_wiener(s, seg, n_tracks, current_view(s), s->st);
     const int n1 = (s->tp_nt + 1) / 2;
     const int begin = part == 1 ? s->tp_t0 : s->tp_t0 + n1, count = part == 1 ? n1 : s->tp_nt - n1;
     if (count <= 0)

@@ -17,6 +17,16 @@ struct StageTimer
     cudaEvent_t a, b;
 };
 
+// buffers one segment's pass through the network reads and writes (a slot of every ring)
+struct NetView
+{
+    float2 *spec;
+    float *maxabs, *mask;
+    __half *act_h, *act_l;
+    __half *lb_h[2], *lb_l[2];
+    const IstftTrack *chunks; // chunk descriptors of the segment (frames beyond a chunk are skipped), or null
+};
+
 struct Session
 {
     Model *m = nullptr;
@@ -29,20 +39,28 @@ struct Session
     cudaStream_t st = nullptr;      // stream every launch goes to
     cudaStream_t own_st = nullptr;  // the session's own stream (st may be replaced by a caller's)
 
-    // activations (HBM layout documented in DESIGN.md)
-    float2 *spec = nullptr;                  // [Mcap][2][2049]
+    // activations (HBM layout documented in DESIGN.md).  Buffers that cross the stages of the segment wavefront (option
+    // "pipeline" = 3) are rings indexed by segment; the plain pointers below are ring slot 0, which is what the in-order
+    // schedules and the kernel-level entry points use.
+    static constexpr int kSpecRing = 4, kActRing = 3, kLbRing = 2, kMaskRing = 2;
+    float2 *spec_ring[kSpecRing] = {};       // [Mcap][2][2049]                    STFT -> Wiener
+    float *maxabs_ring[kSpecRing] = {};      // [T]
+    __half *act_ring_h[kActRing] = {}, *act_ring_l[kActRing] = {}; // [4][Mcap][2H]  (fc1 out | lstm out)   fc1 -> fc2
+    __half *lb_ring_h[2][kLbRing] = {}, *lb_ring_l[2][kLbRing] = {}; // [layer 0/1][slot]: [4][Mcap][H] LSTM layer outputs
+    float *mask_ring[kMaskRing] = {};        // [4][Mcap][kMaskLd]                 fc3 -> Wiener
+    float *xproj_l[3] = {};                  // one input projection [4][Mcap][4H] per layer: the three layers of different
+    float *rowsum_l[3] = {};                 //   segments run side by side in the wavefront;  [4][Mcap] row sums per layer
+    float2 *spec = nullptr;                  // current slots (the in-order schedules swap spec / mask / maxabs)
     __half *xh = nullptr, *xl = nullptr;     // [Mcap][2976]
-    __half *act_h = nullptr, *act_l = nullptr; // [4][Mcap][2H]  (fc1 out | lstm out)
-    __half *lb_h[2] = {}, *lb_l[2] = {};     // [4][Mcap][H] ping-pong LSTM layer outputs
-    float *xproj = nullptr;                  // [4][Mcap][4H]
+    __half *act_h = nullptr, *act_l = nullptr; // = act_ring[0]
     __half *fc2_h = nullptr, *fc2_l = nullptr; // [4][Mcap][H]
-    float *mask = nullptr;                   // [4][Mcap][kMaskLd]
+    float *mask = nullptr;
     float2 *stems = nullptr;                 // [4][Mcap][2][2049]
     float *maxabs = nullptr;                 // [T]
     float *partials = nullptr, *stats = nullptr;
     float *h_state = nullptr, *c_state = nullptr; // [T][3][4][2][Hh]
-    float *rowsum = nullptr;                 // [4][Mcap] row sums of the LSTM layer input (exact-integer W_ih GEMM)
     float *lstm_f32 = nullptr;               // optional fp32 LSTM output (kernel-level API), [4][Mcap][H]
+    int *tile_counters = nullptr;            // [16] GEMM tile queues, one per stream of the wavefront
 
     StftTrack *d_stft = nullptr;   // descriptor arrays [seg_cap][T]
     const IstftTrack *cur_chunks = nullptr; // chunk descriptors of the segment the network is running for (frames beyond a chunk are skipped)
@@ -52,9 +70,15 @@ struct Session
     int seg_cap = 0;
     cudaStream_t st_in = nullptr, st_out = nullptr; // host<->device copy streams (overlap with compute)
     cudaStream_t st_post = nullptr;                 // Wiener/iSTFT/finalize of segment s run here while segment s+1's network runs on st
-    float2 *spec_buf[2] = {};                       // spec / mask / maxabs are double-buffered between the two stages
-    float *mask_buf[2] = {}, *maxabs_buf[2] = {};
-    int pipeline = 2;                               // option "pipeline": 0 = in order, 1 = post stage on its own low-priority stream, 2 (default) = in slots under the next segment's recurrences
+    // option "pipeline": 0 = in order, 1 = post stage on its own low-priority stream, 2 = post stage in slots under the next
+    // segment's recurrences, 3 (default) = segment wavefront: layer l of segment s+1 runs beside layer l+1 of segment s
+    int pipeline = 3;
+    int lane_targets = 1;                           // option "lane_targets": targets per recurrence launch in the wavefront (1, 2 or 4)
+    cudaStream_t st_front = nullptr, st_comm = nullptr;
+    cudaStream_t st_lane[3][kTargets] = {};         // wavefront: one stream per (LSTM layer, target group)
+    void *h_desc = nullptr;                         // pinned staging for the descriptor tables
+    size_t h_desc_bytes = 0;
+    cudaEvent_t desc_copied = nullptr;              // the previous call's descriptor upload has left the staging buffer
     std::vector<cudaEvent_t> ev_pool;
     size_t ev_cursor = 0;
     // option "pipeline" = 2: the post stage (Wiener, iSTFT, finalize) of segment s is cut into three parts that start together
@@ -89,6 +113,8 @@ struct Session
     // measurement
     bool profiling = false;
     std::vector<StageTimer> timers;
+    std::vector<cudaEvent_t> timer_pool; // timing events are created once and reused
+    size_t timer_cursor = 0;
     std::map<std::string, double> stage_ms;
     long launches = 0;
 };
@@ -116,14 +142,15 @@ int ensure_desc_capacity(Session *s, int segs);
 // tp.cu: NCCL is loaded with dlopen on first use, so the library has no link-time dependency on it
 int tp_unique_id(void *id128);
 int tp_init(Session *s, const void *id128, int rank, int world);
-int tp_allgather_masks(Session *s);
+int tp_allgather_masks(Session *s, float *mask, cudaStream_t st);
 void tp_destroy(Session *s);
 
 struct StageScope
 {
     Session *s;
     int idx = -1;
-    StageScope(Session *s_, const char *stage);
+    cudaStream_t st;
+    StageScope(Session *s_, const char *stage, cudaStream_t st_ = nullptr); // null: the session's current stream
     ~StageScope();
 };
 

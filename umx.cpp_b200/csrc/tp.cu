@@ -90,14 +90,14 @@ int tp_init(Session *s, const void *id128, int rank, int world)
     return check(n->comm_init_rank(&s->tp_comm, world, id, rank), "ncclCommInitRank");
 }
 
-int tp_allgather_masks(Session *s)
+int tp_allgather_masks(Session *s, float *mask, cudaStream_t st)
 {
     Nccl *n = nccl();
     UMX_CHECK(n != nullptr && s->tp_comm != nullptr, "target-parallel: communicator is not initialised");
     // in place: this rank's targets are one contiguous slice of the [4][Mcap][4104] mask buffer
     const size_t count = (size_t)s->tp_nt * s->Mcap * kMaskLd;
     s->launches++;
-    return check(n->all_gather(s->mask + (size_t)s->tp_t0 * s->Mcap * kMaskLd, s->mask, count, kNcclFloat32, s->tp_comm, s->st),
+    return check(n->all_gather(mask + (size_t)s->tp_t0 * s->Mcap * kMaskLd, mask, count, kNcclFloat32, s->tp_comm, st),
                  "ncclAllGather");
 }
 
