@@ -31,6 +31,8 @@ import numpy as np
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
+# one hardware work queue per stream of the segment wavefront (must be set before the CUDA context is created)
+os.environ.setdefault("CUDA_DEVICE_MAX_CONNECTIONS", "32")
 
 SR = 44100
 SEG = 2646000
@@ -109,54 +111,73 @@ def synth_model_file(tmpdir: str) -> str:
     return p
 
 
-def reference_rate(model_path: str, window_s: float, repeats: int = 1):
-    """The compiled, unmodified reference (oracle/_ref) on one bounded window through umx_inference.
-    Returns (audio-seconds advanced per wall second, seconds per window, threads)."""
+REF_SAMPLE_S = 7.5      # bounded CPU sample: one 7.5 s window = 323 of the 2584 frames of a stock window
+REF_FULL_FRAMES = 2584
+
+
+def stock_rate(t_sample_s: float, sample_frames: int, track_seconds: float):
+    """audio-s/s of the reference's STOCK path on one benched track, from the time of a bounded sample window.
+    The stock CLI runs every segment as a full 60 s / 2584-frame window however short the chunk is (umx.cpp:161-163),
+    and a track of `track_seconds` has ceil((n + 22050 - 4033) / 1,984,500) segments (umx.cpp:214); the reference's cost is linear
+    in frames (every stage is per frame; checked against one real full window by --impl reference)."""
+    n = int(track_seconds * SR)
+    segs = (n + 22050 - 4033 + STRIDE - 1) // STRIDE
+    t_window = t_sample_s * REF_FULL_FRAMES / sample_frames
+    return track_seconds / (segs * t_window), t_window, segs
+
+
+def reference_sample(model_path: str, warmup: int, steps: int, window_s: float = REF_SAMPLE_S):
+    """The compiled, unmodified reference (oracle/_ref) through umx_inference on one bounded window per step.
+    Returns (mean seconds per step, frames per window)."""
     from oracle import ref, synth
 
     rm = ref.Model(model_path)
     n_buf = int(window_s * SR)
     st = ref.LstmState(512, ref.nb_frames(n_buf))
     audio = synth.make_audio(n_buf, 7)
-    ts = []
-    for _ in range(repeats):
-        t0 = time.time()
+    for _ in range(warmup):
         ref.umx_inference(rm, st, audio, n_buf)
-        ts.append(time.time() - t0)
-    t = float(np.mean(ts))
-    # a window advances 0.75 of its length (25 % overlap, umx.cpp:180)
-    return 0.75 * window_s / t, t, os.cpu_count()
+    t0 = time.time()
+    for _ in range(steps):
+        ref.umx_inference(rm, st, audio, n_buf)
+    return (time.time() - t0) / steps, ref.nb_frames(n_buf)
 
 
 def run_reference(args, rank):
-    """--impl reference: the reference's own CPU implementation of the path, rank 0 only."""
+    """--impl reference: the reference's own CPU implementation of the path, rank 0 only.  Each step is a bounded sample (one
+    7.5 s window through umx_inference); `value` is what the STOCK path costs for the benched track (full 60 s windows), and one
+    real full window is timed after the K steps to check the extrapolation."""
     if rank != 0:
         return
-    window_s = 7.5  # bounded sample: the reference's cost is linear in frames (323 of 2584 per step)
     with tempfile.TemporaryDirectory() as td:
         mp = synth_model_file(td)
-        from oracle import ref, synth
+        dt, frames = reference_sample(mp, args.warmup, args.steps)
+        value, t_window, segs = stock_rate(dt, frames, args.track_seconds)
+        full = None
+        if not args.no_full_window:
+            from oracle import ref, synth
 
-        rm = ref.Model(mp)
-        n_buf = int(window_s * SR)
-        st = ref.LstmState(512, ref.nb_frames(n_buf))
-        audio = synth.make_audio(n_buf, 7)
-        for _ in range(args.warmup):
-            ref.umx_inference(rm, st, audio, n_buf)
-        t0 = time.time()
-        for _ in range(args.steps):
-            ref.umx_inference(rm, st, audio, n_buf)
-        dt = (time.time() - t0) / args.steps
-    value = 0.75 * window_s / dt
-    sample = (f"compiled unmodified reference (oracle/_ref, Eigen GEMM/GEMV, -O3 -march=x86-64-v3 -ffast-math): "
-              f"umx_inference on one {window_s} s window ({ref.nb_frames(n_buf)} frames) per step, synthetic UMX-L "
-              f"u8/u16 weights; a window advances 0.75 of its length")
+            rm = ref.Model(mp)
+            st = ref.LstmState(512, ref.nb_frames(SEG))
+            audio = synth.make_audio(SEG, 7)
+            t0 = time.time()
+            ref.umx_inference(rm, st, audio, SEG)
+            t_full = time.time() - t0
+            full = {"seconds_per_full_window": t_full, "value_from_full_window": args.track_seconds / (segs * t_full),
+                    "extrapolated_seconds_per_full_window": t_window}
+    cores = os.cpu_count()
+    sample = (f"compiled unmodified reference (oracle/_ref, Eigen GEMM/GEMV, -O3 -march=x86-64-v3 -ffast-math), synthetic UMX-L "
+              f"u8/u16 weights: one {REF_SAMPLE_S} s window ({frames} frames) through umx_inference per step = {dt:.2f} s; value = "
+              f"{args.track_seconds:.0f} s track / ({segs} stock windows of {REF_FULL_FRAMES} frames x {t_window:.1f} s); "
+              f"{cores} host threads available to Eigen, single-threaded in practice (SURVEY F6)")
     print(json.dumps({
         "impl": "reference", "metric": "audio-sec demixed/sec (UMX-L, 4 stems, 44.1kHz stereo)", "value": value,
         "unit": "audio-s/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt * 1e3,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": "UMX-L 4-stem full pipeline, synthetic stereo 44.1 kHz (bounded CPU sample)"},
-        "cpu_baseline": {"value": value, "unit": "audio-s/s", "cores": os.cpu_count(), "kind": "reference", "sample": sample},
+        "config": {"workload": f"UMX-L 4-stem full pipeline, synthetic {args.track_seconds:.0f} s stereo 44.1 kHz tracks, stock path "
+                               f"({segs} full 60 s windows per track), timed on a bounded sample per step"},
+        "cpu_baseline": {"value": value, "unit": "audio-s/s", "cores": cores, "kind": "reference", "sample": sample},
+        "stock_window_check": full,
         "e2e": {"value": value, "unit": "audio-s/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }))
 
@@ -171,7 +192,10 @@ def main():
     ap.add_argument("--track-seconds", type=float, default=180.0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--gemm-terms", type=int, default=0)
-    ap.add_argument("--pipeline", type=int, default=-1, help="session option: post stage of segment s on a second stream under the network of s+1")
+    ap.add_argument("--pipeline", type=int, default=-1, help="session option: 0 in order, 2 post stage under the next segment's recurrences, 3 (default) segment wavefront")
+    ap.add_argument("--lane-targets", type=int, default=0, help="session option: targets per stream of the wavefront (1, 2, 4)")
+    ap.add_argument("--no-in-order", action="store_true", help="skip the in-order pass that yields roofline_in_order")
+    ap.add_argument("--no-full-window", action="store_true", help="--impl reference: skip the one real 60 s window after the timed steps")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
@@ -203,9 +227,24 @@ def main():
         sess.set_option("gemm_terms", args.gemm_terms)
     if args.pipeline >= 0:
         sess.set_option("pipeline", args.pipeline)
+    if args.lane_targets:
+        sess.set_option("lane_targets", args.lane_targets)
+    pipeline = args.pipeline if args.pipeline >= 0 else 3
     stream = torch.cuda.current_stream()
     sess.set_stream(stream.cuda_stream)
+    # Stage timers: CUDA event pairs the library records on the launching streams.  Recording costs no synchronisation (the
+    # events are pooled and only read after the timed region), so they stay on inside the timed region.
     sess.set_profiling(True)
+
+    # pin this rank's threads to its share of the host cores: the pinned buffers below are then first touched (and the copy
+    # engines fed) from there
+    if world > 1 and hasattr(os, "sched_setaffinity"):
+        try:
+            cpus = sorted(os.sched_getaffinity(0))
+            per = max(1, len(cpus) // world)
+            os.sched_setaffinity(0, set(cpus[local_rank * per:(local_rank + 1) * per]) or set(cpus))
+        except OSError:
+            pass
 
     host_in = [torch.empty((n, 2), dtype=torch.float32).pin_memory() for _ in range(T)]
     my_tracks = sharding.shard_tracks(T * world, rank, world)  # weak scaling: every rank owns T tracks of the job
@@ -224,26 +263,43 @@ def main():
             dist.barrier()
         torch.cuda.synchronize()
 
+    def read_stages():
+        return {k: max(sess.stage_ms(k), 0.0) for k in list(ALGO) + ["finalize", "h2d", "d2h"]}
+
     for _ in range(args.warmup):
         step_device()
     sampler = ClockSampler(local_rank)
     barrier()
     sampler.start()
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    stage_ms = {k: 0.0 for k in ALGO}
     launches = 0
     ev0.record(stream)
     for _ in range(args.steps):
         step_device()
-        for k in stage_ms:
-            stage_ms[k] += max(sess.stage_ms(k), 0.0)
         launches += sess.launches()
     ev1.record(stream)
     barrier()
     clocks = sampler.stop()
     ms = ev0.elapsed_time(ev1) / args.steps
+    stage_ms = read_stages()  # the LAST timed step (the library keeps the most recent call's timers)
     audio_s, ms_max = sharding.aggregate(T * args.track_seconds, ms, dist if world > 1 else None, dev)
     value = audio_s / (ms_max / 1e3)
+
+    # ---- the same step once more with every kernel in order on one stream (outside the timed region): per-stage times that
+    # do not overlap, i.e. the numbers an ncu launch list of one step reproduces
+    stage_ms_in_order, ms_in_order = None, None
+    if not args.no_in_order:
+        sess.set_option("pipeline", 0)
+        step_device()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(stream)
+        step_device()
+        e1.record(stream)
+        torch.cuda.synchronize()
+        ms_in_order = e0.elapsed_time(e1)
+        stage_ms_in_order = read_stages()
+        sess.set_option("pipeline", pipeline)
 
     # ---- e2e: host buffers through umx_cuda_demix, copies inside the timed region ----
     host_out = [torch.empty((4, n, 2), dtype=torch.float32).pin_memory() for _ in range(T)]
@@ -257,6 +313,7 @@ def main():
         sess.demix_into(ins_np, outs_np)
     torch.cuda.synchronize()
     e2e_s = (time.perf_counter() - t0) / k_e2e
+    copy_ms = read_stages()  # busy time of the two copy streams in the last e2e step
     _, e2e_ms_max = sharding.aggregate(T * args.track_seconds, e2e_s * 1e3, dist if world > 1 else None, dev)
     e2e_value = audio_s / (e2e_ms_max / 1e3)
     checksum = float(np.abs(outs_np[0][:, ::4096]).sum())  # the result was read back
@@ -273,42 +330,63 @@ def main():
         gemm_1 = 4 * ((15.74e9 + 65.03e9 / 3) * pre + (65.03e9 * 2 / 3) * segs + (10.84e9 + 21.69e9) * post)
         work_per_track = {"stft": ALGO["stft"][1] * pre, "istft": ALGO["istft"][1] * post, "wiener": ALGO["wiener"][1] * post,
                           "gemm": gemm_1, "lstm": ALGO["lstm"][1] * segs}
-        per_stage = {}
-        for k, (bound, _) in ALGO.items():
-            t_ms = stage_ms[k] / args.steps
-            if t_ms <= 0:
-                continue
-            ach = work_per_track[k] * T / (t_ms / 1e3) / (1e9 if bound == "hbm" else 1e12)
-            per_stage[k] = {"bound": bound, "ms_per_step": t_ms, "achieved": ach, "peak": pk[bound],
-                            "unit": "GB/s" if bound == "hbm" else "TFLOP/s", "frac": ach / pk[bound]}
-        if "gemm" in per_stage:
-            # MMA work actually issued: every fp16 split pass counts (fc1/fc2/fc3: `terms` passes, W_ih: min(terms, 2) on the
-            # exact integers); SURVEY 8(d) asks for both the algorithmic and the issued utilisation of the tensor pipe
-            terms = args.gemm_terms if args.gemm_terms else 3
-            issued = 4 * (15.74e9 * terms * pre + (65.03e9 / 3) * min(terms, 2) * pre + (65.03e9 * 2 / 3) * min(terms, 2) * segs
-                          + (10.84e9 + 21.69e9) * terms * post)
-            g = per_stage["gemm"]
-            g["achieved_issued"] = issued * T / (g["ms_per_step"] / 1e3) / 1e12
-            g["frac_issued"] = g["achieved_issued"] / pk["tensor"]
-        if "lstm" in per_stage:
-            # the recurrence is a latency problem: time per dependent step is the figure of merit; the
-            # tensor-pipe fraction above is reported because the schema asks for one
-            launches_l = 3 * segs
-            per_stage["lstm"]["us_per_dependent_step"] = per_stage["lstm"]["ms_per_step"] * 1e3 / (launches_l * FRAMES)
-            per_stage["lstm"]["note"] = "latency-bound: 8-CTA clusters on 64 SMs, one MMA batch + DSMEM exchange per step"
-        # dominant kernel: gemm_tc_kernel (its two instantiations are 43 % of the GPU time in the ncu launch list of this command,
-        # profiles/r01_launches_bench_steps1_summary.txt; the recurrence kernel is 34 %).  Under the default schedule the
-        # recurrence's stage time is inflated by the post-stage kernels sharing the GPU with it, so it is not picked by time.
-        top = "gemm" if "gemm" in per_stage else (max(per_stage, key=lambda k: per_stage[k]["ms_per_step"]) if per_stage else None)
-        roofline = None
-        if top:
-            r = per_stage[top]
-            roofline = {"kernel": top, "bound": r["bound"], "achieved": r["achieved"], "peak": r["peak"], "unit": r["unit"],
-                        "frac": r["frac"], "achieved_issued": r.get("achieved_issued"), "frac_issued": r.get("frac_issued"),
-                        "us_per_dependent_step": r.get("us_per_dependent_step"), "note": r.get("note"),
-                        "traffic": TRAFFIC_32.get(top) if T == 32 else None,
-                        "traffic_unit": "DRAM bytes per launch (ncu, 32-track segment batch; see profiles/)", "peak_source": pk["src"],
-                        "share_of_step": r["ms_per_step"] / ms}
+        terms = args.gemm_terms if args.gemm_terms else 3
+        # MMA work actually issued: every fp16 split pass counts (fc1/fc2/fc3: `terms` passes, W_ih: min(terms, 2) on the exact
+        # integers); SURVEY 8(d) asks for both the algorithmic and the issued utilisation of the tensor pipe
+        issued = 4 * (15.74e9 * terms * pre + (65.03e9 / 3) * min(terms, 2) * pre + (65.03e9 * 2 / 3) * min(terms, 2) * segs
+                      + (10.84e9 + 21.69e9) * terms * post)
+
+        def stage_table(ms_by_stage):
+            tab = {}
+            for k, (bound, _) in ALGO.items():
+                t_ms = ms_by_stage.get(k, 0.0)
+                if t_ms <= 0:
+                    continue
+                ach = work_per_track[k] * T / (t_ms / 1e3) / (1e9 if bound == "hbm" else 1e12)
+                tab[k] = {"bound": bound, "ms_per_step": t_ms, "achieved": ach, "peak": pk[bound],
+                          "unit": "GB/s" if bound == "hbm" else "TFLOP/s", "frac": ach / pk[bound]}
+            if "gemm" in tab:
+                g = tab["gemm"]
+                g["achieved_issued"] = issued * T / (g["ms_per_step"] / 1e3) / 1e12
+                g["frac_issued"] = g["achieved_issued"] / pk["tensor"]
+            if "lstm" in tab:
+                # the recurrence is a latency problem: time per dependent step is the figure of merit; the
+                # tensor-pipe fraction is reported because the schema asks for one
+                tab["lstm"]["us_per_dependent_step"] = tab["lstm"]["ms_per_step"] * 1e3 / (3 * segs * FRAMES)
+                tab["lstm"]["note"] = "latency-bound: 8-CTA clusters, one MMA batch + DSMEM exchange per step"
+            return tab
+
+        # Stage times of the LAST TIMED STEP: for every stage the time during which at least one of its kernels was running
+        # (union of the CUDA-event intervals over all streams).  In the default schedule the stages share the GPU, so these
+        # overlap and each stage's rate is what it got while sharing; `roofline_in_order` below has the same kernels alone.
+        per_stage = stage_table(stage_ms)
+
+        def roofline_of(tab, step_ms):
+            if "gemm" not in tab:  # dominant kernel: gemm_tc_kernel (profiles/: largest share of the GPU time in the launch list)
+                return None
+            r = tab["gemm"]
+            return {"kernel": "gemm_tc_kernel", "bound": r["bound"], "achieved": r["achieved"], "peak": r["peak"], "unit": r["unit"],
+                    "frac": r["frac"], "achieved_issued": r.get("achieved_issued"), "frac_issued": r.get("frac_issued"),
+                    "traffic": TRAFFIC_32.get("gemm") if T == 32 else None,
+                    "traffic_unit": "DRAM bytes per launch (ncu, 32-track segment batch; see profiles/)", "peak_source": pk["src"],
+                    "share_of_step": r["ms_per_step"] / step_ms}
+
+        roofline = roofline_of(per_stage, ms)
+        in_order = None
+        if stage_ms_in_order:
+            tab = stage_table(stage_ms_in_order)
+            in_order = roofline_of(tab, ms_in_order)
+            if in_order:
+                in_order["ms_per_step_in_order"] = ms_in_order
+                in_order["stages"] = tab
+                in_order["note"] = ("one extra step with option pipeline = 0 (every kernel in order on one stream) after the timed "
+                                    "region: stage times do not overlap and match an ncu launch list of the step")
+        schedules = {0: "every kernel in order on one stream",
+                     1: "Wiener/iSTFT/finalize of segment s on a second stream",
+                     2: "Wiener/iSTFT/finalize of segment s in slots under the recurrence kernels of segment s+1",
+                     3: "segment wavefront: LSTM layer l of segment s+1 beside layer l+1 of segment s, one stream per (layer, target "
+                        "group), post stage on a low-priority stream; stage times overlap"}
+        GB = 1e9
         out = {
             "metric": "audio-sec demixed/sec (UMX-L, 4 stems, 44.1kHz stereo)", "value": value, "unit": "audio-s/s",
             "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_max, "higher_is_better": True,
@@ -319,21 +397,25 @@ def main():
                                    f"60 s segments, streaming LSTM, Wiener-EM",
                        "tracks_per_gpu": T, "segments_per_track": segs, "weights": "synthetic UMX-L u8/u16 ggml (seed 1234)",
                        "l2": "inputs and intermediates per step are far larger than L2 (>1 GB per track-segment)",
-                       "schedule": ("in order on one stream" if args.pipeline == 0 else
-                                    "Wiener/iSTFT/finalize of segment s run on a second stream under the recurrence kernels of "
-                                    "segment s+1, so the per-stage times overlap and add up to more than the step")},
+                       "schedule": schedules[pipeline], "gemm_terms": terms},
             "e2e": {"value": e2e_value, "unit": "audio-s/s", "h2d_bytes_per_step": T * n * 8, "d2h_bytes_per_step": T * n * 32,
-                    "steps": k_e2e, "checksum": checksum},
-            "gpu_launches": launches, "clocks": clocks, "roofline": roofline, "stages": per_stage,
+                    "steps": k_e2e, "ms_per_step": e2e_ms_max, "h2d_ms": copy_ms.get("h2d"), "d2h_ms": copy_ms.get("d2h"),
+                    "h2d_gbs": (T * n * 8 / GB) / (copy_ms["h2d"] / 1e3) if copy_ms.get("h2d") else None,
+                    "d2h_gbs": (T * n * 32 / GB) / (copy_ms["d2h"] / 1e3) if copy_ms.get("d2h") else None,
+                    "note": "h2d_ms / d2h_ms: busy time of this rank's two copy streams in the last e2e step",
+                    "checksum": checksum},
+            "gpu_launches": launches, "clocks": clocks, "roofline": roofline, "roofline_in_order": in_order, "stages": per_stage,
             "realtime_factor_per_gpu": value / world,
         }
         if world == 1 and not args.no_cpu_baseline:
             with tempfile.TemporaryDirectory() as td:
-                rate, t_win, cores = reference_rate(synth_model_file(td), 15.0)
-            out["cpu_baseline"] = {"value": rate, "unit": "audio-s/s", "cores": 1, "kind": "reference",
-                                   "host_cores": cores,
-                                   "sample": f"compiled unmodified reference (oracle/_ref): umx_inference on one 15 s window "
-                                             f"(646 frames) = {t_win:.1f} s; single-threaded in practice (SURVEY F6)"}
+                dt, frames = reference_sample(synth_model_file(td), 0, 3)
+            rate, t_window, rsegs = stock_rate(dt, frames, args.track_seconds)
+            out["cpu_baseline"] = {"value": rate, "unit": "audio-s/s", "cores": os.cpu_count(), "kind": "reference",
+                                   "sample": f"compiled unmodified reference (oracle/_ref): umx_inference on a {REF_SAMPLE_S} s window "
+                                             f"({frames} frames) = {dt:.2f} s, 3 repeats; value = {args.track_seconds:.0f} s track / "
+                                             f"({rsegs} stock 60 s windows x {t_window:.1f} s, cost linear in frames); "
+                                             f"{os.cpu_count()} host threads available, single-threaded in practice (SURVEY F6)"}
         print(json.dumps(out))
     if world > 1:
         dist.destroy_process_group()

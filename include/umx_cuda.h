@@ -144,7 +144,10 @@ int umx_cuda_lstm_max_active_clusters(void);
 /* Tuning knobs (documented in DESIGN.md): "gemm_terms" 1..3 fp16 split terms per tensor-core GEMM,
  * "gemm_impl" 0 = tcgen05, 1 = SIMT fp32 validation kernel, "lstm_impl" 0 = cluster kernel, 1 = simple,
  * "pipeline" 0 = every segment in order on one stream, 1 = Wiener/iSTFT/finalize of a segment on a second stream,
- * 2 (default) = the same in three parts that start with the next segment's recurrence kernels; results are identical,
+ * 2 = the same in three parts that start with the next segment's recurrence kernels, 3 (default) = segment wavefront:
+ * layer l of segment s+1 runs beside layer l+1 of segment s (the h/c carry of src/lstm.cpp:160-161 is per layer), one stream
+ * per (layer, target group) with "lane_targets" = 1, 2 or 4 targets per group (0, the default: 1 up to 16 tracks, else 4);
+ * results are identical,
  * "skip_zero_frames" 1 (default) = frames of a window beyond a short chunk are computed once (first layer) or not at all
  * (after the network), 0 = every frame of every 60 s window is computed as the reference does; results are identical. */
 int umx_cuda_session_set_option(umx_cuda_session *s, const char *name, int value);

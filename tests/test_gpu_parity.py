@@ -192,11 +192,14 @@ def test_demix_multi_segment_multi_track(umx, gemm_impl, terms):
     assert np.abs(again - got[0]).max() < 1e-6
 
 
-@pytest.mark.parametrize("mode", [1, 2])  # 2 is the default
-def test_demix_pipeline_modes_identical(umx, mode):
-    """Session option "pipeline": the post stage on a second stream (1) or in slots under the next segment's
-    recurrences (2) must give bit-identical stems to the in-order schedule, through host and device paths."""
-    hidden, n_buf = 64, 16384
+@pytest.mark.parametrize("hidden", [64, 1024])  # validation recurrence kernel / the tcgen05 cluster kernel
+@pytest.mark.parametrize("mode,lane_targets", [(1, 0), (2, 0), (3, 0), (3, 1), (3, 2), (3, 4)])  # (3, 0) is the default
+def test_demix_pipeline_modes_identical(umx, mode, lane_targets, hidden):
+    """Session option "pipeline": the post stage on a second stream (1), in slots under the next segment's recurrences (2), or
+    the segment wavefront (3: layer l of segment s+1 beside layer l+1 of segment s, one stream per layer and target group) must
+    give bit-identical stems to the in-order schedule, through the host and device paths.  Up to 7 segments per track, i.e.
+    deeper than every buffer ring of the wavefront."""
+    n_buf = 16384
     gm = umx.load_umx_model(synth.make_ggml(hidden=hidden, seed=78))
     tracks = [synth.make_audio(n, 30 + i) for i, n in enumerate((70000, 41000, 9000))]
     ref_sess = umx.Session(gm, 3, n_buf)
@@ -204,6 +207,7 @@ def test_demix_pipeline_modes_identical(umx, mode):
     want = ref_sess.demix(tracks, shift_offset=4033)
     sess = umx.Session(gm, 3, n_buf)
     sess.set_option("pipeline", mode)
+    sess.set_option("lane_targets", lane_targets)
     for _ in range(2):
         got = sess.demix(tracks, shift_offset=4033)
         for g, w in zip(got, want):

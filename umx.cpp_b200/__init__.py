@@ -16,7 +16,12 @@ from __future__ import annotations
 import ctypes as C
 import os
 
-import numpy as np
+# The segment wavefront runs on ~18 CUDA streams; with the driver's default of 8 hardware work queues several streams share a
+# queue and their kernels serialise behind each other's event waits.  Only takes effect if set before the CUDA context exists
+# (the C library sets the same default when it is loaded: csrc/capi.cu).
+os.environ.setdefault("CUDA_DEVICE_MAX_CONNECTIONS", "32")
+
+import numpy as np  # noqa: E402
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(HERE, "libumx_cuda.so")

@@ -4,11 +4,24 @@
 #include "session.h"
 
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <mutex>
 
 namespace umx
 {
+// The segment wavefront (session.cu) runs on ~18 CUDA streams.  The driver maps streams onto CUDA_DEVICE_MAX_CONNECTIONS hardware
+// work queues (default 8); streams that share a queue serialise behind each other's event waits, which undoes the wavefront.
+// Ask for 32 queues when the library is loaded, unless the host has chosen a value; it takes effect if the CUDA context of the
+// device does not exist yet (hosts that create the context first should export the variable themselves).
+namespace
+{
+struct ConnectionsDefault
+{
+    ConnectionsDefault() { setenv("CUDA_DEVICE_MAX_CONNECTIONS", "32", 0); }
+} g_connections_default;
+} // namespace
+
 static thread_local std::string g_err;
 void set_error(const std::string &msg) { g_err = msg; }
 } // namespace umx
@@ -240,6 +253,8 @@ double umx_cuda_session_stage_ms(umx_cuda_session *s, const char *stage)
 {
     if (!s || !stage)
         return -1.0;
+    if (session_resolve_profile(s->s)) // waits for the most recent call if its timers have not been read yet
+        return -1.0;
     if (std::string(stage) == "total")
     {
         double tot = 0;
@@ -255,6 +270,8 @@ int umx_cuda_session_set_stream(umx_cuda_session *s, void *stream)
 {
     UMX_CHECK(s, "umx_cuda_session_set_stream: null session");
     UMX_CUDA_OK(cudaSetDevice(s->s->device));
+    if (int rc = session_resolve_profile(s->s))
+        return rc;
     UMX_CUDA_OK(cudaStreamSynchronize(s->s->st));
     s->s->st = stream ? static_cast<cudaStream_t>(stream) : s->s->own_st;
     return 0;
@@ -292,8 +309,13 @@ int umx_cuda_session_set_option(umx_cuda_session *s, const char *name, int value
     }
     else if (n == "pipeline")
     {
-        UMX_CHECK(value >= 0 && value <= 2, "pipeline must be 0, 1 or 2");
+        UMX_CHECK(value >= 0 && value <= 3, "pipeline must be 0, 1, 2 or 3");
         s->s->pipeline = value;
+    }
+    else if (n == "lane_targets")
+    {
+        UMX_CHECK(value == 0 || value == 1 || value == 2 || value == 4, "lane_targets must be 0 (chosen by batch size), 1, 2 or 4");
+        s->s->lane_targets = value;
     }
     else if (n == "skip_zero_frames")
     {
@@ -303,6 +325,7 @@ int umx_cuda_session_set_option(umx_cuda_session *s, const char *name, int value
     else if (n == "lstm_impl")
     {
         UMX_CHECK(value == 0 || value == 1, "lstm_impl must be 0 (cluster) or 1 (simple)");
+        UMX_CHECK(value == 1 || lstm_cluster_supported(s->s->Hh), "lstm_impl = 0: the cluster recurrence kernel does not support this model's hidden size");
         s->s->lstm_impl = value;
     }
     else

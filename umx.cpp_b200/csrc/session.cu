@@ -60,19 +60,58 @@ void session_begin_profile(Session *s)
     s->stage_ms.clear();
     s->timers.clear();
     s->timer_cursor = 0;
+    s->profile_resolved = true;
+    if (s->profiling)
+    { // common time base of this call: the stages run on several streams
+        s->profile_base = take_timer_event(s);
+        cudaEventRecord(s->profile_base, s->st);
+    }
 }
 
+// Nothing is waited for here: the timers are read when somebody asks (session_resolve_profile), so a profiled call costs its
+// event records and nothing else.
 int session_end_profile(Session *s)
 {
-    if (!s->profiling)
+    s->profile_resolved = !s->profiling;
+    return 0;
+}
+
+// Per-stage time of the most recent call = length of the UNION of the stage's [start, end] intervals (stages of different
+// segments overlap in the pipelined schedules, and the wavefront runs several launches of one stage side by side).
+int session_resolve_profile(Session *s)
+{
+    if (s->profile_resolved)
         return 0;
-    UMX_CUDA_OK(cudaStreamSynchronize(s->st)); // every internal stream has been joined into s->st by the caller
+    UMX_CUDA_OK(cudaSetDevice(s->device));
+    UMX_CUDA_OK(cudaStreamSynchronize(s->st)); // every internal stream was joined into s->st at the end of the call
+    std::map<std::string, std::vector<std::pair<float, float>>> spans;
     for (auto &t : s->timers)
     {
-        float ms = 0.f;
-        UMX_CUDA_OK(cudaEventElapsedTime(&ms, t.a, t.b));
-        s->stage_ms[t.stage] += ms;
+        float a = 0.f, b = 0.f;
+        UMX_CUDA_OK(cudaEventElapsedTime(&a, s->profile_base, t.a));
+        UMX_CUDA_OK(cudaEventElapsedTime(&b, s->profile_base, t.b));
+        spans[t.stage].push_back({a, b});
     }
+    for (auto &kv : spans)
+    {
+        auto &v = kv.second;
+        std::sort(v.begin(), v.end());
+        double total = 0.0;
+        float lo = v[0].first, hi = v[0].second;
+        for (size_t i = 1; i < v.size(); ++i)
+        {
+            if (v[i].first > hi)
+            {
+                total += hi - lo;
+                lo = v[i].first;
+                hi = v[i].second;
+            }
+            else
+                hi = std::max(hi, v[i].second);
+        }
+        s->stage_ms[kv.first] = total + (hi - lo);
+    }
+    s->profile_resolved = true;
     return 0;
 }
 
@@ -94,26 +133,36 @@ int session_create(Model *m, int max_tracks, int n_buf, Session **out)
     s->H = m->hidden;
     s->Hh = m->hidden / 2;
     s->Mcap = (long)s->T * s->F;
+    if (!lstm_cluster_supported(s->Hh))
+    { // never silent: the validation kernel is ~30x slower than the cluster kernel
+        s->lstm_impl = 1;
+        static bool warned = false;
+        if (!warned)
+            fprintf(stderr, "umx_cuda: hidden_size %d has no tcgen05 cluster recurrence kernel (built for LSTM hidden 512 = UMX-L); "
+                            "this session runs the slow validation recurrence kernel (option lstm_impl = 1)\n", s->H);
+        warned = true;
+    }
     const size_t M = (size_t)s->Mcap, H = (size_t)s->H;
     auto fail = [&](int rc) {
         session_destroy(s);
         return rc;
     };
-    // Streams.  Priorities (greatest first): the deepest LSTM layer — oldest segment in flight — then layer 1, layer 0, the
-    // front stage (STFT, fc1), and last the post stage, which is HBM-bound and fills whatever the others leave idle.
+    // Streams.  Priorities (greatest first): the post stage (its kernels are short, and the finished output ranges should leave
+    // for the host as early as possible), then the deepest LSTM layer — the oldest segment in flight — layer 1, layer 0, and
+    // last the front stage (STFT, fc1) of the newest segment.
     int prio_lo = 0, prio_hi = 0;
     cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi);
     auto prio = [&](int rank_from_top) { return std::min(prio_lo, prio_hi + rank_from_top); };
     bool ok = cudaStreamCreateWithFlags(&s->own_st, cudaStreamNonBlocking) == cudaSuccess &&
               cudaStreamCreateWithFlags(&s->st_in, cudaStreamNonBlocking) == cudaSuccess &&
               cudaStreamCreateWithFlags(&s->st_out, cudaStreamNonBlocking) == cudaSuccess &&
-              cudaStreamCreateWithPriority(&s->st_post, cudaStreamNonBlocking, prio_lo) == cudaSuccess &&
-              cudaStreamCreateWithPriority(&s->st_front, cudaStreamNonBlocking, prio(3)) == cudaSuccess &&
+              cudaStreamCreateWithPriority(&s->st_post, cudaStreamNonBlocking, prio(0)) == cudaSuccess &&
+              cudaStreamCreateWithPriority(&s->st_front, cudaStreamNonBlocking, prio(4)) == cudaSuccess &&
               cudaStreamCreateWithPriority(&s->st_comm, cudaStreamNonBlocking, prio_hi) == cudaSuccess &&
               cudaEventCreateWithFlags(&s->desc_copied, cudaEventDisableTiming) == cudaSuccess;
     for (int l = 0; ok && l < 3; ++l)
         for (int g = 0; ok && g < kTargets; ++g)
-            ok = cudaStreamCreateWithPriority(&s->st_lane[l][g], cudaStreamNonBlocking, prio(2 - l)) == cudaSuccess;
+            ok = cudaStreamCreateWithPriority(&s->st_lane[l][g], cudaStreamNonBlocking, prio(3 - l)) == cudaSuccess;
     if (!ok)
     {
         set_error("session_create: cudaStreamCreate failed");
@@ -662,11 +711,15 @@ int session_infer_segment(Session *s, const float *audio, int n, float *out)
         StageScope sc(s, "h2d");
         UMX_CUDA_OK(cudaMemcpyAsync(s->in_pool[0], audio, sizeof(float2) * (size_t)n, cudaMemcpyHostToDevice, s->st));
     }
-    StftTrack a{s->in_pool[0], n, 0, n, 0};
-    IstftTrack b{s->out_pool[0], n, 0, n, 0};
-    UMX_CUDA_OK(cudaMemcpyAsync(s->d_stft, &a, sizeof a, cudaMemcpyHostToDevice, s->st));
-    UMX_CUDA_OK(cudaMemcpyAsync(s->d_istft, &b, sizeof b, cudaMemcpyHostToDevice, s->st));
-    UMX_CUDA_OK(cudaStreamSynchronize(s->st)); // descriptors live on this stack frame
+    // descriptors go through the session's pinned staging buffer: no synchronisation before the kernels are queued
+    UMX_CUDA_OK(cudaEventSynchronize(s->desc_copied)); // (a previous call's upload has long left the staging buffer)
+    StftTrack *ha = static_cast<StftTrack *>(s->h_desc);
+    IstftTrack *hb = reinterpret_cast<IstftTrack *>(ha + 1);
+    *ha = StftTrack{s->in_pool[0], n, 0, n, 0};
+    *hb = IstftTrack{s->out_pool[0], n, 0, n, 0};
+    UMX_CUDA_OK(cudaMemcpyAsync(s->d_stft, ha, sizeof *ha, cudaMemcpyHostToDevice, s->st));
+    UMX_CUDA_OK(cudaMemcpyAsync(s->d_istft, hb, sizeof *hb, cudaMemcpyHostToDevice, s->st));
+    UMX_CUDA_OK(cudaEventRecord(s->desc_copied, s->st));
     if (int rc = session_run_segment(s, 0, 1))
         return rc;
     {
@@ -679,6 +732,219 @@ int session_infer_segment(Session *s, const float *audio, int n, float *out)
 
 // ---- shift_inference + split_inference (umx.cpp:99-295) ------------------------------------------------
 static int stride_of(int n_buf) { return (int)((1 - 0.25f) * n_buf); } // umx.cpp:180
+
+// the finished range [i_begin, i_end) of every stem of this rank, one strided copy per track, on the output copy stream
+static int ship_ranges(Session *s, const FinalizeTrack *fin_host, int n_tracks, const int64_t *n_samples, float *const *d_out,
+                       float *const *host_out)
+{
+    StageScope sc(s, "d2h", s->st_out);
+    for (int i = 0; i < n_tracks; ++i)
+    {
+        const FinalizeTrack &f = fin_host[i];
+        if (f.i_end <= f.i_begin)
+            continue;
+        const size_t o = 2 * ((size_t)s->tp_t0 * n_samples[i] + f.i_begin), pitch = sizeof(float2) * (size_t)n_samples[i];
+        UMX_CUDA_OK(cudaMemcpy2DAsync(host_out[i] + o, pitch, d_out[i] + o, pitch, sizeof(float2) * (size_t)(f.i_end - f.i_begin),
+                                      (size_t)s->tp_nt, cudaMemcpyDeviceToHost, s->st_out));
+    }
+    return 0;
+}
+
+// the samples segment sg reads (original indices below sg*stride - shift + n_buf) on the input copy stream
+static int ship_inputs(Session *s, int sg, int stride, int shift_offset, int n_tracks, const int64_t *n_samples,
+                       const float *const *d_audio, const float *const *host_in, std::vector<long> &copied_in)
+{
+    StageScope sc(s, "h2d", s->st_in);
+    for (int i = 0; i < n_tracks; ++i)
+    {
+        const long need = std::max(0L, std::min((long)n_samples[i], (long)sg * stride - shift_offset + s->n_buf));
+        if (need > copied_in[i])
+        {
+            UMX_CUDA_OK(cudaMemcpyAsync(const_cast<float *>(d_audio[i]) + 2 * copied_in[i], host_in[i] + 2 * copied_in[i],
+                                        sizeof(float2) * (size_t)(need - copied_in[i]), cudaMemcpyHostToDevice, s->st_in));
+            copied_in[i] = need;
+        }
+    }
+    return 0;
+}
+
+// ---- the segment wavefront (option "pipeline" = 3) ----------------------------------------------------------
+// The recurrences are what a track's latency is made of: 3 layers x 2584 dependent steps per segment, and the h/c carry chains
+// the segments (src/lstm.cpp:112-174, state kept at :160-161).  But the carry is PER LAYER: layer l of segment s+1 needs only
+// layer l of segment s and layer l-1 of segment s+1.  So the three layers run as three pipeline stages on different segments at
+// the same time, and — the four targets being independent until the Wiener filter (src/inference.cpp:70-186) — every
+// (layer, target group) has its own stream:
+//     front   STFT(s), fc1(s)                                             st_front
+//     lane l  W_ih GEMM(s), recurrence(s) of layer l  [+ fc2, fc3 on l=2] st_lane[l][group]
+//     post    (mask all-gather,) Wiener(s), iSTFT(s), finalize(s)          st_post (lowest priority: fills idle SMs)
+// Buffers that cross stages are rings indexed by segment (Session::*_ring); a producer of slot s % depth first waits for the
+// event of the last consumer of segment s - depth.  Every kernel computes exactly what it computes in the in-order schedule, so
+// the result is bit-identical (tests/test_gpu_parity.py).
+static int demix_wavefront(Session *s, const float *const *d_audio, const int64_t *n_samples, int n_tracks, int shift_offset,
+                           float *const *d_out, const float *const *host_in, float *const *host_out, int max_segs, int stride,
+                           const std::vector<FinalizeTrack> &hf, const std::vector<long> &max_range)
+{
+    size_t &ev = s->ev_cursor;
+    cudaStream_t main_st = s->st;
+    // targets per recurrence launch: one (2 clusters) packs the 15 cluster slots of the GPU best when a launch is short (few
+    // tracks); with many tracks per launch the grouping makes no measurable difference and fewer launches are issued
+    const int lt_opt = s->lane_targets > 0 ? s->lane_targets : (n_tracks <= 16 ? 1 : 4);
+    const int lt = std::max(1, std::min(lt_opt, s->tp_nt));
+    const int G = (s->tp_nt + lt - 1) / lt; // target groups = lanes per layer
+    auto grp_t0 = [&](int g) { return s->tp_t0 + g * lt; };
+    auto grp_nt = [&](int g) { return std::min(lt, s->tp_t0 + s->tp_nt - grp_t0(g)); };
+    auto wait = [&](cudaStream_t st, cudaEvent_t e) -> int {
+        UMX_CUDA_OK(cudaStreamWaitEvent(st, e, 0));
+        return 0;
+    };
+    auto record = [&](cudaEvent_t &e, cudaStream_t st) -> int {
+        e = take_event(s, ev);
+        UMX_CUDA_OK(cudaEventRecord(e, st));
+        return 0;
+    };
+    // events per segment
+    std::vector<cudaEvent_t> ev_fc1(max_segs), ev_wiener(max_segs), back_done(max_segs), ev_gather(max_segs);
+    std::vector<cudaEvent_t> ev_wih[3][kTargets], ev_rec[3][kTargets], ev_net[kTargets];
+    for (int g = 0; g < G; ++g)
+    {
+        ev_net[g].resize(max_segs);
+        for (int l = 0; l < 3; ++l)
+        {
+            ev_wih[l][g].resize(max_segs);
+            ev_rec[l][g].resize(max_segs);
+        }
+    }
+    // fork: every internal stream starts after what the caller's stream holds so far (state reset, accumulators, descriptors)
+    cudaEvent_t fork;
+    if (record(fork, main_st))
+        return -1;
+    if (wait(s->st_front, fork) || wait(s->st_post, fork) || wait(s->st_comm, fork))
+        return -1;
+    for (int l = 0; l < 3; ++l)
+        for (int g = 0; g < G; ++g)
+            if (wait(s->st_lane[l][g], fork))
+                return -1;
+    std::vector<long> copied_in(n_tracks, 0);
+
+    for (int sg = 0; sg < max_segs; ++sg)
+    {
+        NetView v{};
+        v.spec = s->spec_ring[sg % Session::kSpecRing];
+        v.maxabs = s->maxabs_ring[sg % Session::kSpecRing];
+        v.mask = s->mask_ring[sg % Session::kMaskRing];
+        v.act_h = s->act_ring_h[sg % Session::kActRing];
+        v.act_l = s->act_ring_l[sg % Session::kActRing];
+        for (int l = 0; l < 2; ++l)
+        {
+            v.lb_h[l] = s->lb_ring_h[l][sg % Session::kLbRing];
+            v.lb_l[l] = s->lb_ring_l[l][sg % Session::kLbRing];
+        }
+        v.chunks = s->skip_zero_frames ? s->d_istft + (size_t)sg * s->T : nullptr;
+
+        // ---- front: STFT + fc1
+        if (host_in)
+        {
+            if (int rc = ship_inputs(s, sg, stride, shift_offset, n_tracks, n_samples, d_audio, host_in, copied_in))
+                return rc;
+            cudaEvent_t e;
+            if (record(e, s->st_in) || wait(s->st_front, e))
+                return -1;
+        }
+        if (sg >= Session::kSpecRing && wait(s->st_front, ev_wiener[sg - Session::kSpecRing])) // spec / maxabs slot is free again
+            return -1;
+        if (int rc = run_stft(s, sg, n_tracks, v, s->st_front))
+            return rc;
+        if (sg >= Session::kActRing) // fc2 of segment sg - 3 has read the activation slot fc1 is about to overwrite
+            for (int g = 0; g < G; ++g)
+                if (wait(s->st_front, ev_net[g][sg - Session::kActRing]))
+                    return -1;
+        if (int rc = net_fc1(s, v, n_tracks, s->st_front, s->tile_counters + 12))
+            return rc;
+        if (record(ev_fc1[sg], s->st_front))
+            return -1;
+
+        // ---- lanes: layer l of this segment for every target group
+        for (int l = 0; l < 3; ++l)
+            for (int g = 0; g < G; ++g)
+            {
+                cudaStream_t st = s->st_lane[l][g];
+                int *counter = s->tile_counters + 4 * l + g;
+                if (wait(st, l == 0 ? ev_fc1[sg] : ev_rec[l - 1][g][sg]))
+                    return -1;
+                if (int rc = net_layer_gemm(s, v, l, n_tracks, grp_t0(g), grp_nt(g), st, counter))
+                    return rc;
+                if (record(ev_wih[l][g][sg], st))
+                    return -1;
+                // the layer output slot: the next layer's GEMM of segment sg - 2 has read it
+                if (l < 2 && sg >= Session::kLbRing && wait(st, ev_wih[l + 1][g][sg - Session::kLbRing]))
+                    return -1;
+                if (int rc = net_layer_rec(s, v, l, n_tracks, grp_t0(g), grp_nt(g), false, st))
+                    return rc;
+                if (record(ev_rec[l][g][sg], st))
+                    return -1;
+                if (l == 2)
+                {
+                    if (sg >= Session::kMaskRing && wait(st, ev_wiener[sg - Session::kMaskRing])) // mask slot is free again
+                        return -1;
+                    if (int rc = net_head(s, v, n_tracks, grp_t0(g), grp_nt(g), st, counter))
+                        return rc;
+                    if (record(ev_net[g][sg], st))
+                        return -1;
+                }
+            }
+
+        // ---- post: (all-gather,) Wiener, iSTFT + overlap-add, finalize, copy-out
+        cudaStream_t join_st = s->tp_world > 1 ? s->st_comm : s->st_post;
+        for (int g = 0; g < G; ++g)
+            if (wait(join_st, ev_net[g][sg]))
+                return -1;
+        if (s->tp_world > 1)
+        { // the one exchange step of the target-parallel mode, on its own stream: it overlaps the next segment's network
+            if (sg >= Session::kMaskRing && wait(s->st_comm, ev_wiener[sg - Session::kMaskRing]))
+                return -1;
+            {
+                StageScope sc(s, "allgather", s->st_comm);
+                if (int rc = tp_allgather_masks(s, v.mask, s->st_comm))
+                    return rc;
+            }
+            if (record(ev_gather[sg], s->st_comm) || wait(s->st_post, ev_gather[sg]))
+                return -1;
+        }
+        if (int rc = run_wiener(s, sg, n_tracks, v, s->st_post))
+            return rc;
+        if (record(ev_wiener[sg], s->st_post))
+            return -1;
+        {
+            StageScope sc(s, "istft", s->st_post);
+            s->launches++;
+            if (int rc = launch_istft(s->stems, s->Mcap * 2 * kBins, s->tp_nt, s->d_istft + (size_t)sg * s->T, n_tracks, s->n_buf,
+                                      s->st_post, s->tp_t0))
+                return rc;
+        }
+        {
+            StageScope sc(s, "finalize", s->st_post);
+            s->launches++;
+            if (int rc = launch_finalize(s->d_final + (size_t)sg * s->T, n_tracks, max_range[sg], shift_offset, s->n_buf, stride,
+                                         s->tp_nt, s->st_post, s->tp_t0))
+                return rc;
+        }
+        if (record(back_done[sg], s->st_post))
+            return -1;
+        if (host_out)
+        {
+            if (wait(s->st_out, back_done[sg]))
+                return -1;
+            if (int rc = ship_ranges(s, hf.data() + (size_t)sg * s->T, n_tracks, n_samples, d_out, host_out))
+                return rc;
+        }
+    }
+    // join: the post stage of the last segment is the last thing to finish; the lanes and the front stream finished before it
+    if (wait(main_st, back_done[max_segs - 1]))
+        return -1;
+    if (host_out)
+        UMX_CUDA_OK(cudaStreamSynchronize(s->st_out));
+    return 0;
+}
 
 int session_demix_device(Session *s, const float *const *d_audio, const int64_t *n_samples, int n_tracks,
                          int shift_offset, float *const *d_out, const float *const *host_in, float *const *host_out)
@@ -728,10 +994,19 @@ int session_demix_device(Session *s, const float *const *d_audio, const int64_t 
             max_range[sg] = std::max(max_range[sg], e - b);
         }
     }
-    UMX_CUDA_OK(cudaMemcpyAsync(s->d_stft, hs.data(), sizeof(StftTrack) * hs.size(), cudaMemcpyHostToDevice, s->st));
-    UMX_CUDA_OK(cudaMemcpyAsync(s->d_istft, hi.data(), sizeof(IstftTrack) * hi.size(), cudaMemcpyHostToDevice, s->st));
-    UMX_CUDA_OK(cudaMemcpyAsync(s->d_final, hf.data(), sizeof(FinalizeTrack) * hf.size(), cudaMemcpyHostToDevice, s->st));
-    UMX_CUDA_OK(cudaStreamSynchronize(s->st)); // hs/hi/hf are pageable host vectors
+    { // upload through the pinned staging buffer (no host synchronisation with the stream; at most one call of run-ahead)
+        UMX_CUDA_OK(cudaEventSynchronize(s->desc_copied));
+        uint8_t *hp = static_cast<uint8_t *>(s->h_desc);
+        const size_t b0 = sizeof(StftTrack) * hs.size(), b1 = sizeof(IstftTrack) * hi.size(), b2 = sizeof(FinalizeTrack) * hf.size();
+        UMX_CHECK(b0 + b1 + b2 <= s->h_desc_bytes, "umx_cuda_demix: descriptor staging too small");
+        std::memcpy(hp, hs.data(), b0);
+        std::memcpy(hp + b0, hi.data(), b1);
+        std::memcpy(hp + b0 + b1, hf.data(), b2);
+        UMX_CUDA_OK(cudaMemcpyAsync(s->d_stft, hp, b0, cudaMemcpyHostToDevice, s->st));
+        UMX_CUDA_OK(cudaMemcpyAsync(s->d_istft, hp + b0, b1, cudaMemcpyHostToDevice, s->st));
+        UMX_CUDA_OK(cudaMemcpyAsync(s->d_final, hp + b0 + b1, b2, cudaMemcpyHostToDevice, s->st));
+        UMX_CUDA_OK(cudaEventRecord(s->desc_copied, s->st));
+    }
 
     size_t &ev = s->ev_cursor;
     ev = 0;
@@ -742,6 +1017,8 @@ int session_demix_device(Session *s, const float *const *d_audio, const int64_t 
         ~SlotGuard() { s->slot = Session::SlotJob{}; }
     } slot_guard{s};
     std::vector<long> copied_in(n_tracks, 0);
+    if (s->pipeline == 3 && max_segs > 1)
+        return demix_wavefront(s, d_audio, n_samples, n_tracks, shift_offset, d_out, host_in, host_out, max_segs, stride, hf, max_range);
     const bool pipelined = s->pipeline != 0 && max_segs > 1;
     const bool slotted = s->pipeline == 2 && max_segs > 1;
     cudaStream_t main_st = s->st;
@@ -755,34 +1032,14 @@ int session_demix_device(Session *s, const float *const *d_audio, const int64_t 
     // ship the finished range of every stem of a segment (after its finalize) while later segments compute
     auto ship_out = [&](int seg) -> int {
         UMX_CUDA_OK(cudaStreamWaitEvent(s->st_out, back_done[seg], 0));
-        for (int i = 0; i < n_tracks; ++i)
-        {
-            const FinalizeTrack &f = hf[(size_t)seg * s->T + i];
-            if (f.i_end <= f.i_begin)
-                continue;
-            for (int stem = s->tp_t0; stem < s->tp_t0 + s->tp_nt; ++stem)
-            {
-                const size_t o = 2 * ((size_t)stem * n_samples[i] + f.i_begin);
-                UMX_CUDA_OK(cudaMemcpyAsync(host_out[i] + o, d_out[i] + o, sizeof(float2) * (size_t)(f.i_end - f.i_begin),
-                                            cudaMemcpyDeviceToHost, s->st_out));
-            }
-        }
-        return 0;
+        return ship_ranges(s, hf.data() + (size_t)seg * s->T, n_tracks, n_samples, d_out, host_out);
     };
     for (int sg = 0; sg < max_segs; ++sg) // sequential: h/c stream from segment to segment
     {
         if (host_in)
-        { // the samples this segment reads: original indices below sg*stride - shift + n_buf
-            for (int i = 0; i < n_tracks; ++i)
-            {
-                const long need = std::max(0L, std::min((long)n_samples[i], (long)sg * stride - shift_offset + s->n_buf));
-                if (need > copied_in[i])
-                {
-                    UMX_CUDA_OK(cudaMemcpyAsync(const_cast<float *>(d_audio[i]) + 2 * copied_in[i], host_in[i] + 2 * copied_in[i],
-                                                sizeof(float2) * (size_t)(need - copied_in[i]), cudaMemcpyHostToDevice, s->st_in));
-                    copied_in[i] = need;
-                }
-            }
+        {
+            if (int rc = ship_inputs(s, sg, stride, shift_offset, n_tracks, n_samples, d_audio, host_in, copied_in))
+                return rc;
             cudaEvent_t e = take_event(s, ev);
             UMX_CUDA_OK(cudaEventRecord(e, s->st_in));
             UMX_CUDA_OK(cudaStreamWaitEvent(s->st, e, 0));
@@ -790,9 +1047,9 @@ int session_demix_device(Session *s, const float *const *d_audio, const int64_t 
         // two-stage pipeline: STFT + networks of segment sg on the main stream; Wiener / iSTFT / finalize of the
         // same segment on st_post, so they fill the SMs the recurrence of segment sg+1 leaves idle
         const int b = sg & 1;
-        s->spec = s->spec_buf[b];
-        s->mask = s->mask_buf[b];
-        s->maxabs = s->maxabs_buf[b];
+        s->spec = s->spec_ring[b];
+        s->mask = s->mask_ring[b];
+        s->maxabs = s->maxabs_ring[b];
         if (pipelined && sg >= 2)
             UMX_CUDA_OK(cudaStreamWaitEvent(main_st, back_done[sg - 2], 0)); // buffer b is free again
         if (int rc = session_front(s, sg, n_tracks))

@@ -73,7 +73,7 @@ struct Session
     // option "pipeline": 0 = in order, 1 = post stage on its own low-priority stream, 2 = post stage in slots under the next
     // segment's recurrences, 3 (default) = segment wavefront: layer l of segment s+1 runs beside layer l+1 of segment s
     int pipeline = 3;
-    int lane_targets = 1;                           // option "lane_targets": targets per recurrence launch in the wavefront (1, 2 or 4)
+    int lane_targets = 0;                           // option "lane_targets": targets per recurrence launch in the wavefront (1, 2, 4; 0 = by batch size)
     cudaStream_t st_front = nullptr, st_comm = nullptr;
     cudaStream_t st_lane[3][kTargets] = {};         // wavefront: one stream per (LSTM layer, target group)
     void *h_desc = nullptr;                         // pinned staging for the descriptor tables
@@ -115,6 +115,8 @@ struct Session
     std::vector<StageTimer> timers;
     std::vector<cudaEvent_t> timer_pool; // timing events are created once and reused
     size_t timer_cursor = 0;
+    cudaEvent_t profile_base = nullptr;  // time base of the most recent profiled call
+    bool profile_resolved = true;        // stage_ms holds the most recent call's times
     std::map<std::string, double> stage_ms;
     long launches = 0;
 };
@@ -138,6 +140,7 @@ int session_demix_host(Session *s, const float *const *audio, const int64_t *n_s
 int session_infer_segment(Session *s, const float *audio, int n, float *out);
 void session_begin_profile(Session *s);
 int session_end_profile(Session *s);
+int session_resolve_profile(Session *s); // waits for the most recent call and fills stage_ms
 int ensure_desc_capacity(Session *s, int segs);
 // tp.cu: NCCL is loaded with dlopen on first use, so the library has no link-time dependency on it
 int tp_unique_id(void *id128);
