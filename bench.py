@@ -194,6 +194,7 @@ def main():
     ap.add_argument("--gemm-terms", type=int, default=0)
     ap.add_argument("--pipeline", type=int, default=-1, help="session option: 0 in order, 2 post stage under the next segment's recurrences, 3 (default) segment wavefront")
     ap.add_argument("--lane-targets", type=int, default=0, help="session option: targets per stream of the wavefront (1, 2, 4)")
+    ap.add_argument("--timeline", default="", help="write the stage intervals of the last timed step to this file (JSON)")
     ap.add_argument("--no-in-order", action="store_true", help="skip the in-order pass that yields roofline_in_order")
     ap.add_argument("--no-full-window", action="store_true", help="--impl reference: skip the one real 60 s window after the timed steps")
     args = ap.parse_args()
@@ -282,6 +283,8 @@ def main():
     clocks = sampler.stop()
     ms = ev0.elapsed_time(ev1) / args.steps
     stage_ms = read_stages()  # the LAST timed step (the library keeps the most recent call's timers)
+    if args.timeline and rank == 0:
+        json.dump(sess.timeline(), open(args.timeline, "w"))
     audio_s, ms_max = sharding.aggregate(T * args.track_seconds, ms, dist if world > 1 else None, dev)
     value = audio_s / (ms_max / 1e3)
 

@@ -136,6 +136,9 @@ int umx_cuda_session_init_target_parallel(umx_cuda_session *s, const void *id128
 int umx_cuda_session_set_profiling(umx_cuda_session *s, int enabled);
 double umx_cuda_session_stage_ms(umx_cuda_session *s, const char *stage);
 long umx_cuda_session_launches(umx_cuda_session *s);
+/* Every stage interval of the most recent profiled call (the stages of different segments overlap): up to cap entries of a
+ * 16-byte NUL-padded stage name, begin and end in ms since the call started.  Returns the number of intervals. */
+int umx_cuda_session_timeline(umx_cuda_session *s, char *stages, float *begin_ms, float *end_ms, int cap);
 /* Launch everything on the caller's cudaStream_t (NULL restores the session's own stream), so a caller
  * can bracket the work with its own CUDA events. */
 int umx_cuda_session_set_stream(umx_cuda_session *s, void *stream);
@@ -143,11 +146,9 @@ int umx_cuda_session_set_stream(umx_cuda_session *s, void *stream);
 int umx_cuda_lstm_max_active_clusters(void);
 /* Tuning knobs (documented in DESIGN.md): "gemm_terms" 1..3 fp16 split terms per tensor-core GEMM,
  * "gemm_impl" 0 = tcgen05, 1 = SIMT fp32 validation kernel, "lstm_impl" 0 = cluster kernel, 1 = simple,
- * "pipeline" 0 = every segment in order on one stream, 1 = Wiener/iSTFT/finalize of a segment on a second stream,
- * 2 = the same in three parts that start with the next segment's recurrence kernels, 3 (default) = segment wavefront:
- * layer l of segment s+1 runs beside layer l+1 of segment s (the h/c carry of src/lstm.cpp:160-161 is per layer), one stream
- * per (layer, target group) with "lane_targets" = 1, 2 or 4 targets per group (0, the default: 1 up to 16 tracks, else 4);
- * results are identical,
+ * "pipeline" 0 = every kernel in order on one stream, 3 (default) = segment wavefront: LSTM layer l of segment s+1 runs beside
+ * layer l+1 of segment s (the h/c carry of src/lstm.cpp:160-161 is per layer), one stream per (layer, target group) with
+ * "lane_targets" = 1, 2 or 4 targets per group (0, the default: 1 up to 16 tracks, else 4); results are identical,
  * "skip_zero_frames" 1 (default) = frames of a window beyond a short chunk are computed once (first layer) or not at all
  * (after the network), 0 = every frame of every 60 s window is computed as the reference does; results are identical. */
 int umx_cuda_session_set_option(umx_cuda_session *s, const char *name, int value);

@@ -14,7 +14,7 @@
 using namespace umx;
 
 template <bool INV>
-static double run(unsigned seed)
+static double run(unsigned seed, bool small_table = false)
 {
     std::vector<float2> tw(4096), x(4096), s(kFftSmemFloat2), out(4096);
     for (int j = 0; j < 4096; ++j)
@@ -27,16 +27,27 @@ static double run(unsigned seed)
         v = make_float2(rand() / (float)RAND_MAX - 0.5f, rand() / (float)RAND_MAX - 0.5f);
     std::vector<std::array<float2, 16>> regs(256);
     auto R = [&](int t) -> float2(&)[16] { return *reinterpret_cast<float2(*)[16]>(regs[t].data()); };
+    std::vector<float2> t256(256);
+    for (int m = 0; m < 256; ++m)
+        t256[m] = tw[16 * m];
     for (int t = 0; t < 256; ++t)
     {
         for (int a = 0; a < 16; ++a)
             R(t)[a] = x[256 * a + t];
-        fft_pass1<INV>(t, R(t), s.data(), tw.data());
+        if (small_table)
+            fft_pass1_t256<INV>(t, R(t), s.data(), t256.data());
+        else
+            fft_pass1<INV>(t, R(t), s.data(), tw.data());
     }
     for (int t = 0; t < 256; ++t)
         fft_pass2_load(t, R(t), s.data());
     for (int t = 0; t < 256; ++t)
-        fft_pass2_store<INV>(t, R(t), s.data(), tw.data());
+    {
+        if (small_table)
+            fft_pass2_store_t256<INV>(t, R(t), s.data(), t256.data(), tw[(t >> 4) * (t & 15)]);
+        else
+            fft_pass2_store<INV>(t, R(t), s.data(), tw.data());
+    }
     for (int t = 0; t < 256; ++t)
     {
         fft_pass3<INV>(t, R(t), s.data());
@@ -85,6 +96,9 @@ int main()
     double ef = run<false>(1), ei = run<true>(2);
     printf("fft4096 forward rel err %.3e inverse rel err %.3e\n", ef, ei);
     int bad = (ef > 2e-6) || (ei > 2e-6);
+    double sf = run<false>(3, true), si = run<true>(4, true); // 256-entry twiddle table variants
+    printf("fft4096 (256-entry twiddle table) forward rel err %.3e inverse rel err %.3e\n", sf, si);
+    bad |= (sf > 2e-6) || (si > 2e-6);
     bad |= check_pad(4096) | check_pad(20000) | check_pad(2646000);
     printf(bad ? "FAIL\n" : "OK\n");
     return bad;

@@ -193,12 +193,11 @@ def test_demix_multi_segment_multi_track(umx, gemm_impl, terms):
 
 
 @pytest.mark.parametrize("hidden", [64, 1024])  # validation recurrence kernel / the tcgen05 cluster kernel
-@pytest.mark.parametrize("mode,lane_targets", [(1, 0), (2, 0), (3, 0), (3, 1), (3, 2), (3, 4)])  # (3, 0) is the default
+@pytest.mark.parametrize("mode,lane_targets", [(3, 0), (3, 1), (3, 2), (3, 4)])  # (3, 0) is the default
 def test_demix_pipeline_modes_identical(umx, mode, lane_targets, hidden):
-    """Session option "pipeline": the post stage on a second stream (1), in slots under the next segment's recurrences (2), or
-    the segment wavefront (3: layer l of segment s+1 beside layer l+1 of segment s, one stream per layer and target group) must
-    give bit-identical stems to the in-order schedule, through the host and device paths.  Up to 7 segments per track, i.e.
-    deeper than every buffer ring of the wavefront."""
+    """Session option "pipeline": the segment wavefront (3: layer l of segment s+1 beside layer l+1 of segment s, one stream per
+    layer and target group) must give bit-identical stems to the in-order schedule (0).  Up to 7 segments per track, i.e. deeper
+    than every buffer ring of the wavefront."""
     n_buf = 16384
     gm = umx.load_umx_model(synth.make_ggml(hidden=hidden, seed=78))
     tracks = [synth.make_audio(n, 30 + i) for i, n in enumerate((70000, 41000, 9000))]

@@ -1,0 +1,10 @@
+#!/bin/bash
+mkdir -p gpurun_out
+timeout 1500 python -m pytest tests -m gpu -q -x > gpurun_out/r02c_tests.log 2>&1; echo "tests exit $?"; tail -4 gpurun_out/r02c_tests.log
+timeout 600 python bench.py --no-cpu-baseline > gpurun_out/r02c_bench.log 2>&1; echo "bench exit $?"
+python - <<'PY'
+import json
+d=json.loads(open('gpurun_out/r02c_bench.log').read().strip().splitlines()[-1])
+print('value', round(d['value']), 'e2e', round(d['e2e']['value']), 'ms', round(d['ms_per_step'],1), 'e2e ms', round(d['e2e']['ms_per_step'],1), {k: round(v['ms_per_step'],1) for k,v in d['stages'].items()}, d['clocks']['sm_mhz'])
+r=d['roofline_in_order']; print('in order', round(r['ms_per_step_in_order'],1), {k: (round(v['ms_per_step'],1), round(v['frac'],3)) for k,v in r['stages'].items()})
+PY

@@ -40,7 +40,7 @@ EXPORTS = [
     "umx_cuda_session_reset", "umx_cuda_session_get_state", "umx_cuda_infer_segment", "umx_cuda_demix",
     "umx_cuda_demix_device", "umx_cuda_segment_plan", "umx_cuda_stft", "umx_cuda_istft", "umx_cuda_lstm_forward",
     "umx_cuda_wiener", "umx_cuda_target_mags", "umx_cuda_session_set_profiling", "umx_cuda_session_stage_ms",
-    "umx_cuda_session_launches", "umx_cuda_session_set_option", "umx_cuda_session_set_stream",
+    "umx_cuda_session_launches", "umx_cuda_session_timeline", "umx_cuda_session_set_option", "umx_cuda_session_set_stream",
     "umx_cuda_wiener_noalloc", "umx_cuda_lstm_max_active_clusters", "umx_cuda_nccl_unique_id",
     "umx_cuda_session_init_target_parallel",
 ]
@@ -90,6 +90,7 @@ def lib():
     l.umx_cuda_session_stage_ms.argtypes = [vp, C.c_char_p]
     l.umx_cuda_session_launches.restype = C.c_long
     l.umx_cuda_session_launches.argtypes = [vp]
+    l.umx_cuda_session_timeline.argtypes = [vp, vp, vp, vp, ip]
     l.umx_cuda_session_set_option.argtypes = [vp, C.c_char_p, ip]
     l.umx_cuda_session_set_stream.argtypes = [vp, vp]
     l.umx_cuda_wiener_noalloc.argtypes = [vp, vp, ip, ip, vp, vp]
@@ -203,6 +204,13 @@ class Session:
 
     def launches(self) -> int:
         return int(self._lib.umx_cuda_session_launches(self._h))
+
+    def timeline(self):
+        """[(stage, begin_ms, end_ms)] of the most recent profiled call."""
+        n = _check(self._lib.umx_cuda_session_timeline(self._h, None, None, None, 0), "umx_cuda_session_timeline")
+        names, b, e = np.zeros((n, 16), np.uint8), np.zeros(n, np.float32), np.zeros(n, np.float32)
+        _check(self._lib.umx_cuda_session_timeline(self._h, _p(names), _p(b), _p(e), n), "umx_cuda_session_timeline")
+        return [(bytes(names[i]).split(b"\0")[0].decode(), float(b[i]), float(e[i])) for i in range(n)]
 
     def state(self, track: int, target: int, layer: int, direction: int):
         hh = self.model.hidden_size // 2

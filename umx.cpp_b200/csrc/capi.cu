@@ -266,6 +266,27 @@ double umx_cuda_session_stage_ms(umx_cuda_session *s, const char *stage)
     return it == s->s->stage_ms.end() ? -1.0 : it->second;
 }
 
+int umx_cuda_session_timeline(umx_cuda_session *s, char *stages, float *begin_ms, float *end_ms, int cap)
+{
+    UMX_CHECK(s, "umx_cuda_session_timeline: null session");
+    if (int rc = session_resolve_profile(s->s))
+        return rc;
+    const auto &tl = s->s->timeline;
+    for (int i = 0; i < cap && i < (int)tl.size(); ++i)
+    {
+        if (stages)
+        {
+            std::memset(stages + 16 * i, 0, 16);
+            std::strncpy(stages + 16 * i, tl[i].stage.c_str(), 15);
+        }
+        if (begin_ms)
+            begin_ms[i] = tl[i].begin_ms;
+        if (end_ms)
+            end_ms[i] = tl[i].end_ms;
+    }
+    return (int)tl.size();
+}
+
 int umx_cuda_session_set_stream(umx_cuda_session *s, void *stream)
 {
     UMX_CHECK(s, "umx_cuda_session_set_stream: null session");
@@ -309,8 +330,8 @@ int umx_cuda_session_set_option(umx_cuda_session *s, const char *name, int value
     }
     else if (n == "pipeline")
     {
-        UMX_CHECK(value >= 0 && value <= 3, "pipeline must be 0, 1, 2 or 3");
-        s->s->pipeline = value;
+        UMX_CHECK(value >= 0 && value <= 3, "pipeline must be 0 (in order) or 3 (segment wavefront)");
+        s->s->pipeline = value == 0 ? 0 : 3; // 1 and 2 were two-stream schedules the wavefront replaced
     }
     else if (n == "lane_targets")
     {

@@ -125,6 +125,40 @@ UMX_HD void fft_pass1(int t, float2 (&r)[16], float2 *s, const float2 *tw)
     }
 }
 
+// The same two passes with a 256-entry twiddle table t256[m] = tw[16 m] (2 KB: small enough for shared memory next to four
+// workspaces).  Pass 1 needs tw[16 b p] = t256[(b p) & 255]; pass 2 needs tw[c p + 16 c q] = tw[c p] * t256[(c q) & 255], the
+// first factor being a per-thread constant (`base`, loaded once per kernel).
+template <bool INV>
+UMX_HD void fft_pass1_t256(int t, float2 (&r)[16], float2 *s, const float2 *t256)
+{
+    dft16<INV>(r);
+    const int b = t >> 4;
+#pragma unroll
+    for (int p = 0; p < 16; ++p)
+    {
+        float2 v = r[p];
+        if (p != 0)
+        {
+            const float2 w = t256[(b * p) & 255];
+            v = INV ? cmulc(v, w) : cmul(v, w);
+        }
+        s[256 * p + t] = v;
+    }
+}
+
+template <bool INV>
+UMX_HD void fft_pass2_store_t256(int t, float2 (&r)[16], float2 *s, const float2 *t256, float2 base)
+{
+    const int p = t >> 4, c = t & 15;
+    dft16<INV>(r);
+#pragma unroll
+    for (int q = 0; q < 16; ++q)
+    {
+        const float2 w = q == 0 ? base : cmul(base, t256[(c * q) & 255]);
+        s[c * 257 + 16 * q + p] = INV ? cmulc(r[q], w) : cmul(r[q], w);
+    }
+}
+
 // pass 2a: load ; (barrier) ; pass 2b: transform + transposed store
 UMX_HD void fft_pass2_load(int t, float2 (&r)[16], const float2 *s)
 {

@@ -149,7 +149,7 @@ struct WienerArgs
     const float *maxabs;  // [track] max |X|
     float *partials;      // [track][chunks][2049][20]
     float *stats;         // [track][2049][16]
-    float2 *out;          // [4][M][2][2049]
+    float2 *out;          // [4][M][2][2049]; null: statistics only (the filter pass is fused into the inverse STFT)
     long out_stem_stride;
     float2 *mix_out;      // optional: mix / max_abs (the reference mutates its argument)
     int F;
@@ -159,6 +159,8 @@ struct WienerArgs
 };
 constexpr int kWienerChunks = 19;
 int launch_wiener(const WienerArgs &a, cudaStream_t st);
+// stft.cu: filter pass + inverse STFT + overlap-add in one kernel; `w` as for launch_wiener after its statistics are in w.stats
+int launch_wiener_istft(const WienerArgs &w, const IstftTrack *d_tracks, int n_buf, cudaStream_t st);
 
 // ---- model prep ----------------------------------------------------------------------------------
 int launch_dequant_u8(const uint8_t *q, float scale, float offset, float *out, long n, cudaStream_t st);

@@ -85,12 +85,14 @@ int session_resolve_profile(Session *s)
     UMX_CUDA_OK(cudaSetDevice(s->device));
     UMX_CUDA_OK(cudaStreamSynchronize(s->st)); // every internal stream was joined into s->st at the end of the call
     std::map<std::string, std::vector<std::pair<float, float>>> spans;
+    s->timeline.clear();
     for (auto &t : s->timers)
     {
         float a = 0.f, b = 0.f;
         UMX_CUDA_OK(cudaEventElapsedTime(&a, s->profile_base, t.a));
         UMX_CUDA_OK(cudaEventElapsedTime(&b, s->profile_base, t.b));
         spans[t.stage].push_back({a, b});
+        s->timeline.push_back({t.stage, a, b});
     }
     for (auto &kv : spans)
     {
@@ -197,7 +199,6 @@ int session_create(Model *m, int max_tracks, int n_buf, Session **out)
     rc |= salloc(s, &s->fc2_l, 4 * M * H);
     for (int i = 0; i < Session::kMaskRing; ++i)
         rc |= salloc(s, &s->mask_ring[i], 4 * M * kMaskLd);
-    rc |= salloc(s, &s->stems, 4 * M * 2 * kBins);
     rc |= salloc(s, &s->partials, (size_t)s->T * kWienerChunks * 20 * kBins);
     rc |= salloc(s, &s->stats, (size_t)s->T * 16 * kBins);
     rc |= salloc(s, &s->h_state, (size_t)s->T * 3 * 8 * s->Hh, true);
@@ -520,75 +521,12 @@ static int net_head(Session *s, const NetView &v, int n_tracks, int t0, int nt, 
     return run_gemm(s, b, st, 0, tile_counter);
 }
 
-static int session_back_part(Session *s, int seg, int n_tracks, int part);
-
-// One part of the deferred post stage (option "pipeline" = 2) on st_post, starting when the main stream reaches this point.
-static int slot_run_next(Session *s)
-{
-    Session::SlotJob &j = s->slot;
-    if (j.seg < 0 || j.next > 2)
-        return 0;
-    cudaEvent_t e = take_event(s, s->ev_cursor);
-    UMX_CUDA_OK(cudaEventRecord(e, s->st));
-    UMX_CUDA_OK(cudaStreamWaitEvent(s->st_post, e, 0));
-    cudaStream_t keep_st = s->st;
-    float2 *keep_spec = s->spec;
-    float *keep_mask = s->mask, *keep_maxabs = s->maxabs;
-    s->st = s->st_post;
-    s->spec = j.spec;
-    s->mask = j.mask;
-    s->maxabs = j.maxabs;
-    int rc = session_back_part(s, j.seg, j.n_tracks, j.next);
-    if (!rc && j.next >= 1)
-    { // the stems whose overlap-add this part completed: normalise / trim them and, for host-buffer calls, send them off
-        const int n1 = (s->tp_nt + 1) / 2;
-        const int begin = j.next == 1 ? s->tp_t0 : s->tp_t0 + n1, count = j.next == 1 ? n1 : s->tp_nt - n1;
-        if (count > 0)
-        {
-            StageScope sc(s, "finalize");
-            s->launches++;
-            rc = launch_finalize(j.fin, j.n_tracks, j.max_range, j.shift, s->n_buf, j.stride, count, s->st, begin);
-        }
-        if (!rc && j.next == 2 && cudaEventRecord(j.done, s->st) != cudaSuccess)
-            rc = -1;
-        if (!rc && j.host_out && count > 0)
-        {
-            cudaEvent_t e2 = take_event(s, s->ev_cursor);
-            if (cudaEventRecord(e2, s->st) != cudaSuccess || cudaStreamWaitEvent(s->st_out, e2, 0) != cudaSuccess)
-                rc = -1;
-            for (int i = 0; !rc && i < j.n_tracks; ++i)
-            {
-                const FinalizeTrack &f = j.fin_host[i];
-                if (f.i_end <= f.i_begin)
-                    continue;
-                // the finished range of `count` stems of this track in one strided copy
-                const size_t o = 2 * ((size_t)begin * j.n_samples[i] + f.i_begin);
-                if (cudaMemcpy2DAsync(j.host_out[i] + o, sizeof(float2) * (size_t)j.n_samples[i], j.d_out[i] + o,
-                                      sizeof(float2) * (size_t)j.n_samples[i], sizeof(float2) * (size_t)(f.i_end - f.i_begin),
-                                      (size_t)count, cudaMemcpyDeviceToHost, s->st_out) != cudaSuccess)
-                {
-                    set_error("umx_cuda_demix: device-to-host copy failed");
-                    rc = -1;
-                }
-            }
-        }
-    }
-    s->st = keep_st;
-    s->spec = keep_spec;
-    s->mask = keep_mask;
-    s->maxabs = keep_maxabs;
-    ++j.next;
-    return rc;
-}
-
 int session_lstm(Session *s, int n_tracks, int target_begin, int target_count, bool want_f32)
 {
     const NetView v = current_view(s);
     for (int l = 0; l < 3; ++l)
     {
         if (int rc = net_layer_gemm(s, v, l, n_tracks, target_begin, target_count, s->st, nullptr))
-            return rc;
-        if (int rc = slot_run_next(s)) // a part of the previous segment's post stage shares the GPU with this recurrence
             return rc;
         if (int rc = net_layer_rec(s, v, l, n_tracks, target_begin, target_count, want_f32, s->st))
             return rc;
@@ -632,9 +570,9 @@ int session_front(Session *s, int seg, int n_tracks)
     return 0;
 }
 
-static int run_wiener(Session *s, int seg, int n_tracks, const NetView &v, cudaStream_t st)
+// Wiener-EM statistics (reduce + finalize), then the filter pass fused into the inverse STFT + overlap-add
+static int run_post(Session *s, int seg, int n_tracks, const NetView &v, cudaStream_t st, cudaEvent_t *inputs_consumed = nullptr)
 {
-    StageScope sc(s, "wiener", st);
     WienerArgs w{};
     w.spec = v.spec;
     w.mask = v.mask;
@@ -644,40 +582,32 @@ static int run_wiener(Session *s, int seg, int n_tracks, const NetView &v, cudaS
     w.maxabs = v.maxabs;
     w.partials = s->partials;
     w.stats = s->stats;
-    w.out = s->stems;
-    w.out_stem_stride = s->Mcap * 2 * kBins;
+    w.out = nullptr; // statistics only
+    w.out_stem_stride = 0;
     w.mix_out = nullptr;
     w.F = s->F;
     w.n_tracks = n_tracks;
     w.stem_begin = s->tp_t0;
     w.stem_count = s->tp_nt;
     w.chunks = s->d_istft + (size_t)seg * s->T;
-    s->launches += 3;
-    return launch_wiener(w, st);
-}
-
-// part 0: Wiener-EM; parts 1 and 2: iSTFT + overlap-add of the first / second half of this rank's stems
-static int session_back_part(Session *s, int seg, int n_tracks, int part)
-{
-    const IstftTrack *dis = s->d_istft + (size_t)seg * s->T;
-    if (part == 0)
-        return run_wiener(s, seg, n_tracks, current_view(s), s->st);
-    const int n1 = (s->tp_nt + 1) / 2;
-    const int begin = part == 1 ? s->tp_t0 : s->tp_t0 + n1, count = part == 1 ? n1 : s->tp_nt - n1;
-    if (count <= 0)
-        return 0;
-    StageScope sc(s, "istft");
-    s->launches++;
-    return launch_istft(s->stems, s->Mcap * 2 * kBins, count, dis, n_tracks, s->n_buf, s->st, begin);
-}
-
-int session_back(Session *s, int seg, int n_tracks)
-{
-    for (int part = 0; part < 3; ++part)
-        if (int rc = session_back_part(s, seg, n_tracks, part))
+    {
+        StageScope sc(s, "wiener", st);
+        s->launches += 2;
+        if (int rc = launch_wiener(w, st))
             return rc;
+    }
+    {
+        StageScope sc(s, "istft", st);
+        s->launches++;
+        if (int rc = launch_wiener_istft(w, s->d_istft + (size_t)seg * s->T, s->n_buf, st))
+            return rc;
+    }
+    if (inputs_consumed)
+        UMX_CUDA_OK(cudaEventRecord(*inputs_consumed, st));
     return 0;
 }
+
+int session_back(Session *s, int seg, int n_tracks) { return run_post(s, seg, n_tracks, current_view(s), s->st); }
 
 int session_run_segment(Session *s, int seg, int n_tracks)
 {
@@ -910,17 +840,9 @@ static int demix_wavefront(Session *s, const float *const *d_audio, const int64_
             if (record(ev_gather[sg], s->st_comm) || wait(s->st_post, ev_gather[sg]))
                 return -1;
         }
-        if (int rc = run_wiener(s, sg, n_tracks, v, s->st_post))
+        ev_wiener[sg] = take_event(s, ev); // recorded when the filter pass has consumed this segment's spec / mask / maxabs
+        if (int rc = run_post(s, sg, n_tracks, v, s->st_post, &ev_wiener[sg]))
             return rc;
-        if (record(ev_wiener[sg], s->st_post))
-            return -1;
-        {
-            StageScope sc(s, "istft", s->st_post);
-            s->launches++;
-            if (int rc = launch_istft(s->stems, s->Mcap * 2 * kBins, s->tp_nt, s->d_istft + (size_t)sg * s->T, n_tracks, s->n_buf,
-                                      s->st_post, s->tp_t0))
-                return rc;
-        }
         {
             StageScope sc(s, "finalize", s->st_post);
             s->launches++;
@@ -1010,31 +932,12 @@ int session_demix_device(Session *s, const float *const *d_audio, const int64_t 
 
     size_t &ev = s->ev_cursor;
     ev = 0;
-    s->slot = Session::SlotJob{};
-    struct SlotGuard // no deferred job may outlive this call, whichever way it returns
-    {
-        Session *s;
-        ~SlotGuard() { s->slot = Session::SlotJob{}; }
-    } slot_guard{s};
     std::vector<long> copied_in(n_tracks, 0);
     if (s->pipeline == 3 && max_segs > 1)
         return demix_wavefront(s, d_audio, n_samples, n_tracks, shift_offset, d_out, host_in, host_out, max_segs, stride, hf, max_range);
-    const bool pipelined = s->pipeline != 0 && max_segs > 1;
-    const bool slotted = s->pipeline == 2 && max_segs > 1;
-    cudaStream_t main_st = s->st;
+    // in order on the caller's stream: h/c stream from segment to segment
     std::vector<cudaEvent_t> back_done(max_segs);
-    if (pipelined)
-    { // the post stream starts after everything queued so far (accumulator memsets, descriptors)
-        cudaEvent_t e = take_event(s, ev);
-        UMX_CUDA_OK(cudaEventRecord(e, main_st));
-        UMX_CUDA_OK(cudaStreamWaitEvent(s->st_post, e, 0));
-    }
-    // ship the finished range of every stem of a segment (after its finalize) while later segments compute
-    auto ship_out = [&](int seg) -> int {
-        UMX_CUDA_OK(cudaStreamWaitEvent(s->st_out, back_done[seg], 0));
-        return ship_ranges(s, hf.data() + (size_t)seg * s->T, n_tracks, n_samples, d_out, host_out);
-    };
-    for (int sg = 0; sg < max_segs; ++sg) // sequential: h/c stream from segment to segment
+    for (int sg = 0; sg < max_segs; ++sg)
     {
         if (host_in)
         {
@@ -1044,72 +947,24 @@ int session_demix_device(Session *s, const float *const *d_audio, const int64_t 
             UMX_CUDA_OK(cudaEventRecord(e, s->st_in));
             UMX_CUDA_OK(cudaStreamWaitEvent(s->st, e, 0));
         }
-        // two-stage pipeline: STFT + networks of segment sg on the main stream; Wiener / iSTFT / finalize of the
-        // same segment on st_post, so they fill the SMs the recurrence of segment sg+1 leaves idle
-        const int b = sg & 1;
-        s->spec = s->spec_ring[b];
-        s->mask = s->mask_ring[b];
-        s->maxabs = s->maxabs_ring[b];
-        if (pipelined && sg >= 2)
-            UMX_CUDA_OK(cudaStreamWaitEvent(main_st, back_done[sg - 2], 0)); // buffer b is free again
-        if (int rc = session_front(s, sg, n_tracks))
+        if (int rc = session_run_segment(s, sg, n_tracks))
             return rc;
-        if (slotted)
-        {
-            // whatever is left of the previous segment's post stage (all of it was started under this segment's recurrences
-            // unless the network has fewer than three of them), then its finished ranges can leave for the host
-            while (s->slot.seg >= 0 && s->slot.next <= 2)
-                if (int rc = slot_run_next(s))
-                    return rc;
-            s->slot = Session::SlotJob{};
-            back_done[sg] = take_event(s, ev);
-            if (sg + 1 < max_segs)
-            { // defer this segment's post stage: its parts start with the recurrences of segment sg + 1
-                s->slot.seg = sg;
-                s->slot.n_tracks = n_tracks;
-                s->slot.next = 0;
-                s->slot.fin = s->d_final + (size_t)sg * s->T;
-                s->slot.max_range = max_range[sg];
-                s->slot.shift = shift_offset;
-                s->slot.stride = stride;
-                s->slot.spec = s->spec;
-                s->slot.mask = s->mask;
-                s->slot.maxabs = s->maxabs;
-                s->slot.done = back_done[sg];
-                s->slot.fin_host = hf.data() + (size_t)sg * s->T;
-                s->slot.host_out = host_out;
-                s->slot.d_out = d_out;
-                s->slot.n_samples = n_samples;
-                continue;
-            }
-        }
-        if (pipelined)
-        {
-            cudaEvent_t e = take_event(s, ev);
-            UMX_CUDA_OK(cudaEventRecord(e, main_st));
-            UMX_CUDA_OK(cudaStreamWaitEvent(s->st_post, e, 0));
-            s->st = s->st_post; // the back stage's launches (and stage timers) go to the post stream
-        }
-        int rc_back = session_back(s, sg, n_tracks);
-        if (!rc_back)
         {
             StageScope sc(s, "finalize");
             s->launches++;
-            rc_back = launch_finalize(s->d_final + (size_t)sg * s->T, n_tracks, max_range[sg], shift_offset, s->n_buf, stride, s->tp_nt, s->st, s->tp_t0);
-        }
-        cudaStream_t back_st = s->st;
-        s->st = main_st;
-        if (rc_back)
-            return rc_back;
-        if (!slotted)
-            back_done[sg] = take_event(s, ev);
-        UMX_CUDA_OK(cudaEventRecord(back_done[sg], back_st));
-        if (host_out)
-            if (int rc = ship_out(sg))
+            if (int rc = launch_finalize(s->d_final + (size_t)sg * s->T, n_tracks, max_range[sg], shift_offset, s->n_buf, stride,
+                                         s->tp_nt, s->st, s->tp_t0))
                 return rc;
+        }
+        if (host_out)
+        { // ship the finished range of every stem while later segments compute
+            back_done[sg] = take_event(s, ev);
+            UMX_CUDA_OK(cudaEventRecord(back_done[sg], s->st));
+            UMX_CUDA_OK(cudaStreamWaitEvent(s->st_out, back_done[sg], 0));
+            if (int rc = ship_ranges(s, hf.data() + (size_t)sg * s->T, n_tracks, n_samples, d_out, host_out))
+                return rc;
+        }
     }
-    if (pipelined) // completion of the caller-visible stream implies completion of the post stage
-        UMX_CUDA_OK(cudaStreamWaitEvent(main_st, back_done[max_segs - 1], 0));
     if (host_out)
         UMX_CUDA_OK(cudaStreamSynchronize(s->st_out));
     return 0;

@@ -55,7 +55,6 @@ struct Session
     __half *act_h = nullptr, *act_l = nullptr; // = act_ring[0]
     __half *fc2_h = nullptr, *fc2_l = nullptr; // [4][Mcap][H]
     float *mask = nullptr;
-    float2 *stems = nullptr;                 // [4][Mcap][2][2049]
     float *maxabs = nullptr;                 // [T]
     float *partials = nullptr, *stats = nullptr;
     float *h_state = nullptr, *c_state = nullptr; // [T][3][4][2][Hh]
@@ -69,9 +68,9 @@ struct Session
     FinalizeTrack *d_final = nullptr;
     int seg_cap = 0;
     cudaStream_t st_in = nullptr, st_out = nullptr; // host<->device copy streams (overlap with compute)
-    cudaStream_t st_post = nullptr;                 // Wiener/iSTFT/finalize of segment s run here while segment s+1's network runs on st
-    // option "pipeline": 0 = in order, 1 = post stage on its own low-priority stream, 2 = post stage in slots under the next
-    // segment's recurrences, 3 (default) = segment wavefront: layer l of segment s+1 runs beside layer l+1 of segment s
+    cudaStream_t st_post = nullptr;                 // wavefront: Wiener statistics, filter + iSTFT, finalize of a segment
+    // option "pipeline": 0 = every kernel in order on one stream, 3 (default) = segment wavefront: layer l of segment s+1 runs
+    // beside layer l+1 of segment s (1 and 2, earlier two-stream schedules, are accepted and mean 3)
     int pipeline = 3;
     int lane_targets = 0;                           // option "lane_targets": targets per recurrence launch in the wavefront (1, 2, 4; 0 = by batch size)
     cudaStream_t st_front = nullptr, st_comm = nullptr;
@@ -81,24 +80,6 @@ struct Session
     cudaEvent_t desc_copied = nullptr;              // the previous call's descriptor upload has left the staging buffer
     std::vector<cudaEvent_t> ev_pool;
     size_t ev_cursor = 0;
-    // option "pipeline" = 2: the post stage (Wiener, iSTFT, finalize) of segment s is cut into three parts that start together
-    // with the three recurrence kernels of segment s+1 (which occupy 64 of the 148 SMs) on st_post
-    struct SlotJob
-    {
-        int seg = -1, n_tracks = 0, next = 0;
-        const FinalizeTrack *fin = nullptr;
-        long max_range = 0;
-        int shift = 0, stride = 0;
-        float2 *spec = nullptr;
-        float *mask = nullptr, *maxabs = nullptr;
-        cudaEvent_t done = nullptr;
-        // host-buffer calls: each half of the stems leaves for the host as soon as its iSTFT part and finalize are queued
-        const FinalizeTrack *fin_host = nullptr; // host copy of fin
-        float *const *host_out = nullptr;
-        float *const *d_out = nullptr;
-        const int64_t *n_samples = nullptr;
-    } slot;
-
     // grow-only pools for whole-track demixing
     std::vector<float2 *> acc_pool, in_pool, out_pool;
     std::vector<long> acc_cap, in_cap, out_cap;
@@ -118,6 +99,12 @@ struct Session
     cudaEvent_t profile_base = nullptr;  // time base of the most recent profiled call
     bool profile_resolved = true;        // stage_ms holds the most recent call's times
     std::map<std::string, double> stage_ms;
+    struct Span
+    {
+        std::string stage;
+        float begin_ms, end_ms;
+    };
+    std::vector<Span> timeline; // every stage interval of the most recent profiled call, relative to its start
     long launches = 0;
 };
 

@@ -11,6 +11,7 @@
 #include "common.cuh"
 #include "fft4096.cuh"
 #include "kernels.cuh"
+#include "wiener_math.cuh"
 
 #include <cmath>
 #include <mutex>
@@ -327,6 +328,252 @@ __global__ void __launch_bounds__(256, 3) istft_kernel(const float2 *__restrict_
 }
 
 // ------------------------------------------------------------------------------------------------
+// Wiener filter pass + inverse STFT + overlap-add in one kernel (reference: src/wiener.cpp:276-422 feeding src/dsp.cpp:178-258,
+// then umx.cpp:234-249).  The four filtered stem spectrograms are never written to memory: a CTA takes a run of frames of one
+// track and, frame by frame,
+//   A. all 512 threads, thread per bin: mixture (L, R) and the 4 x 2 masks from HBM, the four sources' spatial covariances of
+//      the bin from L2, the PSDs, Cxx^-1 — ONCE for the four stems — then every stem's y_j = G_j x, merged as Z = Y_L + i Y_R
+//      with its Hermitian extension straight into that stem's FFT workspace in shared memory;
+//   B. each half of the CTA (256 threads) runs the complex inverse FFT (fft4096.cuh) of two stems, one after the other;
+//   C. window, 1/4096, 1/(window-sum-square + 1e-8) and the overlap-add, which needs no shared memory: sample n = t + 256 k of a
+//      frame belongs to thread t for every frame, so the three partial hops a stem carries from frame to frame live in that
+//      thread's registers (added in the reference's frame order); complete hops go to the chunk / track accumulator.
+// DRAM traffic per (frame, bin): 48 bytes in (16 mixture + 32 masks) instead of 48 in + 64 out + 64 in of the two-kernel form.
+// ------------------------------------------------------------------------------------------------
+constexpr int kWiThreads = 512;
+constexpr int kWiFrames = 32; // frames per CTA (+ 3 halo frames whose hops the previous CTA emits)
+// shared memory: four FFT workspaces, then the staged inputs of one frame (mixture 2 x 2049 complex, 4 x (2 x 2049) masks)
+constexpr int kWiWsBytes = 4 * kFftSmemFloat2 * 8;            // 131,584
+constexpr int kWiSpecBytes = 2 * kBins * 8;                   // 32,784 (multiple of 16)
+constexpr int kWiMaskBytes = ((kFc3Out * 4 + 15) / 16) * 16;  // 16,400 per target
+constexpr int kWiSmemBytes = kWiWsBytes + kWiSpecBytes + 4 * kWiMaskBytes + 16 + 256 * 8; // + mbarrier + 256-entry twiddle table
+static_assert(kWiSmemBytes <= 232448, "fused Wiener/iSTFT kernel: shared memory budget exceeded");
+static_assert(kMaskLd * 4 % 16 == 0 && kWiSpecBytes % 16 == 0, "bulk copies need 16-byte aligned rows");
+
+__device__ __forceinline__ float istft_scale(int f, int n, int k, int F, float2 tw_t)
+{
+    // interior frames (every sample covered by 4 frames): the window-sum-square of the periodic Hann at hop N/4 is 1.5, so the
+    // scale win[n] / 4096 / (wss + 1e-8) is KS * (1 - cos(theta_t + k pi/8)), n = t + 256 k (see istft_kernel)
+    constexpr float KS = 0.5f / (4096.0f * (1.5f + 1e-8f));
+    if (f >= 3 && f + 3 < F)
+        return fmaf(tw_t.x, -KS * kCos8[k], fmaf(tw_t.y, -KS * kSin8[k], KS));
+    return __ldg(&g_win[n]) * (1.0f / (float)kNfft) / (wss_at(f, n, F, g_win) + 1e-8f);
+}
+
+namespace wi
+{
+__device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count)
+{
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes)
+{
+    asm volatile("{\n\t.reg .b64 st;\n\tmbarrier.arrive.expect_tx.shared::cta.b64 st, [%0], %1;\n\t}" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ bool mbar_try_wait(uint32_t bar, uint32_t parity)
+{
+    uint32_t ok;
+    asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+                 : "=r"(ok)
+                 : "r"(bar), "r"(parity)
+                 : "memory");
+    return ok != 0;
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity)
+{
+    if (mbar_try_wait(bar, parity))
+        return;
+    const long long t0 = clock64();
+    while (!mbar_try_wait(bar, parity))
+        if (clock64() - t0 > 4000000000LL) // a protocol bug must abort the kernel, never hang the GPU
+            __trap();
+}
+// global -> shared bulk copy (TMA, 1-D), bytes counted on the mbarrier
+__device__ __forceinline__ void bulk_load(uint32_t dst, const void *src, uint32_t bytes, uint32_t bar)
+{
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst), "l"(src),
+                 "r"(bytes), "r"(bar)
+                 : "memory");
+}
+__device__ __forceinline__ void bar_half(int half) { asm volatile("bar.sync %0, 256;" ::"r"(1 + half) : "memory"); }
+// mem += v, no return value: the accumulators are touched by one thread per launch, launches are stream-ordered
+__device__ __forceinline__ void red_add2(float2 *p, float2 v)
+{
+    asm volatile("red.global.add.v2.f32 [%0], {%1, %2};" ::"l"(p), "f"(v.x), "f"(v.y) : "memory");
+}
+} // namespace wi
+
+__global__ void __launch_bounds__(kWiThreads, 1)
+    wiener_istft_kernel(const float2 *__restrict__ spec, const float *__restrict__ mask, long mask_target_stride, int mask_ld,
+                        const float *__restrict__ maxabs, const float *__restrict__ stats, int F,
+                        const IstftTrack *__restrict__ tracks, int n_buf, int stem_begin, int stem_count)
+{
+    extern __shared__ __align__(128) uint8_t smem_raw[];
+    float2 *sm = reinterpret_cast<float2 *>(smem_raw);                                   // four FFT workspaces
+    const float2 *in_spec = reinterpret_cast<const float2 *>(smem_raw + kWiWsBytes);     // [2][2049] mixture of the frame
+    const uint8_t *in_mask = smem_raw + kWiWsBytes + kWiSpecBytes;                       // 4 x [2 x 2049] masks
+    const uint32_t bar = wi::smem_u32(smem_raw + kWiWsBytes + kWiSpecBytes + 4 * kWiMaskBytes);
+    float2 *t256 = reinterpret_cast<float2 *>(smem_raw + kWiWsBytes + kWiSpecBytes + 4 * kWiMaskBytes + 16); // tw[16 m]
+    const int tid = threadIdx.x, half = tid >> 8, t = tid & 255;
+    const int trk = blockIdx.z;
+    const IstftTrack tk = tracks[trk];
+    const int f0 = blockIdx.x * kWiFrames;
+    const int f_need = frames_reaching(tk.n_wave, F); // frames that reach an emitted sample (see istft_kernel)
+    if (f0 >= f_need)
+        return;
+    const int f1 = min(f_need, f0 + kWiFrames);
+    const bool last_cta = (f1 == F);
+    const int f_first = max(f0 - 3, 0);
+    const float ma = wiener_max_abs(maxabs, trk);
+    const float inv_ma = 1.0f / ma;
+    const float *st_base = stats + (long)trk * 16 * kBins;
+    const float2 tw_t = g_tw[t]; // (cos, -sin)(2 pi t / 4096)
+
+    // the frame's inputs arrive by bulk copies issued one frame ahead (they land while the previous frame's FFTs run)
+    auto stage = [&](int f) {
+        const long row = (long)trk * F + f;
+        wi::mbar_expect_tx(bar, kWiSpecBytes + 4 * kWiMaskBytes);
+        wi::bulk_load(wi::smem_u32(in_spec), spec + row * 2 * kBins, kWiSpecBytes, bar);
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+            wi::bulk_load(wi::smem_u32(in_mask + j * kWiMaskBytes), mask + (long)j * mask_target_stride + row * mask_ld, kWiMaskBytes, bar);
+    };
+    if (tid == 0)
+    {
+        wi::mbar_init(bar, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        stage(f_first);
+    }
+    if (tid < 256)
+        t256[tid] = g_tw[16 * tid];
+    const float2 tw_base = g_tw[(t >> 4) * (t & 15)]; // this thread's constant factor of the pass-2 twiddles
+    __syncthreads();
+
+    // this half's stems: slot 0 -> stem index `half`, slot 1 -> `half + 2` (relative to stem_begin); workspace = stem index
+    float2 acc[2][3][4]; // [slot][hops still missing 1, 2, 3 frames][j]: partial sums of positions 1024 (f + h) + t + 256 j
+#pragma unroll
+    for (int sl = 0; sl < 2; ++sl)
+#pragma unroll
+        for (int h = 0; h < 3; ++h)
+#pragma unroll
+            for (int j = 0; j < 4; ++j)
+                acc[sl][h][j] = make_float2(0.f, 0.f);
+
+    uint32_t parity = 0;
+    for (int f = f_first; f < f1; ++f)
+    {
+        // ---- A: filter; Z_j = Y_jL + i Y_jR and its Hermitian extension into workspace j
+        wi::mbar_wait(bar, parity);
+        parity ^= 1;
+#pragma unroll 2
+        for (int b = tid; b < kBins; b += kWiThreads)
+        {
+            float R[16];
+#pragma unroll
+            for (int i = 0; i < 16; ++i)
+                R[i] = __ldg(st_base + (long)i * kBins + b);
+            WienerIn in;
+            in.XL = in_spec[b];
+            in.XR = in_spec[kBins + b];
+#pragma unroll
+            for (int j = 0; j < 4; ++j)
+            {
+                const float *mk = reinterpret_cast<const float *>(in_mask + j * kWiMaskBytes);
+                in.mL[j] = mk[b];
+                in.mR[j] = mk[kBins + b];
+            }
+            WienerCommon c;
+            wiener_common(in, R, inv_ma, 0, c);
+#pragma unroll
+            for (int j = 0; j < 4; ++j)
+            {
+                const int idx = j - stem_begin;
+                if (idx < 0 || idx >= stem_count)
+                    continue;
+                float2 yL, yR;
+                wiener_source(c, R, j, ma, yL, yR);
+                float2 *w = sm + idx * kFftSmemFloat2;
+                if (b == 0 || b == kBins - 1)
+                    w[b == 0 ? 0 : 2048] = make_float2(yL.x, yR.x); // the half-spectrum inverse ignores Im of DC and Nyquist
+                else
+                {
+                    w[b] = make_float2(yL.x - yR.y, yL.y + yR.x);
+                    w[4096 - b] = make_float2(yL.x + yR.y, yR.x - yL.y); // conj(Y_L) + i conj(Y_R)
+                }
+            }
+        }
+        __syncthreads(); // workspaces complete; the staged inputs have been consumed
+        if (tid == 0 && f + 1 < f1)
+            stage(f + 1);
+        // ---- B + C: two stems per half, one after the other; the halves only meet again at the end of the frame
+#pragma unroll
+        for (int sl = 0; sl < 2; ++sl)
+        {
+            const int idx = half + 2 * sl;
+            if (idx >= stem_count) // uniform per half
+                continue;
+            float2 *s = sm + idx * kFftSmemFloat2;
+            float2 r[16];
+#pragma unroll
+            for (int a = 0; a < 16; ++a)
+                r[a] = s[256 * a + t];
+            wi::bar_half(half);
+            fft_pass1_t256<true>(t, r, s, t256);
+            wi::bar_half(half);
+            fft_pass2_load(t, r, s);
+            wi::bar_half(half);
+            fft_pass2_store_t256<true>(t, r, s, t256, tw_base);
+            wi::bar_half(half);
+            fft_pass3<true>(t, r, s);
+            // r[k] = (y_L, y_R)[n], n = t + 256 k: scale (in place), then overlap-add in registers
+#pragma unroll
+            for (int k = 0; k < 16; ++k)
+            {
+                const float sc = istft_scale(f, t + 256 * k, k, F, tw_t);
+                r[k].x *= sc;
+                r[k].y *= sc;
+            }
+            const int stem = stem_begin + idx;
+            float2 *out = tk.out + (long)stem * tk.out_stem_stride + tk.out_offset;
+            auto emit = [&](int hop, int j, float2 v) {
+                const int i = kHop * hop + t + 256 * j - kPad;
+                if (i >= 0 && i < tk.n_wave)
+                {
+                    if (tk.accumulate)
+                    { // out[off + k] += w[k] * y[k] (umx.cpp:234-249)
+                        const float wgt = tri_weight(i, n_buf);
+                        wi::red_add2(out + i, make_float2(wgt * v.x, wgt * v.y));
+                    }
+                    else
+                        out[i] = v;
+                }
+            };
+#pragma unroll
+            for (int j = 0; j < 4; ++j)
+            {
+                // hop f is complete: contributions were added in frame order f-3, f-2, f-1, f (as the reference does)
+                const float2 done = make_float2(acc[sl][0][j].x + r[j].x, acc[sl][0][j].y + r[j].y);
+                acc[sl][0][j] = make_float2(acc[sl][1][j].x + r[4 + j].x, acc[sl][1][j].y + r[4 + j].y);
+                acc[sl][1][j] = make_float2(acc[sl][2][j].x + r[8 + j].x, acc[sl][2][j].y + r[8 + j].y);
+                acc[sl][2][j] = r[12 + j];
+                if (f >= f0)
+                    emit(f, j, done);
+            }
+            if (last_cta && f == F - 1)
+            { // the final frame also completes hops F .. F+2 (nothing follows it)
+#pragma unroll
+                for (int h = 0; h < 3; ++h)
+#pragma unroll
+                    for (int j = 0; j < 4; ++j)
+                        emit(F + h, j, acc[sl][h][j]);
+            }
+        }
+        __syncthreads(); // every pass-3 read is done before the next frame's filter pass overwrites the workspaces
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
 // out = acc / sum_weight, trimmed to the original track (umx.cpp:251-273,136-147); output samples
 // [i_begin, i_end) of each track (a range is final as soon as the last segment touching it has been added)
 // ------------------------------------------------------------------------------------------------
@@ -435,6 +682,23 @@ int launch_istft(const float2 *stems, long stem_stride, int n_stems, const Istft
         return rc;
     dim3 grid(ceil_div(F, G), n_stems, n_tracks);
     istft_kernel<<<grid, 256, smem, st>>>(stems, stem_stride, F, G, d_tracks, n_buf, stem_begin);
+    UMX_CUDA_OK(cudaGetLastError());
+    return 0;
+}
+
+int launch_wiener_istft(const WienerArgs &w, const IstftTrack *d_tracks, int n_buf, cudaStream_t st)
+{
+    UMX_CHECK(!w.mask_is_mag && w.stats && w.maxabs && w.stem_count >= 1 && w.stem_count <= 4, "wiener_istft: bad arguments");
+    const size_t smem = kWiSmemBytes;
+    static PerDeviceOnce once;
+    if (int rc = once.run([&](int) {
+            UMX_CUDA_OK(cudaFuncSetAttribute(wiener_istft_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+            return 0;
+        }))
+        return rc;
+    dim3 grid(ceil_div(w.F, kWiFrames), 1, w.n_tracks);
+    wiener_istft_kernel<<<grid, kWiThreads, smem, st>>>(w.spec, w.mask, w.mask_target_stride, w.mask_ld, w.maxabs, w.stats, w.F,
+                                                        d_tracks, n_buf, w.stem_begin, w.stem_count);
     UMX_CUDA_OK(cudaGetLastError());
     return 0;
 }

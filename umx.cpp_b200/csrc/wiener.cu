@@ -13,54 +13,13 @@
 // the phase are materialised.  PSD quirk kept: v = sum_ch (re+im)^2 / 2 (wiener.cpp:187-202).
 #include "common.cuh"
 #include "kernels.cuh"
+#include "wiener_math.cuh"
 
 namespace umx
 {
 
 constexpr int kWienerQ = 20;         // per source: S00, S11, Re S01, Im S01, V
 constexpr int kWienerApplyFrames = 16;
-
-__device__ __forceinline__ float wiener_max_abs(const float *maxabs, int trk)
-{
-    return fmaxf(1.0f, maxabs[trk] / kWienerScale); // wiener.cpp:36-52
-}
-
-// y_jc / max_abs for one channel.  inv_ma = 1 / max_abs: the reference's own build uses -freciprocal-math, and an
-// IEEE division per element (with its divergent slow path) made these kernels issue-bound instead of HBM-bound.
-__device__ __forceinline__ float2 initial_estimate(float m, float2 X, float inv_ma, int is_mag)
-{
-    if (is_mag)
-    { // polar(mag, arg X): X == 0 has phase 0
-        const float a2 = X.x * X.x + X.y * X.y;
-        if (a2 > 0.f)
-        {
-            const float sc = m * rsqrtf(a2) * inv_ma;
-            return make_float2(sc * X.x, sc * X.y);
-        }
-        return make_float2(m * inv_ma, 0.f);
-    }
-    const float sc = m * inv_ma;
-    return make_float2(sc * X.x, sc * X.y);
-}
-
-// one frame of inputs for one bin: mix (L, R) and the 4 sources' (L, R) masks / magnitudes
-struct WienerIn
-{
-    float2 XL, XR;
-    float mL[4], mR[4];
-};
-__device__ __forceinline__ void wiener_load(const WienerArgs &a, long row, int b, WienerIn &w)
-{
-    w.XL = __ldg(&a.spec[(row * 2 + 0) * kBins + b]);
-    w.XR = __ldg(&a.spec[(row * 2 + 1) * kBins + b]);
-#pragma unroll
-    for (int j = 0; j < 4; ++j)
-    {
-        const float *mk = a.mask + (long)j * a.mask_target_stride + row * a.mask_ld;
-        w.mL[j] = __ldg(mk + b);
-        w.mR[j] = __ldg(mk + kBins + b);
-    }
-}
 
 constexpr int kWienerUnroll = 4; // frames whose loads are in flight together (the kernels are latency-bound otherwise)
 
@@ -145,7 +104,6 @@ __global__ void __launch_bounds__(256) wiener_apply_kernel(const WienerArgs a)
         return;
     const float ma = wiener_max_abs(a.maxabs, trk);
     const float inv_ma = 1.0f / ma;
-    const float reg = sqrtf(kWienerEps); // wiener.cpp:155-163
     float R[16];
     {
         const float *s = a.stats + (long)trk * 16 * kBins + b;
@@ -155,72 +113,35 @@ __global__ void __launch_bounds__(256) wiener_apply_kernel(const WienerArgs a)
     }
     for (int f0 = f_begin; f0 < f_end; f0 += 2)
     {
-      WienerIn in[2];
+        WienerIn in[2];
 #pragma unroll
-      for (int u = 0; u < 2; ++u)
-          wiener_load(a, (long)trk * a.F + min(f0 + u, f_end - 1), b, in[u]);
+        for (int u = 0; u < 2; ++u)
+            wiener_load(a, (long)trk * a.F + min(f0 + u, f_end - 1), b, in[u]);
 #pragma unroll
-      for (int u = 0; u < 2; ++u)
-      {
-        const int f = f0 + u;
-        if (f >= f_end)
-            break;
-        const long row = (long)trk * a.F + f;
-        const float2 XL = in[u].XL, XR = in[u].XR;
-        const float2 x0 = make_float2(XL.x * inv_ma, XL.y * inv_ma); // wiener.cpp:118-129
-        const float2 x1 = make_float2(XR.x * inv_ma, XR.y * inv_ma);
-        float v[4];
-        float c00 = 0.f, c11 = 0.f, c01r = 0.f, c01i = 0.f;
-#pragma unroll
-        for (int j = 0; j < 4; ++j)
+        for (int u = 0; u < 2; ++u)
         {
-            const float2 yL = initial_estimate(in[u].mL[j], XL, inv_ma, a.mask_is_mag);
-            const float2 yR = initial_estimate(in[u].mR[j], XR, inv_ma, a.mask_is_mag);
-            const float sL = yL.x + yL.y, sR = yR.x + yR.y;
-            v[j] = (sL * sL + sR * sR) * 0.5f;
-            c00 += reg + v[j] * R[4 * j + 0];
-            c11 += reg + v[j] * R[4 * j + 1];
-            c01r += v[j] * R[4 * j + 2];
-            c01i += v[j] * R[4 * j + 3];
-        }
-        // inverse of the Hermitian 2x2 [[c00, c01],[conj c01, c11]] (invert4D, wiener.cpp:54-84)
-        const float det = c00 * c11 - (c01r * c01r + c01i * c01i);
-        const float inv_det = 1.0f / det; // conj(det)/norm(det) with det real (one division per bin-frame)
-        const float i00 = inv_det * c11, i11 = inv_det * c00;
-        const float i01r = -inv_det * c01r, i01i = -inv_det * c01i; // inv01 ; inv10 = conj(inv01)
+            const int f = f0 + u;
+            if (f >= f_end)
+                break;
+            const long row = (long)trk * a.F + f;
+            WienerCommon c;
+            wiener_common(in[u], R, inv_ma, a.mask_is_mag, c);
 #pragma unroll
-        for (int j = 0; j < 4; ++j)
-          if (j >= a.stem_begin && j < a.stem_begin + a.stem_count) // target-parallel ranks only write their own stems
-        {
-            const float r00 = R[4 * j + 0], r11 = R[4 * j + 1], r01r = R[4 * j + 2], r01i = R[4 * j + 3];
-            // gain = v * R * inv ; R10 = conj(R01), inv10 = conj(inv01)
-            // g00 = r00*i00 + R01*conj(inv01)
-            const float g00r = v[j] * (r00 * i00 + (r01r * i01r + r01i * i01i));
-            const float g00i = v[j] * (r01i * i01r - r01r * i01i);
-            // g01 = r00*inv01 + R01*i11
-            const float g01r = v[j] * (r00 * i01r + r01r * i11);
-            const float g01i = v[j] * (r00 * i01i + r01i * i11);
-            // g10 = conj(R01)*i00 + r11*conj(inv01)
-            const float g10r = v[j] * (r01r * i00 + r11 * i01r);
-            const float g10i = v[j] * (-r01i * i00 - r11 * i01i);
-            // g11 = conj(R01)*inv01 + r11*i11
-            const float g11r = v[j] * ((r01r * i01r + r01i * i01i) + r11 * i11);
-            const float g11i = v[j] * (r01r * i01i - r01i * i01r);
-            float2 y0, y1;
-            y0.x = (g00r * x0.x - g00i * x0.y) + (g01r * x1.x - g01i * x1.y);
-            y0.y = (g00r * x0.y + g00i * x0.x) + (g01r * x1.y + g01i * x1.x);
-            y1.x = (g10r * x0.x - g10i * x0.y) + (g11r * x1.x - g11i * x1.y);
-            y1.y = (g10r * x0.y + g10i * x0.x) + (g11r * x1.y + g11i * x1.x);
-            float2 *o = a.out + (long)j * a.out_stem_stride + (row * 2) * kBins + b;
-            o[0] = make_float2(y0.x * ma, y0.y * ma);
-            o[kBins] = make_float2(y1.x * ma, y1.y * ma);
+            for (int j = 0; j < 4; ++j)
+                if (j >= a.stem_begin && j < a.stem_begin + a.stem_count) // target-parallel ranks only write their own stems
+                {
+                    float2 y0, y1;
+                    wiener_source(c, R, j, ma, y0, y1);
+                    float2 *o = a.out + (long)j * a.out_stem_stride + (row * 2) * kBins + b;
+                    o[0] = y0;
+                    o[kBins] = y1;
+                }
+            if (a.mix_out)
+            {
+                a.mix_out[(row * 2 + 0) * kBins + b] = c.x0;
+                a.mix_out[(row * 2 + 1) * kBins + b] = c.x1;
+            }
         }
-        if (a.mix_out)
-        {
-            a.mix_out[(row * 2 + 0) * kBins + b] = x0;
-            a.mix_out[(row * 2 + 1) * kBins + b] = x1;
-        }
-      }
     }
 }
 
@@ -231,6 +152,8 @@ int launch_wiener(const WienerArgs &a, cudaStream_t st)
     UMX_CUDA_OK(cudaGetLastError());
     wiener_finalize_kernel<<<dim3(tiles, a.n_tracks), 256, 0, st>>>(a);
     UMX_CUDA_OK(cudaGetLastError());
+    if (!a.out)
+        return 0; // statistics only
     wiener_apply_kernel<<<dim3(tiles, ceil_div(a.F, kWienerApplyFrames), a.n_tracks), 256, 0, st>>>(a);
     UMX_CUDA_OK(cudaGetLastError());
     return 0;
