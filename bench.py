@@ -317,6 +317,8 @@ def main():
     torch.cuda.synchronize()
     e2e_s = (time.perf_counter() - t0) / k_e2e
     copy_ms = read_stages()  # busy time of the two copy streams in the last e2e step
+    if args.timeline and rank == 0:
+        json.dump(sess.timeline(), open(args.timeline + ".e2e.json", "w"))
     _, e2e_ms_max = sharding.aggregate(T * args.track_seconds, e2e_s * 1e3, dist if world > 1 else None, dev)
     e2e_value = audio_s / (e2e_ms_max / 1e3)
     checksum = float(np.abs(outs_np[0][:, ::4096]).sum())  # the result was read back

@@ -76,7 +76,10 @@ struct alignas(64) TcParams
     CUtensorMap a_hi[kMaxGemmProblems], a_lo[kMaxGemmProblems], b_hi[kMaxGemmProblems], b_lo[kMaxGemmProblems];
     TcProblem p[kMaxGemmProblems];
     int count, total_tiles, terms, pad_;
-    int *tile_counter; // null: tiles blockIdx.x, + gridDim.x, ...; else: tiles drawn from this global counter (zero at launch)
+    // null: tiles blockIdx.x, + gridDim.x, ...; else int[2] {next tile, CTAs finished}, both zero at launch: tiles are drawn from
+    // the first, and the last CTA to finish puts both back to zero for the next launch (no memset between launches: a memset
+    // node may be served by a copy engine and then queues behind whatever host<->device copies that engine has pending)
+    int *tile_counter;
 };
 
 __device__ __forceinline__ float act_apply(float v, int act)
@@ -483,6 +486,15 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_tc_kernel(const __grid_const
         tc_fence_after();
         tmem_dealloc(tmem_base, kTmemCols);
     }
+    if (P.tile_counter && threadIdx.x == 0)
+    { // this CTA's last draw is long done (the producer left its loop): the last CTA out re-arms the queue
+        if (atomicAdd(P.tile_counter + 1, 1) == (int)gridDim.x - 1)
+        {
+            P.tile_counter[0] = 0;
+            P.tile_counter[1] = 0;
+            __threadfence();
+        }
+    }
 }
 
 // ---- host side -----------------------------------------------------------------------------------------
@@ -575,8 +587,6 @@ int launch_gemm_tc(const GemmBatch &batch, int terms, cudaStream_t st, int *tile
     }
     P.total_tiles = tiles;
     P.tile_counter = tile_counter;
-    if (tile_counter) // the queue starts at zero for every launch (stream-ordered, 4 bytes)
-        UMX_CUDA_OK(cudaMemsetAsync(tile_counter, 0, sizeof(int), st));
 
     static PerDeviceOnce once;
     static int sm_count[64] = {};

@@ -35,6 +35,7 @@ struct FinalizeTrack
 constexpr int kIstftFramesPerCta = 32; // + 3 halo frames recomputed per CTA
 
 int init_fft_tables(int device);
+int launch_zero_f32(float *p, int n, cudaStream_t st); // p[0..n) = 0 by a kernel (stays on the compute engines)
 // skip_zero: frames beyond the first all-zero one of a short chunk are not computed (nothing downstream reads them)
 int launch_stft(const StftTrack *d_tracks, int n_tracks, int n_buf, float2 *spec, __half *xh, __half *xl,
                 float *maxabs, cudaStream_t st, int skip_zero = 0);
@@ -99,8 +100,9 @@ struct GemmBatch
 
 int launch_gemm_simt(const GemmBatch &batch, cudaStream_t st);
 // terms: 1 = A_hi*B_hi ; 2 = + A_lo*B_hi ; 3 = + A_hi*B_lo
-// tile_counter (optional, device int): tiles are drawn from it at run time instead of the static blockIdx stride, so a launch that
-// shares the GPU with other kernels finishes as soon as the CTAs that did get an SM have worked through all tiles
+// tile_counter (optional, device int[2], zero before the first launch; every launch leaves it zero): tiles are drawn from it at
+// run time instead of the static blockIdx stride, so a launch that shares the GPU with other kernels finishes as soon as the
+// CTAs that did get an SM have worked through all tiles.  Launches that may overlap need counters of their own.
 int launch_gemm_tc(const GemmBatch &batch, int terms, cudaStream_t st, int *tile_counter = nullptr);
 
 // ---- lstm ----------------------------------------------------------------------------------------
@@ -160,7 +162,10 @@ struct WienerArgs
 constexpr int kWienerChunks = 19;
 int launch_wiener(const WienerArgs &a, cudaStream_t st);
 // stft.cu: filter pass + inverse STFT + overlap-add in one kernel; `w` as for launch_wiener after its statistics are in w.stats
-int launch_wiener_istft(const WienerArgs &w, const IstftTrack *d_tracks, int n_buf, cudaStream_t st);
+// frames [frame_begin, frame_end) only (frame_end < 0: all): the launch emits the samples of those frames' hops, so a segment's
+// post stage can be cut into parts whose finished output ranges leave for the host while the next part computes
+int launch_wiener_istft(const WienerArgs &w, const IstftTrack *d_tracks, int n_buf, cudaStream_t st, int frame_begin = 0,
+                        int frame_end = -1);
 
 // ---- model prep ----------------------------------------------------------------------------------
 int launch_dequant_u8(const uint8_t *q, float scale, float offset, float *out, long n, cudaStream_t st);

@@ -36,6 +36,28 @@ static cudaEvent_t take_timer_event(Session *s)
     }
     return s->timer_pool[s->timer_cursor++];
 }
+// Timing events are only ever recorded on compute streams.  For the two copy streams (st_in, st_out) a plain event is recorded
+// there and the timestamp is taken on a probe stream that waits for it: a timing event in a stream served by a copy engine
+// held back the compute work waiting on that stream's later events until ALL queued copies had run.
+static void record_timer(Session *s, cudaEvent_t timer, cudaStream_t st)
+{
+    if (st != s->st_in && st != s->st_out)
+    {
+        cudaEventRecord(timer, st);
+        return;
+    }
+    if (s->probe_cursor == s->probe_pool.size())
+    {
+        cudaEvent_t e;
+        cudaEventCreateWithFlags(&e, cudaEventDisableTiming);
+        s->probe_pool.push_back(e);
+    }
+    cudaEvent_t x = s->probe_pool[s->probe_cursor++];
+    cudaStream_t probe = st == s->st_in ? s->st_probe[0] : s->st_probe[1];
+    cudaEventRecord(x, st);
+    cudaStreamWaitEvent(probe, x, 0);
+    cudaEventRecord(timer, probe);
+}
 StageScope::StageScope(Session *s_, const char *stage, cudaStream_t st_) : s(s_), st(st_ ? st_ : s_->st)
 {
     if (!s->profiling)
@@ -44,14 +66,14 @@ StageScope::StageScope(Session *s_, const char *stage, cudaStream_t st_) : s(s_)
     t.stage = stage;
     t.a = take_timer_event(s);
     t.b = take_timer_event(s);
-    cudaEventRecord(t.a, st);
+    record_timer(s, t.a, st);
     s->timers.push_back(t);
     idx = (int)s->timers.size() - 1;
 }
 StageScope::~StageScope()
 {
     if (idx >= 0)
-        cudaEventRecord(s->timers[idx].b, st);
+        record_timer(s, s->timers[idx].b, st);
 }
 
 void session_begin_profile(Session *s)
@@ -60,6 +82,7 @@ void session_begin_profile(Session *s)
     s->stage_ms.clear();
     s->timers.clear();
     s->timer_cursor = 0;
+    s->probe_cursor = 0;
     s->profile_resolved = true;
     if (s->profiling)
     { // common time base of this call: the stages run on several streams
@@ -84,6 +107,8 @@ int session_resolve_profile(Session *s)
         return 0;
     UMX_CUDA_OK(cudaSetDevice(s->device));
     UMX_CUDA_OK(cudaStreamSynchronize(s->st)); // every internal stream was joined into s->st at the end of the call
+    UMX_CUDA_OK(cudaStreamSynchronize(s->st_probe[0]));
+    UMX_CUDA_OK(cudaStreamSynchronize(s->st_probe[1]));
     std::map<std::string, std::vector<std::pair<float, float>>> spans;
     s->timeline.clear();
     for (auto &t : s->timers)
@@ -149,22 +174,24 @@ int session_create(Model *m, int max_tracks, int n_buf, Session **out)
         session_destroy(s);
         return rc;
     };
-    // Streams.  Priorities (greatest first): the post stage (its kernels are short, and the finished output ranges should leave
-    // for the host as early as possible), then the deepest LSTM layer — the oldest segment in flight — layer 1, layer 0, and
-    // last the front stage (STFT, fc1) of the newest segment.
+    // Streams.  Priorities (greatest first): the front stage (STFT, fc1: short, and everything else of a segment waits for it; the
+    // buffer rings bound how far it runs ahead), the post stage (short kernels, and the finished output ranges should leave for
+    // the host as early as possible), then the deepest LSTM layer — the oldest segment in flight — layer 1, layer 0.
     int prio_lo = 0, prio_hi = 0;
     cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi);
     auto prio = [&](int rank_from_top) { return std::min(prio_lo, prio_hi + rank_from_top); };
     bool ok = cudaStreamCreateWithFlags(&s->own_st, cudaStreamNonBlocking) == cudaSuccess &&
               cudaStreamCreateWithFlags(&s->st_in, cudaStreamNonBlocking) == cudaSuccess &&
               cudaStreamCreateWithFlags(&s->st_out, cudaStreamNonBlocking) == cudaSuccess &&
-              cudaStreamCreateWithPriority(&s->st_post, cudaStreamNonBlocking, prio(0)) == cudaSuccess &&
-              cudaStreamCreateWithPriority(&s->st_front, cudaStreamNonBlocking, prio(4)) == cudaSuccess &&
+              cudaStreamCreateWithPriority(&s->st_post, cudaStreamNonBlocking, prio(1)) == cudaSuccess &&
+              cudaStreamCreateWithPriority(&s->st_front, cudaStreamNonBlocking, prio(0)) == cudaSuccess &&
               cudaStreamCreateWithPriority(&s->st_comm, cudaStreamNonBlocking, prio_hi) == cudaSuccess &&
+              cudaStreamCreateWithFlags(&s->st_probe[0], cudaStreamNonBlocking) == cudaSuccess &&
+              cudaStreamCreateWithFlags(&s->st_probe[1], cudaStreamNonBlocking) == cudaSuccess &&
               cudaEventCreateWithFlags(&s->desc_copied, cudaEventDisableTiming) == cudaSuccess;
     for (int l = 0; ok && l < 3; ++l)
         for (int g = 0; ok && g < kTargets; ++g)
-            ok = cudaStreamCreateWithPriority(&s->st_lane[l][g], cudaStreamNonBlocking, prio(3 - l)) == cudaSuccess;
+            ok = cudaStreamCreateWithPriority(&s->st_lane[l][g], cudaStreamNonBlocking, prio(4 - l)) == cudaSuccess;
     if (!ok)
     {
         set_error("session_create: cudaStreamCreate failed");
@@ -203,7 +230,7 @@ int session_create(Model *m, int max_tracks, int n_buf, Session **out)
     rc |= salloc(s, &s->stats, (size_t)s->T * 16 * kBins);
     rc |= salloc(s, &s->h_state, (size_t)s->T * 3 * 8 * s->Hh, true);
     rc |= salloc(s, &s->c_state, (size_t)s->T * 3 * 8 * s->Hh, true);
-    rc |= salloc(s, &s->tile_counters, 16, true);
+    rc |= salloc(s, &s->tile_counters, 2 * 16, true);
     if (rc)
         return fail(-1);
     s->spec = s->spec_ring[0];
@@ -221,6 +248,15 @@ int session_create(Model *m, int max_tracks, int n_buf, Session **out)
         return fail(-1);
     *out = s;
     return 0;
+}
+
+// The post stage of a segment (filter + inverse STFT + overlap-add, finalize, copy-out) is cut into kPostParts runs of frames, so
+// the first finished output ranges of a segment are on their way to the host while the rest of it is still computed: the tail
+// of a host-buffer call after the last kernel is one part's copy, not a whole segment's.
+static int post_part_frame(int F, int q)
+{
+    const int per = ((F + kPostParts - 1) / kPostParts + 31) / 32 * 32; // whole CTAs of the fused kernel
+    return std::min(F, q * per);
 }
 
 int ensure_desc_capacity(Session *s, int segs)
@@ -244,8 +280,8 @@ int ensure_desc_capacity(Session *s, int segs)
     const size_t n = (size_t)segs * s->T;
     UMX_CUDA_OK(cudaMalloc(&s->d_stft, sizeof(StftTrack) * n));
     UMX_CUDA_OK(cudaMalloc(&s->d_istft, sizeof(IstftTrack) * n));
-    UMX_CUDA_OK(cudaMalloc(&s->d_final, sizeof(FinalizeTrack) * n));
-    s->h_desc_bytes = (sizeof(StftTrack) + sizeof(IstftTrack) + sizeof(FinalizeTrack)) * n;
+    UMX_CUDA_OK(cudaMalloc(&s->d_final, sizeof(FinalizeTrack) * n * kPostParts));
+    s->h_desc_bytes = (sizeof(StftTrack) + sizeof(IstftTrack) + sizeof(FinalizeTrack) * kPostParts) * n;
     UMX_CUDA_OK(cudaMallocHost(&s->h_desc, s->h_desc_bytes));
     s->seg_cap = segs;
     return 0;
@@ -278,7 +314,9 @@ void session_destroy(Session *s)
         cudaEventDestroy(e);
     if (s->desc_copied)
         cudaEventDestroy(s->desc_copied);
-    for (cudaStream_t st : {s->st_in, s->st_out, s->st_post, s->st_front, s->st_comm, s->own_st})
+    for (auto e : s->probe_pool)
+        cudaEventDestroy(e);
+    for (cudaStream_t st : {s->st_in, s->st_out, s->st_post, s->st_front, s->st_comm, s->st_probe[0], s->st_probe[1], s->own_st})
         if (st)
             cudaStreamDestroy(st);
     for (auto &row : s->st_lane)
@@ -547,7 +585,10 @@ int session_network(Session *s, int n_tracks)
 static int run_stft(Session *s, int seg, int n_tracks, const NetView &v, cudaStream_t st)
 {
     StageScope sc(s, "stft", st);
-    UMX_CUDA_OK(cudaMemsetAsync(v.maxabs, 0, sizeof(float) * s->T, st));
+    // max|X| per track starts at zero: a kernel, not a memset node (a copy engine may serve memsets, and there they queue behind
+    // the host<->device copies of the whole call)
+    if (int rc = launch_zero_f32(v.maxabs, s->T, st))
+        return rc;
     s->launches++;
     return launch_stft(s->d_stft + (size_t)seg * s->T, n_tracks, s->n_buf, v.spec, s->xh, s->xl, v.maxabs, st, s->skip_zero_frames);
 }
@@ -571,7 +612,7 @@ int session_front(Session *s, int seg, int n_tracks)
 }
 
 // Wiener-EM statistics (reduce + finalize), then the filter pass fused into the inverse STFT + overlap-add
-static int run_post(Session *s, int seg, int n_tracks, const NetView &v, cudaStream_t st, cudaEvent_t *inputs_consumed = nullptr)
+static WienerArgs post_args(Session *s, int seg, int n_tracks, const NetView &v)
 {
     WienerArgs w{};
     w.spec = v.spec;
@@ -590,24 +631,34 @@ static int run_post(Session *s, int seg, int n_tracks, const NetView &v, cudaStr
     w.stem_begin = s->tp_t0;
     w.stem_count = s->tp_nt;
     w.chunks = s->d_istft + (size_t)seg * s->T;
-    {
-        StageScope sc(s, "wiener", st);
-        s->launches += 2;
-        if (int rc = launch_wiener(w, st))
-            return rc;
-    }
-    {
-        StageScope sc(s, "istft", st);
-        s->launches++;
-        if (int rc = launch_wiener_istft(w, s->d_istft + (size_t)seg * s->T, s->n_buf, st))
-            return rc;
-    }
-    if (inputs_consumed)
-        UMX_CUDA_OK(cudaEventRecord(*inputs_consumed, st));
-    return 0;
+    return w;
+}
+static int run_post_stats(Session *s, int seg, int n_tracks, const NetView &v, cudaStream_t st)
+{
+    StageScope sc(s, "wiener", st);
+    s->launches += 2;
+    return launch_wiener(post_args(s, seg, n_tracks, v), st);
+}
+static int run_post_part(Session *s, int seg, int n_tracks, const NetView &v, cudaStream_t st, int part)
+{
+    const int fa = post_part_frame(s->F, part), fb = part + 1 == kPostParts ? s->F : post_part_frame(s->F, part + 1);
+    if (fa >= fb)
+        return 0;
+    StageScope sc(s, "istft", st);
+    s->launches++;
+    return launch_wiener_istft(post_args(s, seg, n_tracks, v), s->d_istft + (size_t)seg * s->T, s->n_buf, st, fa, fb);
 }
 
-int session_back(Session *s, int seg, int n_tracks) { return run_post(s, seg, n_tracks, current_view(s), s->st); }
+int session_back(Session *s, int seg, int n_tracks)
+{
+    const NetView v = current_view(s);
+    if (int rc = run_post_stats(s, seg, n_tracks, v, s->st))
+        return rc;
+    for (int q = 0; q < kPostParts; ++q)
+        if (int rc = run_post_part(s, seg, n_tracks, v, s->st, q))
+            return rc;
+    return 0;
+}
 
 int session_run_segment(Session *s, int seg, int n_tracks)
 {
@@ -788,7 +839,7 @@ static int demix_wavefront(Session *s, const float *const *d_audio, const int64_
             for (int g = 0; g < G; ++g)
                 if (wait(s->st_front, ev_net[g][sg - Session::kActRing]))
                     return -1;
-        if (int rc = net_fc1(s, v, n_tracks, s->st_front, s->tile_counters + 12))
+        if (int rc = net_fc1(s, v, n_tracks, s->st_front, s->tile_counters + 2 * 12))
             return rc;
         if (record(ev_fc1[sg], s->st_front))
             return -1;
@@ -798,7 +849,7 @@ static int demix_wavefront(Session *s, const float *const *d_audio, const int64_
             for (int g = 0; g < G; ++g)
             {
                 cudaStream_t st = s->st_lane[l][g];
-                int *counter = s->tile_counters + 4 * l + g;
+                int *counter = s->tile_counters + 2 * (4 * l + g);
                 if (wait(st, l == 0 ? ev_fc1[sg] : ev_rec[l - 1][g][sg]))
                     return -1;
                 if (int rc = net_layer_gemm(s, v, l, n_tracks, grp_t0(g), grp_nt(g), st, counter))
@@ -840,24 +891,33 @@ static int demix_wavefront(Session *s, const float *const *d_audio, const int64_
             if (record(ev_gather[sg], s->st_comm) || wait(s->st_post, ev_gather[sg]))
                 return -1;
         }
-        ev_wiener[sg] = take_event(s, ev); // recorded when the filter pass has consumed this segment's spec / mask / maxabs
-        if (int rc = run_post(s, sg, n_tracks, v, s->st_post, &ev_wiener[sg]))
+        if (int rc = run_post_stats(s, sg, n_tracks, v, s->st_post))
             return rc;
+        for (int q = 0; q < kPostParts; ++q)
         {
-            StageScope sc(s, "finalize", s->st_post);
-            s->launches++;
-            if (int rc = launch_finalize(s->d_final + (size_t)sg * s->T, n_tracks, max_range[sg], shift_offset, s->n_buf, stride,
-                                         s->tp_nt, s->st_post, s->tp_t0))
+            if (int rc = run_post_part(s, sg, n_tracks, v, s->st_post, q))
                 return rc;
-        }
-        if (record(back_done[sg], s->st_post))
-            return -1;
-        if (host_out)
-        {
-            if (wait(s->st_out, back_done[sg]))
+            if (q + 1 == kPostParts && record(ev_wiener[sg], s->st_post)) // this segment's spec / mask / maxabs are consumed
                 return -1;
-            if (int rc = ship_ranges(s, hf.data() + (size_t)sg * s->T, n_tracks, n_samples, d_out, host_out))
-                return rc;
+            const size_t d = ((size_t)sg * kPostParts + q) * s->T;
+            if (max_range[(size_t)sg * kPostParts + q] > 0)
+            {
+                StageScope sc(s, "finalize", s->st_post);
+                s->launches++;
+                if (int rc = launch_finalize(s->d_final + d, n_tracks, max_range[(size_t)sg * kPostParts + q], shift_offset, s->n_buf,
+                                             stride, s->tp_nt, s->st_post, s->tp_t0))
+                    return rc;
+            }
+            if (q + 1 == kPostParts && record(back_done[sg], s->st_post))
+                return -1;
+            if (host_out && max_range[(size_t)sg * kPostParts + q] > 0)
+            {
+                cudaEvent_t e;
+                if (record(e, s->st_post) || wait(s->st_out, e))
+                    return -1;
+                if (int rc = ship_ranges(s, hf.data() + d, n_tracks, n_samples, d_out, host_out))
+                    return rc;
+            }
         }
     }
     // join: the post stage of the last segment is the last thing to finish; the lanes and the front stream finished before it
@@ -892,13 +952,13 @@ int session_demix_device(Session *s, const float *const *d_audio, const int64_t 
     // descriptors for every (segment, track); tracks that have ended run an empty chunk
     std::vector<StftTrack> hs((size_t)max_segs * s->T);
     std::vector<IstftTrack> hi((size_t)max_segs * s->T);
-    std::vector<FinalizeTrack> hf((size_t)max_segs * s->T);
+    std::vector<FinalizeTrack> hf((size_t)max_segs * kPostParts * s->T);
     // output range that is final once segment sg has been added: shifted positions below (sg+1)*stride
     auto final_end = [&](int i, int sg) {
         const long e = (sg == max_segs - 1) ? (long)n_samples[i] : (long)(sg + 1) * stride - shift_offset;
         return std::max(0L, std::min((long)n_samples[i], e));
     };
-    std::vector<long> max_range(max_segs, 0);
+    std::vector<long> max_range((size_t)max_segs * kPostParts, 0);
     for (int i = 0; i < n_tracks; ++i)
     {
         if (grow(&s->acc_pool[i], &s->acc_cap[i], 4 * L[i]))
@@ -911,11 +971,21 @@ int session_demix_device(Session *s, const float *const *d_audio, const int64_t 
             hs[(size_t)sg * s->T + i] = {reinterpret_cast<const float2 *>(d_audio[i]), (long)n_samples[i],
                                          off - shift_offset, clen, 0};
             hi[(size_t)sg * s->T + i] = {s->acc_pool[i], L[i], off, clen, 1};
-            const long b = sg == 0 ? 0 : final_end(i, sg - 1), e = final_end(i, sg);
-            hf[(size_t)sg * s->T + i] = {s->acc_pool[i], reinterpret_cast<float2 *>(d_out[i]), L[i], (long)n_samples[i], b, e};
-            max_range[sg] = std::max(max_range[sg], e - b);
+            // part q of the segment's post stage emits the chunk samples below 1024 * (its last frame + 1) - 2048
+            long b = sg == 0 ? 0 : final_end(i, sg - 1);
+            for (int q = 0; q < kPostParts; ++q)
+            {
+                long e = final_end(i, sg);
+                if (q + 1 < kPostParts)
+                    e = std::min(e, std::max(b, off + (long)kHop * post_part_frame(s->F, q + 1) - kPad - shift_offset));
+                const size_t d = ((size_t)sg * kPostParts + q) * s->T + i;
+                hf[d] = {s->acc_pool[i], reinterpret_cast<float2 *>(d_out[i]), L[i], (long)n_samples[i], b, e};
+                max_range[(size_t)sg * kPostParts + q] = std::max(max_range[(size_t)sg * kPostParts + q], e - b);
+                b = e;
+            }
         }
     }
+    s->ev_cursor = 0;
     { // upload through the pinned staging buffer (no host synchronisation with the stream; at most one call of run-ahead)
         UMX_CUDA_OK(cudaEventSynchronize(s->desc_copied));
         uint8_t *hp = static_cast<uint8_t *>(s->h_desc);
@@ -924,19 +994,24 @@ int session_demix_device(Session *s, const float *const *d_audio, const int64_t 
         std::memcpy(hp, hs.data(), b0);
         std::memcpy(hp + b0, hi.data(), b1);
         std::memcpy(hp + b0 + b1, hf.data(), b2);
-        UMX_CUDA_OK(cudaMemcpyAsync(s->d_stft, hp, b0, cudaMemcpyHostToDevice, s->st));
-        UMX_CUDA_OK(cudaMemcpyAsync(s->d_istft, hp + b0, b1, cudaMemcpyHostToDevice, s->st));
-        UMX_CUDA_OK(cudaMemcpyAsync(s->d_final, hp + b0 + b1, b2, cudaMemcpyHostToDevice, s->st));
-        UMX_CUDA_OK(cudaEventRecord(s->desc_copied, s->st));
+        // The tables travel at the HEAD of the input copy stream, not on the compute stream: a copy engine serves one stream's
+        // queued copies to the end before it turns to another stream's, so three small uploads issued elsewhere would sit behind
+        // every input copy of the call (measured: the first kernel then starts when the last input byte has arrived).
+        cudaEvent_t prev = take_event(s, s->ev_cursor);
+        UMX_CUDA_OK(cudaEventRecord(prev, s->st)); // the previous call's kernels (stream order) are done with the old tables
+        UMX_CUDA_OK(cudaStreamWaitEvent(s->st_in, prev, 0));
+        UMX_CUDA_OK(cudaMemcpyAsync(s->d_stft, hp, b0, cudaMemcpyHostToDevice, s->st_in));
+        UMX_CUDA_OK(cudaMemcpyAsync(s->d_istft, hp + b0, b1, cudaMemcpyHostToDevice, s->st_in));
+        UMX_CUDA_OK(cudaMemcpyAsync(s->d_final, hp + b0 + b1, b2, cudaMemcpyHostToDevice, s->st_in));
+        UMX_CUDA_OK(cudaEventRecord(s->desc_copied, s->st_in));
+        UMX_CUDA_OK(cudaStreamWaitEvent(s->st, s->desc_copied, 0));
     }
 
     size_t &ev = s->ev_cursor;
-    ev = 0;
     std::vector<long> copied_in(n_tracks, 0);
     if (s->pipeline == 3 && max_segs > 1)
         return demix_wavefront(s, d_audio, n_samples, n_tracks, shift_offset, d_out, host_in, host_out, max_segs, stride, hf, max_range);
     // in order on the caller's stream: h/c stream from segment to segment
-    std::vector<cudaEvent_t> back_done(max_segs);
     for (int sg = 0; sg < max_segs; ++sg)
     {
         if (host_in)
@@ -947,22 +1022,33 @@ int session_demix_device(Session *s, const float *const *d_audio, const int64_t 
             UMX_CUDA_OK(cudaEventRecord(e, s->st_in));
             UMX_CUDA_OK(cudaStreamWaitEvent(s->st, e, 0));
         }
-        if (int rc = session_run_segment(s, sg, n_tracks))
+        if (int rc = session_front(s, sg, n_tracks))
             return rc;
+        const NetView v = current_view(s);
+        if (int rc = run_post_stats(s, sg, n_tracks, v, s->st))
+            return rc;
+        for (int q = 0; q < kPostParts; ++q)
         {
-            StageScope sc(s, "finalize");
-            s->launches++;
-            if (int rc = launch_finalize(s->d_final + (size_t)sg * s->T, n_tracks, max_range[sg], shift_offset, s->n_buf, stride,
-                                         s->tp_nt, s->st, s->tp_t0))
+            if (int rc = run_post_part(s, sg, n_tracks, v, s->st, q))
                 return rc;
-        }
-        if (host_out)
-        { // ship the finished range of every stem while later segments compute
-            back_done[sg] = take_event(s, ev);
-            UMX_CUDA_OK(cudaEventRecord(back_done[sg], s->st));
-            UMX_CUDA_OK(cudaStreamWaitEvent(s->st_out, back_done[sg], 0));
-            if (int rc = ship_ranges(s, hf.data() + (size_t)sg * s->T, n_tracks, n_samples, d_out, host_out))
-                return rc;
+            const size_t d = ((size_t)sg * kPostParts + q) * s->T;
+            if (max_range[(size_t)sg * kPostParts + q] <= 0)
+                continue;
+            {
+                StageScope sc(s, "finalize");
+                s->launches++;
+                if (int rc = launch_finalize(s->d_final + d, n_tracks, max_range[(size_t)sg * kPostParts + q], shift_offset, s->n_buf,
+                                             stride, s->tp_nt, s->st, s->tp_t0))
+                    return rc;
+            }
+            if (host_out)
+            { // ship the finished range of every stem while later parts and segments compute
+                cudaEvent_t e = take_event(s, ev);
+                UMX_CUDA_OK(cudaEventRecord(e, s->st));
+                UMX_CUDA_OK(cudaStreamWaitEvent(s->st_out, e, 0));
+                if (int rc = ship_ranges(s, hf.data() + d, n_tracks, n_samples, d_out, host_out))
+                    return rc;
+            }
         }
     }
     if (host_out)

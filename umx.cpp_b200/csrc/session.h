@@ -11,6 +11,8 @@
 namespace umx
 {
 
+constexpr int kPostParts = 4; // runs of frames a segment's post stage is cut into (session.cu)
+
 struct StageTimer
 {
     std::string stage;
@@ -59,7 +61,7 @@ struct Session
     float *partials = nullptr, *stats = nullptr;
     float *h_state = nullptr, *c_state = nullptr; // [T][3][4][2][Hh]
     float *lstm_f32 = nullptr;               // optional fp32 LSTM output (kernel-level API), [4][Mcap][H]
-    int *tile_counters = nullptr;            // [16] GEMM tile queues, one per stream of the wavefront
+    int *tile_counters = nullptr;            // [16][2] GEMM tile queues, one per stream of the wavefront
 
     StftTrack *d_stft = nullptr;   // descriptor arrays [seg_cap][T]
     const IstftTrack *cur_chunks = nullptr; // chunk descriptors of the segment the network is running for (frames beyond a chunk are skipped)
@@ -96,6 +98,9 @@ struct Session
     std::vector<StageTimer> timers;
     std::vector<cudaEvent_t> timer_pool; // timing events are created once and reused
     size_t timer_cursor = 0;
+    std::vector<cudaEvent_t> probe_pool; // plain events that carry copy-stream positions over to the probe streams
+    size_t probe_cursor = 0;
+    cudaStream_t st_probe[2] = {};       // timestamps of the copy streams' progress are taken here (session.cu: record_timer)
     cudaEvent_t profile_base = nullptr;  // time base of the most recent profiled call
     bool profile_resolved = true;        // stage_ms holds the most recent call's times
     std::map<std::string, double> stage_ms;

@@ -407,7 +407,8 @@ __device__ __forceinline__ void red_add2(float2 *p, float2 v)
 __global__ void __launch_bounds__(kWiThreads, 1)
     wiener_istft_kernel(const float2 *__restrict__ spec, const float *__restrict__ mask, long mask_target_stride, int mask_ld,
                         const float *__restrict__ maxabs, const float *__restrict__ stats, int F,
-                        const IstftTrack *__restrict__ tracks, int n_buf, int stem_begin, int stem_count)
+                        const IstftTrack *__restrict__ tracks, int n_buf, int stem_begin, int stem_count, int frame_begin,
+                        int frame_end)
 {
     extern __shared__ __align__(128) uint8_t smem_raw[];
     float2 *sm = reinterpret_cast<float2 *>(smem_raw);                                   // four FFT workspaces
@@ -418,8 +419,8 @@ __global__ void __launch_bounds__(kWiThreads, 1)
     const int tid = threadIdx.x, half = tid >> 8, t = tid & 255;
     const int trk = blockIdx.z;
     const IstftTrack tk = tracks[trk];
-    const int f0 = blockIdx.x * kWiFrames;
-    const int f_need = frames_reaching(tk.n_wave, F); // frames that reach an emitted sample (see istft_kernel)
+    const int f0 = frame_begin + blockIdx.x * kWiFrames; // this launch emits the hops of frames [frame_begin, frame_end)
+    const int f_need = min(frame_end, frames_reaching(tk.n_wave, F)); // frames that reach an emitted sample (see istft_kernel)
     if (f0 >= f_need)
         return;
     const int f1 = min(f_need, f0 + kWiFrames);
@@ -686,8 +687,24 @@ int launch_istft(const float2 *stems, long stem_stride, int n_stems, const Istft
     return 0;
 }
 
-int launch_wiener_istft(const WienerArgs &w, const IstftTrack *d_tracks, int n_buf, cudaStream_t st)
+__global__ void zero_f32_kernel(float *p, int n)
 {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n)
+        p[i] = 0.f;
+}
+int launch_zero_f32(float *p, int n, cudaStream_t st)
+{
+    zero_f32_kernel<<<ceil_div(n, 256), 256, 0, st>>>(p, n);
+    UMX_CUDA_OK(cudaGetLastError());
+    return 0;
+}
+
+int launch_wiener_istft(const WienerArgs &w, const IstftTrack *d_tracks, int n_buf, cudaStream_t st, int frame_begin, int frame_end)
+{
+    if (frame_end < 0)
+        frame_end = w.F;
+    UMX_CHECK(frame_begin >= 0 && frame_begin < frame_end && frame_end <= w.F, "wiener_istft: bad frame range");
     UMX_CHECK(!w.mask_is_mag && w.stats && w.maxabs && w.stem_count >= 1 && w.stem_count <= 4, "wiener_istft: bad arguments");
     const size_t smem = kWiSmemBytes;
     static PerDeviceOnce once;
@@ -696,9 +713,9 @@ int launch_wiener_istft(const WienerArgs &w, const IstftTrack *d_tracks, int n_b
             return 0;
         }))
         return rc;
-    dim3 grid(ceil_div(w.F, kWiFrames), 1, w.n_tracks);
+    dim3 grid(ceil_div(frame_end - frame_begin, kWiFrames), 1, w.n_tracks);
     wiener_istft_kernel<<<grid, kWiThreads, smem, st>>>(w.spec, w.mask, w.mask_target_stride, w.mask_ld, w.maxabs, w.stats, w.F,
-                                                        d_tracks, n_buf, w.stem_begin, w.stem_count);
+                                                        d_tracks, n_buf, w.stem_begin, w.stem_count, frame_begin, frame_end);
     UMX_CUDA_OK(cudaGetLastError());
     return 0;
 }
