@@ -418,9 +418,9 @@ __global__ void __launch_bounds__(kWiThreads, 1)
     float2 *t256 = reinterpret_cast<float2 *>(smem_raw + kWiWsBytes + kWiSpecBytes + 4 * kWiMaskBytes + 16); // tw[16 m]
     const int tid = threadIdx.x, half = tid >> 8, t = tid & 255;
     const int trk = blockIdx.z;
-    const IstftTrack tk = tracks[trk];
+    const int n_wave = tracks[trk].n_wave;
     const int f0 = frame_begin + blockIdx.x * kWiFrames; // this launch emits the hops of frames [frame_begin, frame_end)
-    const int f_need = min(frame_end, frames_reaching(tk.n_wave, F)); // frames that reach an emitted sample (see istft_kernel)
+    const int f_need = min(frame_end, frames_reaching(n_wave, F)); // frames that reach an emitted sample (see istft_kernel)
     if (f0 >= f_need)
         return;
     const int f1 = min(f_need, f0 + kWiFrames);
@@ -429,7 +429,6 @@ __global__ void __launch_bounds__(kWiThreads, 1)
     const float ma = wiener_max_abs(maxabs, trk);
     const float inv_ma = 1.0f / ma;
     const float *st_base = stats + (long)trk * 16 * kBins;
-    const float2 tw_t = g_tw[t]; // (cos, -sin)(2 pi t / 4096)
 
     // the frame's inputs arrive by bulk copies issued one frame ahead (they land while the previous frame's FFTs run)
     auto stage = [&](int f) {
@@ -448,7 +447,6 @@ __global__ void __launch_bounds__(kWiThreads, 1)
     }
     if (tid < 256)
         t256[tid] = g_tw[16 * tid];
-    const float2 tw_base = g_tw[(t >> 4) * (t & 15)]; // this thread's constant factor of the pass-2 twiddles
     __syncthreads();
 
     // this half's stems: slot 0 -> stem index `half`, slot 1 -> `half + 2` (relative to stem_begin); workspace = stem index
@@ -519,6 +517,10 @@ __global__ void __launch_bounds__(kWiThreads, 1)
 #pragma unroll
             for (int a = 0; a < 16; ++a)
                 r[a] = s[256 * a + t];
+            // two per-thread constants, fetched per transform rather than held in registers across the frame loop (the kernel
+            // has none to spare): the constant factor of the pass-2 twiddles and (cos, -sin)(2 pi t / 4096) for the window
+            const float2 tw_base = __ldg(&g_tw[(t >> 4) * (t & 15)]);
+            const float2 tw_now = __ldg(&g_tw[t]);
             wi::bar_half(half);
             fft_pass1_t256<true>(t, r, s, t256);
             wi::bar_half(half);
@@ -527,21 +529,26 @@ __global__ void __launch_bounds__(kWiThreads, 1)
             fft_pass2_store_t256<true>(t, r, s, t256, tw_base);
             wi::bar_half(half);
             fft_pass3<true>(t, r, s);
-            // r[k] = (y_L, y_R)[n], n = t + 256 k: scale (in place), then overlap-add in registers
+            // r[k] = (y_L, y_R)[n], n = t + 256 k: scale (in place), then overlap-add in registers.
+            // (The 16 interior scales depend on (t, k) only, but hoisted out of the frame loop they cost 16 registers the kernel
+            // does not have: they were spilled, and with 227 KB of shared memory there is no L1 left to catch the reloads.  Two
+            // FMAs each from tw_now, which is loaded per transform, so the compiler cannot hoist them.)
 #pragma unroll
             for (int k = 0; k < 16; ++k)
             {
-                const float sc = istft_scale(f, t + 256 * k, k, F, tw_t);
+                const float sc = istft_scale(f, t + 256 * k, k, F, tw_now);
                 r[k].x *= sc;
                 r[k].y *= sc;
             }
-            const int stem = stem_begin + idx;
-            float2 *out = tk.out + (long)stem * tk.out_stem_stride + tk.out_offset;
+            // (the track descriptor is read again here rather than kept in registers across the frame loop)
+            const IstftTrack *tkp = tracks + trk;
+            float2 *out = tkp->out + (long)(stem_begin + idx) * tkp->out_stem_stride + tkp->out_offset;
+            const int accumulate = tkp->accumulate;
             auto emit = [&](int hop, int j, float2 v) {
                 const int i = kHop * hop + t + 256 * j - kPad;
-                if (i >= 0 && i < tk.n_wave)
+                if (i >= 0 && i < n_wave)
                 {
-                    if (tk.accumulate)
+                    if (accumulate)
                     { // out[off + k] += w[k] * y[k] (umx.cpp:234-249)
                         const float wgt = tri_weight(i, n_buf);
                         wi::red_add2(out + i, make_float2(wgt * v.x, wgt * v.y));
