@@ -92,6 +92,8 @@ int umx_cuda_segment_plan(int64_t n_samples, int shift_offset, int n_buf, int64_
 /* stft (src/dsp.hpp:114, src/dsp.cpp:141-176): audio float[n][2] zero-extended to n_buf;
  * spec: complex float[2049][F][2], F = nb_frames(n_buf). */
 int umx_cuda_stft(const float *audio, int n, int n_buf, float *spec);
+/* The same with true reflect padding (reflect_pad = 1: upstream's torch.stft; 0 = umx_cuda_stft). */
+int umx_cuda_stft_opts(const float *audio, int n, int n_buf, float *spec, int reflect_pad);
 /* istft (src/dsp.hpp:115, src/dsp.cpp:178-207): spec complex float[2049][F][2] -> wave float[n_wave][2] */
 int umx_cuda_istft(const float *spec, int n_buf, int n_wave, float *wave);
 /* umx_lstm_forward (src/lstm.hpp:22-24, src/lstm.cpp:101-179) for `target`, state of track slot 0:
@@ -100,6 +102,9 @@ int umx_cuda_lstm_forward(umx_cuda_session *s, int target, const float *input, i
 /* wiener_filter (src/wiener.hpp:19-21, src/wiener.cpp:92-425): mix complex float[2049][F][2] (IN/OUT:
  * left divided by max_abs like the reference), mags 4 x float[2049][F][2] -> out 4 x complex [2049][F][2] */
 int umx_cuda_wiener(float *mix, const float *mags, int F, float *out);
+/* wiener_filter with the upstream-faithful variants of the session options (all zero and niter = 1: umx_cuda_wiener):
+ * psd_abs2 / reg_once / win_len / niter as "wiener_psd" / "wiener_reg" / "wiener_win_len" / "wiener_niter" below. */
+int umx_cuda_wiener_opts(float *mix, const float *mags, int F, float *out, int psd_abs2, int reg_once, int win_len, int niter);
 /* The network only (src/inference.cpp:29-186): spec complex [2049][F][2] -> target magnitudes
  * 4 x float[2049][F][2]; LSTM state of track slot 0 advances. F == nb_frames(n_buf) of the session. */
 int umx_cuda_target_mags(umx_cuda_session *s, const float *spec, float *mags);
@@ -150,7 +155,13 @@ int umx_cuda_lstm_max_active_clusters(void);
  * layer l+1 of segment s (the h/c carry of src/lstm.cpp:160-161 is per layer), one stream per (layer, target group) with
  * "lane_targets" = 1, 2 or 4 targets per group (0, the default: 1 up to 16 tracks, else 4); results are identical,
  * "skip_zero_frames" 1 (default) = frames of a window beyond a short chunk are computed once (first layer) or not at all
- * (after the network), 0 = every frame of every 60 s window is computed as the reference does; results are identical. */
+ * (after the network), 0 = every frame of every 60 s window is computed as the reference does; results are identical.
+ * Upstream-faithful variants, all 0 by default = what the reference does (its deviations from Open-Unmix):
+ * "stft_pad" 1 = true reflect padding (torch.stft) instead of the symmetric edge copy of src/dsp.cpp:109-128,
+ * "wiener_psd" 1 = PSD |y|^2 instead of (re+im)^2 (src/wiener.cpp:187-202), "wiener_reg" 1 = regulariser added once instead
+ * of once per source (src/wiener.cpp:301-325), "wiener_win_len" N = EM statistics and max|X| per window of N frames
+ * (upstream 300; at most 19 windows per segment) instead of per segment, "wiener_niter" 0 = no EM iteration (default 1 =
+ * src/wiener.hpp:14), "lstm_reset" 1 = LSTM state zeroed before every segment instead of streamed (src/lstm.cpp:160-161). */
 int umx_cuda_session_set_option(umx_cuda_session *s, const char *name, int value);
 
 #ifdef __cplusplus

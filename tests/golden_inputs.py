@@ -88,3 +88,20 @@ def parse_cli_plan(stdout: str):
     import re
 
     return [(int(a), int(b)) for a, b in re.findall(r"offset: (\d+), chunk shape: \(2, (\d+)\)", stdout)]
+
+
+# ---- upstream-faithful variants: inputs for tests/golden/make_golden_upstream.py (which ran vendor/open-unmix-pytorch on them) ----
+UP_F = 12          # frames
+UP_WIN = 5         # frames per Wiener window (upstream default is 300; 5 gives three windows, the last one short)
+UP_BIN_STEP = 16   # bins kept in the golden file
+UP_GOLDEN = os.path.join(ROOT, "tests", "golden", "upstream_variants.npz")
+
+
+def upstream_wiener_inputs():
+    """(mix (2, F, 2049) c64, mags (4, 2, F, 2049) f32): a loud and a quiet stretch so the per-window max|X| differs."""
+    rng = np.random.default_rng(21)
+    mix = (rng.standard_normal((2, UP_F, 2049)) + 1j * rng.standard_normal((2, UP_F, 2049))).astype(np.complex64)
+    mix[:, :UP_WIN] *= 40.0
+    mix[:, UP_WIN:] *= 0.5
+    mags = (rng.uniform(0, 1, (4, 2, UP_F, 2049)) * np.abs(mix)[None]).astype(np.float32)
+    return mix, mags

@@ -128,3 +128,20 @@ def test_demix_multisegment_matches_reference_cli():
     err = float(np.abs(sub - want).max())
     sdr = float(10 * np.log10((want.astype(np.float64) ** 2).sum() / ((sub - want).astype(np.float64) ** 2).sum()))
     assert err < 1e-5 and sdr > 100.0, (err, sdr)
+
+
+def test_upstream_variants_match_open_unmix():
+    """The option-switched variants of the oracle (what the session options "stft_pad", "wiener_psd", "wiener_reg",
+    "wiener_win_len", "wiener_niter" select) against UPSTREAM Open-Unmix itself: golden vectors made by
+    tests/golden/make_golden_upstream.py from vendor/open-unmix-pytorch (torch.stft with reflect padding;
+    openunmix.filtering.wiener per window, float64)."""
+    g = np.load(gi.UP_GOLDEN)
+    assert rel(O.stft(gi.audio(), gi.N_BUF, reflect=True), g["stft_reflect"]) < 1e-5
+    assert rel(O.stft(gi.audio(), gi.N_BUF, reflect=False), g["stft_reflect"]) > 1e-3  # the reference's padding IS different
+    mix, mags = gi.upstream_wiener_inputs()
+    for it in (0, 1):
+        y = O.wiener_windows(mix, mags, gi.UP_WIN, psd_abs2=True, reg_once=True, niter=it)
+        assert rel(y[..., :: gi.UP_BIN_STEP], g[f"wiener_win_niter{it}"]) < 2e-4, it
+    # and each switch matters: the reference's own arithmetic does not reproduce upstream
+    y_ref = O.wiener_windows(mix, mags, 0)
+    assert rel(y_ref[..., :: gi.UP_BIN_STEP], g["wiener_win_niter1"]) > 1e-3

@@ -39,7 +39,7 @@ EXPORTS = [
     "umx_cuda_model_device", "umx_cuda_model_tensor", "umx_cuda_session_create", "umx_cuda_session_destroy",
     "umx_cuda_session_reset", "umx_cuda_session_get_state", "umx_cuda_infer_segment", "umx_cuda_demix",
     "umx_cuda_demix_device", "umx_cuda_segment_plan", "umx_cuda_stft", "umx_cuda_istft", "umx_cuda_lstm_forward",
-    "umx_cuda_wiener", "umx_cuda_target_mags", "umx_cuda_session_set_profiling", "umx_cuda_session_stage_ms",
+    "umx_cuda_wiener", "umx_cuda_wiener_opts", "umx_cuda_stft_opts", "umx_cuda_target_mags", "umx_cuda_session_set_profiling", "umx_cuda_session_stage_ms",
     "umx_cuda_session_launches", "umx_cuda_session_timeline", "umx_cuda_session_set_option", "umx_cuda_session_set_stream",
     "umx_cuda_wiener_noalloc", "umx_cuda_lstm_max_active_clusters", "umx_cuda_nccl_unique_id",
     "umx_cuda_session_init_target_parallel",
@@ -84,6 +84,8 @@ def lib():
     l.umx_cuda_istft.argtypes = [vp, ip, ip, vp]
     l.umx_cuda_lstm_forward.argtypes = [vp, ip, vp, ip, vp]
     l.umx_cuda_wiener.argtypes = [vp, vp, ip, vp]
+    l.umx_cuda_wiener_opts.argtypes = [vp, vp, ip, vp, ip, ip, ip, ip]
+    l.umx_cuda_stft_opts.argtypes = [vp, ip, ip, vp, ip]
     l.umx_cuda_target_mags.argtypes = [vp, vp, vp]
     l.umx_cuda_session_set_profiling.argtypes = [vp, ip]
     l.umx_cuda_session_stage_ms.restype = C.c_double
@@ -298,13 +300,14 @@ def segment_plan(n_samples: int, shift_offset: int = DEFAULT_SHIFT_OFFSET, n_buf
 
 
 # -- src/dsp.hpp:114-115
-def stft(audio: np.ndarray, n_buf: int | None = None) -> np.ndarray:
+def stft(audio: np.ndarray, n_buf: int | None = None, reflect_pad: bool = False) -> np.ndarray:
+    """reflect_pad: true reflect padding (upstream torch.stft) instead of the reference's symmetric edge copy."""
     n = audio.shape[1]
     n_buf = n if n_buf is None else n_buf
     F = nb_frames(n_buf)
     a = np.ascontiguousarray(audio.T.astype(np.float32))
     out = np.empty(2 * F * NB_BINS, dtype=np.complex64)
-    _check(lib().umx_cuda_stft(_p(a), n, n_buf, _p(out)), "stft")
+    _check(lib().umx_cuda_stft_opts(_p(a), n, n_buf, _p(out), int(reflect_pad)), "stft")
     return _spec_from_ref(out, F)
 
 
@@ -317,13 +320,14 @@ def istft(spec: np.ndarray, n_buf: int, n_wave: int | None = None) -> np.ndarray
 
 
 # -- src/wiener.hpp:19-21
-def wiener_filter(mix: np.ndarray, mags: np.ndarray):
-    """-> (y (4,2,F,B) complex64, mix/max_abs as the reference leaves its first argument)."""
+def wiener_filter(mix: np.ndarray, mags: np.ndarray, psd_abs2: bool = False, reg_once: bool = False, win_len: int = 0, niter: int = 1):
+    """-> (y (4,2,F,B) complex64, mix/max_abs as the reference leaves its first argument).  The keyword arguments select the
+    upstream-faithful variants (session options "wiener_psd", "wiener_reg", "wiener_win_len", "wiener_niter")."""
     F = mix.shape[1]
     m = _spec_to_ref(mix.astype(np.complex64))
     g = np.ascontiguousarray(mags.astype(np.float32).transpose(0, 3, 2, 1))
     out = np.empty((4, NB_BINS, F, 2), dtype=np.complex64)
-    _check(lib().umx_cuda_wiener(_p(m), _p(g), F, _p(out)), "wiener_filter")
+    _check(lib().umx_cuda_wiener_opts(_p(m), _p(g), F, _p(out), int(psd_abs2), int(reg_once), int(win_len), int(niter)), "wiener_filter")
     return np.ascontiguousarray(out.transpose(0, 3, 2, 1)), _spec_from_ref(m.reshape(-1), F)
 
 

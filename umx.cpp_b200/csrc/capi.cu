@@ -349,6 +349,37 @@ int umx_cuda_session_set_option(umx_cuda_session *s, const char *name, int value
         UMX_CHECK(value == 1 || lstm_cluster_supported(s->s->Hh), "lstm_impl = 0: the cluster recurrence kernel does not support this model's hidden size");
         s->s->lstm_impl = value;
     }
+    else if (n == "stft_pad")
+    {
+        UMX_CHECK(value == 0 || value == 1, "stft_pad must be 0 (the reference's symmetric edge copy) or 1 (reflect)");
+        s->s->stft_reflect = value;
+    }
+    else if (n == "wiener_psd")
+    {
+        UMX_CHECK(value == 0 || value == 1, "wiener_psd must be 0 (the reference's (re+im)^2) or 1 (|y|^2)");
+        s->s->wiener_psd_abs2 = value;
+    }
+    else if (n == "wiener_reg")
+    {
+        UMX_CHECK(value == 0 || value == 1, "wiener_reg must be 0 (regulariser once per source, as the reference) or 1 (once)");
+        s->s->wiener_reg_once = value;
+    }
+    else if (n == "wiener_win_len")
+    {
+        UMX_CHECK(value == 0 || (value > 0 && (s->s->F + value - 1) / value <= kWienerChunks),
+                  "wiener_win_len must be 0 (whole segment) or give at most 19 windows per segment");
+        s->s->wiener_win_len = value;
+    }
+    else if (n == "wiener_niter")
+    {
+        UMX_CHECK(value == 0 || value == 1, "wiener_niter must be 0 (no EM iteration) or 1 (one, as the reference)");
+        s->s->wiener_niter = value;
+    }
+    else if (n == "lstm_reset")
+    {
+        UMX_CHECK(value == 0 || value == 1, "lstm_reset must be 0 (state streams across segments, as the reference) or 1");
+        s->s->lstm_reset = value;
+    }
     else
     {
         set_error("umx_cuda_session_set_option: unknown option " + n);
@@ -363,7 +394,9 @@ int umx_cuda_session_set_option(umx_cuda_session *s, const char *name, int value
 extern "C"
 {
 
-int umx_cuda_stft(const float *audio, int n, int n_buf, float *spec)
+int umx_cuda_stft(const float *audio, int n, int n_buf, float *spec) { return umx_cuda_stft_opts(audio, n, n_buf, spec, 0); }
+
+int umx_cuda_stft_opts(const float *audio, int n, int n_buf, float *spec, int reflect_pad)
 {
     if (require_device())
         return -1;
@@ -382,7 +415,7 @@ int umx_cuda_stft(const float *audio, int n, int n_buf, float *spec)
     UMX_CUDA_OK(cudaMemcpy(d_audio.p, audio, sizeof(float2) * (size_t)n, cudaMemcpyHostToDevice));
     StftTrack tk{d_audio.as<float2>(), n, 0, n, 0};
     UMX_CUDA_OK(cudaMemcpy(d_desc.p, &tk, sizeof tk, cudaMemcpyHostToDevice));
-    if (int rc = launch_stft(d_desc.as<StftTrack>(), 1, n_buf, d_spec.as<float2>(), nullptr, nullptr, nullptr, 0))
+    if (int rc = launch_stft(d_desc.as<StftTrack>(), 1, n_buf, d_spec.as<float2>(), nullptr, nullptr, nullptr, 0, 0, reflect_pad != 0))
         return rc;
     if (int rc = launch_to_ref_layout_c64(d_spec.as<float2>(), d_ref.as<float2>(), F, 0))
         return rc;
@@ -417,16 +450,21 @@ int umx_cuda_istft(const float *spec, int n_buf, int n_wave, float *wave)
     return 0;
 }
 
-int umx_cuda_wiener(float *mix, const float *mags, int F, float *out)
+int umx_cuda_wiener(float *mix, const float *mags, int F, float *out) { return umx_cuda_wiener_opts(mix, mags, F, out, 0, 0, 0, 1); }
+
+int umx_cuda_wiener_opts(float *mix, const float *mags, int F, float *out, int psd_abs2, int reg_once, int win_len, int niter)
 {
     if (require_device())
         return -1;
     UMX_CHECK(mix && mags && out && F >= 1, "umx_cuda_wiener: bad argument");
+    UMX_CHECK(niter == 0 || niter == 1, "umx_cuda_wiener_opts: niter must be 0 or 1");
+    const int n_win = win_len > 0 ? (F + win_len - 1) / win_len : 1;
+    UMX_CHECK(win_len >= 0 && n_win <= kWienerChunks, "umx_cuda_wiener_opts: at most 19 windows");
     const size_t e = (size_t)F * 2 * kBins;
     DevBuf d_ref, d_mix, d_mixo, d_mref, d_mag, d_max, d_part, d_stats, d_out, d_desc;
     if (d_ref.alloc(sizeof(float2) * e * 4) || d_mix.alloc(sizeof(float2) * e) || d_mixo.alloc(sizeof(float2) * e) ||
-        d_mref.alloc(sizeof(float) * e * 4) || d_mag.alloc(sizeof(float) * e * 4) || d_max.alloc(sizeof(float)) ||
-        d_part.alloc(sizeof(float) * kWienerChunks * 20 * kBins) || d_stats.alloc(sizeof(float) * 16 * kBins) ||
+        d_mref.alloc(sizeof(float) * e * 4) || d_mag.alloc(sizeof(float) * e * 4) || d_max.alloc(sizeof(float) * kWienerChunks) ||
+        d_part.alloc(sizeof(float) * kWienerChunks * 20 * kBins) || d_stats.alloc(sizeof(float) * kWienerChunks * 16 * kBins) ||
         d_out.alloc(sizeof(float2) * e * 4))
         return -1;
     UMX_CUDA_OK(cudaMemcpy(d_ref.p, mix, sizeof(float2) * e, cudaMemcpyHostToDevice));
@@ -436,14 +474,17 @@ int umx_cuda_wiener(float *mix, const float *mags, int F, float *out)
     for (int j = 0; j < 4; ++j)
         if (int rc = launch_from_ref_layout_f32(d_mref.as<float>() + j * e, d_mag.as<float>() + j * e, F, 0))
             return rc;
-    // max |X| on the host side of the API would cost a pass; reuse the reduction idiom of the STFT kernel
-    {
-        std::vector<float> h(2 * e);
-        std::memcpy(h.data(), mix, sizeof(float) * 2 * e);
-        float mx = 0.f;
-        for (size_t i = 0; i < e; ++i)
-            mx = std::max(mx, std::sqrt(h[2 * i] * h[2 * i] + h[2 * i + 1] * h[2 * i + 1]));
-        UMX_CUDA_OK(cudaMemcpy(d_max.p, &mx, sizeof(float), cudaMemcpyHostToDevice));
+    { // max |X| per window; the reference order of mix is [bin][frame][channel]
+        std::vector<float> mx(kWienerChunks, 0.f);
+        for (int b = 0; b < kBins; ++b)
+            for (int f = 0; f < F; ++f)
+                for (int c = 0; c < 2; ++c)
+                {
+                    const float *z = mix + 2 * (((size_t)b * F + f) * 2 + c);
+                    float &m = mx[win_len > 0 ? f / win_len : 0];
+                    m = std::max(m, std::sqrt(z[0] * z[0] + z[1] * z[1]));
+                }
+        UMX_CUDA_OK(cudaMemcpy(d_max.p, mx.data(), sizeof(float) * kWienerChunks, cudaMemcpyHostToDevice));
     }
     WienerArgs w{};
     w.spec = d_mix.as<float2>();
@@ -454,6 +495,11 @@ int umx_cuda_wiener(float *mix, const float *mags, int F, float *out)
     w.maxabs = d_max.as<float>();
     w.partials = d_part.as<float>();
     w.stats = d_stats.as<float>();
+    w.stat_windows = kWienerChunks;
+    w.psd_abs2 = psd_abs2 != 0;
+    w.reg_once = reg_once != 0;
+    w.win_len = win_len;
+    w.no_em = niter == 0;
     w.out = d_out.as<float2>();
     w.out_stem_stride = (long)e;
     w.mix_out = d_mixo.as<float2>();

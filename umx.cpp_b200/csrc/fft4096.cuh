@@ -203,5 +203,15 @@ UMX_HD int padded_to_sample(int P, int n_buf)
         P = 2 * n_buf + 4095 - P;
     return P - 2048;
 }
+// The same map for true reflect padding (torch.stft(center=True, pad_mode="reflect"), what upstream Open-Unmix does: the edge
+// sample is NOT repeated): option "stft_pad" = 1.
+UMX_HD int padded_to_sample_reflect(int P, int n_buf)
+{
+    if (P < 2048)
+        return 2048 - P;
+    if (P >= n_buf + 2048)
+        return 2 * n_buf + 2046 - P;
+    return P - 2048;
+}
 
 } // namespace umx

@@ -36,9 +36,12 @@ constexpr int kIstftFramesPerCta = 32; // + 3 halo frames recomputed per CTA
 
 int init_fft_tables(int device);
 int launch_zero_f32(float *p, int n, cudaStream_t st); // p[0..n) = 0 by a kernel (stays on the compute engines)
+int launch_zero_strided(float *p, long stride, long off, int count, int n_tracks, cudaStream_t st); // p[trk*stride + off + i] = 0
 // skip_zero: frames beyond the first all-zero one of a short chunk are not computed (nothing downstream reads them)
+// maxabs: [track][stat_windows] max |X| per Wiener window (window = frame / win_len; win_len = 0: one window, slot 0)
+// reflect_pad: 0 = the reference's symmetric edge copy (src/dsp.cpp:109-128), 1 = true reflect padding (upstream torch.stft)
 int launch_stft(const StftTrack *d_tracks, int n_tracks, int n_buf, float2 *spec, __half *xh, __half *xl,
-                float *maxabs, cudaStream_t st, int skip_zero = 0);
+                float *maxabs, cudaStream_t st, int skip_zero = 0, int reflect_pad = 0, int win_len = 0, int stat_windows = 1);
 int launch_istft(const float2 *stems, long stem_stride, int n_stems, const IstftTrack *d_tracks, int n_tracks,
                  int n_buf, cudaStream_t st, int stem_begin = 0);
 int launch_finalize(const FinalizeTrack *d_tracks, int n_tracks, long max_range, int shift, int n_buf, int stride, int n_stems,
@@ -148,9 +151,10 @@ struct WienerArgs
     long mask_target_stride;
     int mask_ld;
     int mask_is_mag;      // 1: inputs are |Y_j| (kernel-level API), 0: inputs are the masks
-    const float *maxabs;  // [track] max |X|
-    float *partials;      // [track][chunks][2049][20]
-    float *stats;         // [track][2049][16]
+    const float *maxabs;  // [track][stat_windows] max |X| per window (slot 0 when win_len == 0)
+    float *partials;      // [track][chunks][20][2049]
+    float *stats;         // [track][stat_windows][16][2049]
+    int stat_windows;     // window slots per track in maxabs / stats: >= number of windows (1 is enough when win_len == 0)
     float2 *out;          // [4][M][2][2049]; null: statistics only (the filter pass is fused into the inverse STFT)
     long out_stem_stride;
     float2 *mix_out;      // optional: mix / max_abs (the reference mutates its argument)
@@ -158,6 +162,12 @@ struct WienerArgs
     int n_tracks;
     int stem_begin, stem_count; // stems whose output is written (all 4 unless target-parallel)
     const IstftTrack *chunks; // optional, per track: only the frames that reach its chunk are reduced and filtered
+    // upstream-faithful variants (all 0 = the reference's behaviour, src/wiener.cpp):
+    int psd_abs2;  // 1: PSD v = mean_ch |y|^2 (upstream filtering.py) instead of ((re+im)_L^2 + (re+im)_R^2)/2 (wiener.cpp:187-202)
+    int reg_once;  // 1: sqrt(eps) I added to Cxx once (upstream) instead of once per source (wiener.cpp:301-325)
+    int win_len;   // > 0: statistics and max|X| per window of win_len frames (upstream wiener_win_len = 300), <= kWienerChunks
+                   //      windows; 0: one window = the whole segment (the reference)
+    int no_em;     // 1: no EM iteration (upstream niter = 0): y_j = mask_j X
 };
 constexpr int kWienerChunks = 19;
 int launch_wiener(const WienerArgs &a, cudaStream_t st);

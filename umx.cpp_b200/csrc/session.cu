@@ -202,7 +202,7 @@ int session_create(Model *m, int max_tracks, int n_buf, Session **out)
     for (int i = 0; i < Session::kSpecRing; ++i)
     {
         rc |= salloc(s, &s->spec_ring[i], M * 2 * kBins);
-        rc |= salloc(s, &s->maxabs_ring[i], (size_t)s->T, true);
+        rc |= salloc(s, &s->maxabs_ring[i], (size_t)s->T * kWienerChunks, true);
     }
     rc |= salloc(s, &s->xh, M * kFc1InPad, true); // pad columns stay zero
     rc |= salloc(s, &s->xl, M * kFc1InPad, true);
@@ -227,7 +227,7 @@ int session_create(Model *m, int max_tracks, int n_buf, Session **out)
     for (int i = 0; i < Session::kMaskRing; ++i)
         rc |= salloc(s, &s->mask_ring[i], 4 * M * kMaskLd);
     rc |= salloc(s, &s->partials, (size_t)s->T * kWienerChunks * 20 * kBins);
-    rc |= salloc(s, &s->stats, (size_t)s->T * 16 * kBins);
+    rc |= salloc(s, &s->stats, (size_t)s->T * kWienerChunks * 16 * kBins);
     rc |= salloc(s, &s->h_state, (size_t)s->T * 3 * 8 * s->Hh, true);
     rc |= salloc(s, &s->c_state, (size_t)s->T * 3 * 8 * s->Hh, true);
     rc |= salloc(s, &s->tile_counters, 2 * 16, true);
@@ -491,6 +491,13 @@ static int net_layer_rec(Session *s, const NetView &v, int l, int n_tracks, int 
     a.target_begin = t0;
     a.target_count = nt;
     a.chunks = l == 0 ? v.chunks : nullptr;
+    if (s->lstm_reset)
+    { // upstream: every segment starts from zero state (the reference streams h/c across segments, src/lstm.cpp:160-161)
+        const long off = (long)t0 * 2 * Hh;
+        if (launch_zero_strided(a.h_state, a.state_track_stride, off, nt * 2 * Hh, n_tracks, st) ||
+            launch_zero_strided(a.c_state, a.state_track_stride, off, nt * 2 * Hh, n_tracks, st))
+            return -1;
+    }
     s->launches++;
     if (s->lstm_impl == 0)
     {
@@ -587,10 +594,11 @@ static int run_stft(Session *s, int seg, int n_tracks, const NetView &v, cudaStr
     StageScope sc(s, "stft", st);
     // max|X| per track starts at zero: a kernel, not a memset node (a copy engine may serve memsets, and there they queue behind
     // the host<->device copies of the whole call)
-    if (int rc = launch_zero_f32(v.maxabs, s->T, st))
+    if (int rc = launch_zero_f32(v.maxabs, s->T * kWienerChunks, st))
         return rc;
     s->launches++;
-    return launch_stft(s->d_stft + (size_t)seg * s->T, n_tracks, s->n_buf, v.spec, s->xh, s->xl, v.maxabs, st, s->skip_zero_frames);
+    return launch_stft(s->d_stft + (size_t)seg * s->T, n_tracks, s->n_buf, v.spec, s->xh, s->xl, v.maxabs, st, s->skip_zero_frames,
+                       s->stft_reflect, s->wiener_win_len, kWienerChunks);
 }
 
 int session_front(Session *s, int seg, int n_tracks)
@@ -623,6 +631,11 @@ static WienerArgs post_args(Session *s, int seg, int n_tracks, const NetView &v)
     w.maxabs = v.maxabs;
     w.partials = s->partials;
     w.stats = s->stats;
+    w.stat_windows = kWienerChunks;
+    w.psd_abs2 = s->wiener_psd_abs2;
+    w.reg_once = s->wiener_reg_once;
+    w.win_len = s->wiener_win_len;
+    w.no_em = s->wiener_niter == 0;
     w.out = nullptr; // statistics only
     w.out_stem_stride = 0;
     w.mix_out = nullptr;

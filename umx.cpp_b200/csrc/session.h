@@ -93,6 +93,13 @@ struct Session
     void *tp_comm = nullptr; // ncclComm_t
     // options
     int gemm_impl = 0, gemm_terms = 3, lstm_impl = 0;
+    // upstream-faithful variants (all 0 = what the reference does; SURVEY Appendix B lists the reference's deviations)
+    int stft_reflect = 0;      // "stft_pad" 1: true reflect padding (torch.stft) instead of the symmetric edge copy (src/dsp.cpp:109-128)
+    int wiener_psd_abs2 = 0;   // "wiener_psd" 1: v = mean_ch |y|^2 instead of ((re+im)_L^2 + (re+im)_R^2)/2 (src/wiener.cpp:187-202)
+    int wiener_reg_once = 0;   // "wiener_reg" 1: sqrt(eps) I added once instead of once per source (src/wiener.cpp:301-325)
+    int wiener_win_len = 0;    // "wiener_win_len" N: EM statistics per window of N frames (upstream 300) instead of per segment
+    int wiener_niter = 1;      // "wiener_niter" 0: no EM iteration (y = mask X); 1: one iteration (src/wiener.hpp:14)
+    int lstm_reset = 0;        // "lstm_reset" 1: h/c zeroed before every segment (upstream) instead of streamed (src/lstm.cpp:160-161)
     // measurement
     bool profiling = false;
     std::vector<StageTimer> timers;

@@ -73,7 +73,8 @@ int init_fft_tables(int device)
 // ------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256) stft_kernel(const StftTrack *__restrict__ tracks, int n_buf, int F,
                                                    float2 *__restrict__ spec, __half *__restrict__ xh,
-                                                   __half *__restrict__ xl, float *__restrict__ maxabs, int skip_zero)
+                                                   __half *__restrict__ xl, float *__restrict__ maxabs, int skip_zero,
+                                                   int reflect_pad, int win_len, int stat_windows)
 {
     __shared__ float2 s[kFftSmemFloat2];
     __shared__ float s_red[8];
@@ -91,7 +92,7 @@ __global__ void __launch_bounds__(256) stft_kernel(const StftTrack *__restrict__
     for (int a = 0; a < 16; ++a)
     {
         const int n = 256 * a + t;
-        const int smp = padded_to_sample(kHop * f + n, n_buf);
+        const int smp = reflect_pad ? padded_to_sample_reflect(kHop * f + n, n_buf) : padded_to_sample(kHop * f + n, n_buf);
         float2 v = make_float2(0.f, 0.f);
         if (smp < tk.n_valid)
         {
@@ -160,7 +161,7 @@ __global__ void __launch_bounds__(256) stft_kernel(const StftTrack *__restrict__
 #pragma unroll
             for (int i = 1; i < 8; ++i)
                 m = fmaxf(m, s_red[i]);
-            atomicMax(reinterpret_cast<int *>(maxabs) + trk, __float_as_int(m)); // m >= 0
+            atomicMax(reinterpret_cast<int *>(maxabs) + trk * stat_windows + (win_len > 0 ? f / win_len : 0), __float_as_int(m)); // m >= 0
         }
     }
 }
@@ -408,8 +409,9 @@ __global__ void __launch_bounds__(kWiThreads, 1)
     wiener_istft_kernel(const float2 *__restrict__ spec, const float *__restrict__ mask, long mask_target_stride, int mask_ld,
                         const float *__restrict__ maxabs, const float *__restrict__ stats, int F,
                         const IstftTrack *__restrict__ tracks, int n_buf, int stem_begin, int stem_count, int frame_begin,
-                        int frame_end)
+                        int frame_end, int stat_windows, int win_len, int flags)
 {
+    const int psd_abs2 = flags & 1, reg_once = (flags >> 1) & 1, no_em = (flags >> 2) & 1; // WienerArgs: upstream-faithful variants
     extern __shared__ __align__(128) uint8_t smem_raw[];
     float2 *sm = reinterpret_cast<float2 *>(smem_raw);                                   // four FFT workspaces
     const float2 *in_spec = reinterpret_cast<const float2 *>(smem_raw + kWiWsBytes);     // [2][2049] mixture of the frame
@@ -426,9 +428,6 @@ __global__ void __launch_bounds__(kWiThreads, 1)
     const int f1 = min(f_need, f0 + kWiFrames);
     const bool last_cta = (f1 == F);
     const int f_first = max(f0 - 3, 0);
-    const float ma = wiener_max_abs(maxabs, trk);
-    const float inv_ma = 1.0f / ma;
-    const float *st_base = stats + (long)trk * 16 * kBins;
 
     // the frame's inputs arrive by bulk copies issued one frame ahead (they land while the previous frame's FFTs run)
     auto stage = [&](int f) {
@@ -463,6 +462,11 @@ __global__ void __launch_bounds__(kWiThreads, 1)
     for (int f = f_first; f < f1; ++f)
     {
         // ---- A: filter; Z_j = Y_jL + i Y_jR and its Hermitian extension into workspace j
+        // statistics and max|X| of this frame's window (one window = the whole segment unless win_len > 0)
+        const int slot = trk * stat_windows + wiener_window(f, win_len);
+        const float ma = wiener_max_abs(maxabs, slot);
+        const float inv_ma = 1.0f / ma;
+        const float *st_base = stats + (long)slot * 16 * kBins;
         wi::mbar_wait(bar, parity);
         parity ^= 1;
 #pragma unroll 2
@@ -471,7 +475,7 @@ __global__ void __launch_bounds__(kWiThreads, 1)
             float R[16];
 #pragma unroll
             for (int i = 0; i < 16; ++i)
-                R[i] = __ldg(st_base + (long)i * kBins + b);
+                R[i] = no_em ? 0.f : __ldg(st_base + (long)i * kBins + b);
             WienerIn in;
             in.XL = in_spec[b];
             in.XR = in_spec[kBins + b];
@@ -483,7 +487,7 @@ __global__ void __launch_bounds__(kWiThreads, 1)
                 in.mR[j] = mk[kBins + b];
             }
             WienerCommon c;
-            wiener_common(in, R, inv_ma, 0, c);
+            wiener_common(in, R, inv_ma, 0, c, psd_abs2, reg_once);
 #pragma unroll
             for (int j = 0; j < 4; ++j)
             {
@@ -491,7 +495,13 @@ __global__ void __launch_bounds__(kWiThreads, 1)
                 if (idx < 0 || idx >= stem_count)
                     continue;
                 float2 yL, yR;
-                wiener_source(c, R, j, ma, yL, yR);
+                if (no_em)
+                { // no EM iteration: y_j = mask_j X
+                    yL = make_float2(in.mL[j] * in.XL.x, in.mL[j] * in.XL.y);
+                    yR = make_float2(in.mR[j] * in.XR.x, in.mR[j] * in.XR.y);
+                }
+                else
+                    wiener_source(c, R, j, ma, yL, yR);
                 float2 *w = sm + idx * kFftSmemFloat2;
                 if (b == 0 || b == kBins - 1)
                     w[b == 0 ? 0 : 2048] = make_float2(yL.x, yR.x); // the half-spectrum inverse ignores Im of DC and Nyquist
@@ -667,11 +677,12 @@ __global__ void from_ref_layout_kernel(const T *__restrict__ in, T *__restrict__
 // launchers
 // ------------------------------------------------------------------------------------------------
 int launch_stft(const StftTrack *d_tracks, int n_tracks, int n_buf, float2 *spec, __half *xh, __half *xl,
-                float *maxabs, cudaStream_t st, int skip_zero)
+                float *maxabs, cudaStream_t st, int skip_zero, int reflect_pad, int win_len, int stat_windows)
 {
     const int F = n_buf / kHop + 1;
+    UMX_CHECK(win_len <= 0 || ceil_div(F, win_len) <= stat_windows, "stft: more Wiener windows than max|X| slots");
     dim3 grid(F, n_tracks);
-    stft_kernel<<<grid, 256, 0, st>>>(d_tracks, n_buf, F, spec, xh, xl, maxabs, skip_zero);
+    stft_kernel<<<grid, 256, 0, st>>>(d_tracks, n_buf, F, spec, xh, xl, maxabs, skip_zero, reflect_pad, win_len, stat_windows);
     UMX_CUDA_OK(cudaGetLastError());
     return 0;
 }
@@ -707,12 +718,28 @@ int launch_zero_f32(float *p, int n, cudaStream_t st)
     return 0;
 }
 
+// p[track * stride + off + i] = 0 for i < count, track < n_tracks
+__global__ void zero_strided_kernel(float *p, long stride, long off, int count)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < count)
+        p[(long)blockIdx.y * stride + off + i] = 0.f;
+}
+int launch_zero_strided(float *p, long stride, long off, int count, int n_tracks, cudaStream_t st)
+{
+    zero_strided_kernel<<<dim3(ceil_div(count, 256), n_tracks), 256, 0, st>>>(p, stride, off, count);
+    UMX_CUDA_OK(cudaGetLastError());
+    return 0;
+}
+
 int launch_wiener_istft(const WienerArgs &w, const IstftTrack *d_tracks, int n_buf, cudaStream_t st, int frame_begin, int frame_end)
 {
     if (frame_end < 0)
         frame_end = w.F;
     UMX_CHECK(frame_begin >= 0 && frame_begin < frame_end && frame_end <= w.F, "wiener_istft: bad frame range");
-    UMX_CHECK(!w.mask_is_mag && w.stats && w.maxabs && w.stem_count >= 1 && w.stem_count <= 4, "wiener_istft: bad arguments");
+    UMX_CHECK(!w.mask_is_mag && w.stats && w.maxabs && w.stem_count >= 1 && w.stem_count <= 4 && w.stat_windows >= 1,
+              "wiener_istft: bad arguments");
+    UMX_CHECK(w.win_len <= 0 || ceil_div(w.F, w.win_len) <= w.stat_windows, "wiener_istft: more windows than statistics slots");
     const size_t smem = kWiSmemBytes;
     static PerDeviceOnce once;
     if (int rc = once.run([&](int) {
@@ -722,7 +749,9 @@ int launch_wiener_istft(const WienerArgs &w, const IstftTrack *d_tracks, int n_b
         return rc;
     dim3 grid(ceil_div(frame_end - frame_begin, kWiFrames), 1, w.n_tracks);
     wiener_istft_kernel<<<grid, kWiThreads, smem, st>>>(w.spec, w.mask, w.mask_target_stride, w.mask_ld, w.maxabs, w.stats, w.F,
-                                                        d_tracks, n_buf, w.stem_begin, w.stem_count, frame_begin, frame_end);
+                                                        d_tracks, n_buf, w.stem_begin, w.stem_count, frame_begin, frame_end,
+                                                        w.stat_windows, w.win_len,
+                                                        (w.psd_abs2 ? 1 : 0) | (w.reg_once ? 2 : 0) | (w.no_em ? 4 : 0));
     UMX_CUDA_OK(cudaGetLastError());
     return 0;
 }

@@ -29,11 +29,13 @@ __global__ void __launch_bounds__(256) wiener_reduce_kernel(const WienerArgs a)
     const int chunk = blockIdx.y, trk = blockIdx.z;
     if (b >= kBins)
         return;
-    const int fc = (a.F + kWienerChunks - 1) / kWienerChunks;
+    // chunk = a run of frames whose partial sums are kept apart: F/19 frames each for whole-segment statistics, one window each
+    // when the statistics are per window (a.win_len > 0)
+    const int fc = a.win_len > 0 ? a.win_len : (a.F + kWienerChunks - 1) / kWienerChunks;
     // frames beyond the chunk have an all-zero mixture spectrum: exactly zero terms in every sum (and the masks there are not computed)
     const int f_lim = a.chunks ? frames_reaching(a.chunks[trk].n_wave, a.F) : a.F;
     const int f_begin = chunk * fc, f_end = min(f_lim, f_begin + fc);
-    const float ma = 1.0f / wiener_max_abs(a.maxabs, trk); // reciprocal: see initial_estimate
+    const float ma = 1.0f / wiener_max_abs(a.maxabs, trk * a.stat_windows + (a.win_len > 0 ? chunk : 0)); // reciprocal: see initial_estimate
     float acc[kWienerQ];
 #pragma unroll
     for (int i = 0; i < kWienerQ; ++i)
@@ -54,12 +56,11 @@ __global__ void __launch_bounds__(256) wiener_reduce_kernel(const WienerArgs a)
             {
                 const float2 yL = initial_estimate(in[u].mL[j], in[u].XL, ma, a.mask_is_mag);
                 const float2 yR = initial_estimate(in[u].mR[j], in[u].XR, ma, a.mask_is_mag);
-                const float sL = yL.x + yL.y, sR = yR.x + yR.y;
                 acc[5 * j + 0] += yL.x * yL.x + yL.y * yL.y;
                 acc[5 * j + 1] += yR.x * yR.x + yR.y * yR.y;
                 acc[5 * j + 2] += yL.x * yR.x + yL.y * yR.y; // yL * conj(yR)
                 acc[5 * j + 3] += yL.y * yR.x - yL.x * yR.y;
-                acc[5 * j + 4] += (sL * sL + sR * sR) * 0.5f;
+                acc[5 * j + 4] += wiener_psd(yL, yR, a.psd_abs2);
             }
         }
     }
@@ -72,16 +73,17 @@ __global__ void __launch_bounds__(256) wiener_reduce_kernel(const WienerArgs a)
 __global__ void __launch_bounds__(256) wiener_finalize_kernel(const WienerArgs a)
 {
     const int b = blockIdx.x * 256 + threadIdx.x;
-    const int trk = blockIdx.y;
+    const int trk = blockIdx.y, win = blockIdx.z; // one window: all chunks (whole-segment statistics) or chunk `win`
     if (b >= kBins)
         return;
     const float *p = a.partials + (long)trk * kWienerChunks * kWienerQ * kBins + b;
-    float *s = a.stats + (long)trk * 16 * kBins + b;
+    float *s = a.stats + ((long)trk * a.stat_windows + win) * 16 * kBins + b;
+    const int c_begin = a.win_len > 0 ? win : 0, c_end = a.win_len > 0 ? win + 1 : kWienerChunks;
 #pragma unroll
     for (int j = 0; j < 4; ++j)
     {
         float q[5] = {0.f, 0.f, 0.f, 0.f, kWienerEps}; // weight starts at eps (wiener.cpp:210)
-        for (int c = 0; c < kWienerChunks; ++c)
+        for (int c = c_begin; c < c_end; ++c)
 #pragma unroll
             for (int i = 0; i < 5; ++i)
                 q[i] += p[((long)c * kWienerQ + 5 * j + i) * kBins];
@@ -102,15 +104,9 @@ __global__ void __launch_bounds__(256) wiener_apply_kernel(const WienerArgs a)
     const int f_begin = blockIdx.y * kWienerApplyFrames, f_end = min(f_lim, f_begin + kWienerApplyFrames);
     if (f_begin >= f_end)
         return;
-    const float ma = wiener_max_abs(a.maxabs, trk);
-    const float inv_ma = 1.0f / ma;
+    int win = -1;
+    float ma = 1.f, inv_ma = 1.f;
     float R[16];
-    {
-        const float *s = a.stats + (long)trk * 16 * kBins + b;
-#pragma unroll
-        for (int i = 0; i < 16; ++i)
-            R[i] = s[(long)i * kBins];
-    }
     for (int f0 = f_begin; f0 < f_end; f0 += 2)
     {
         WienerIn in[2];
@@ -123,15 +119,31 @@ __global__ void __launch_bounds__(256) wiener_apply_kernel(const WienerArgs a)
             const int f = f0 + u;
             if (f >= f_end)
                 break;
+            if (wiener_window(f, a.win_len) != win)
+            { // statistics and max|X| of this frame's window (one window unless a.win_len > 0)
+                win = wiener_window(f, a.win_len);
+                ma = wiener_max_abs(a.maxabs, trk * a.stat_windows + win);
+                inv_ma = 1.0f / ma;
+                const float *s = a.stats + ((long)trk * a.stat_windows + win) * 16 * kBins + b;
+#pragma unroll
+                for (int i = 0; i < 16; ++i)
+                    R[i] = s[(long)i * kBins];
+            }
             const long row = (long)trk * a.F + f;
             WienerCommon c;
-            wiener_common(in[u], R, inv_ma, a.mask_is_mag, c);
+            wiener_common(in[u], R, inv_ma, a.mask_is_mag, c, a.psd_abs2, a.reg_once);
 #pragma unroll
             for (int j = 0; j < 4; ++j)
                 if (j >= a.stem_begin && j < a.stem_begin + a.stem_count) // target-parallel ranks only write their own stems
                 {
                     float2 y0, y1;
-                    wiener_source(c, R, j, ma, y0, y1);
+                    if (a.no_em)
+                    { // no EM iteration: the initial estimate itself
+                        y0 = initial_estimate(in[u].mL[j], in[u].XL, 1.f, a.mask_is_mag);
+                        y1 = initial_estimate(in[u].mR[j], in[u].XR, 1.f, a.mask_is_mag);
+                    }
+                    else
+                        wiener_source(c, R, j, ma, y0, y1);
                     float2 *o = a.out + (long)j * a.out_stem_stride + (row * 2) * kBins + b;
                     o[0] = y0;
                     o[kBins] = y1;
@@ -148,10 +160,15 @@ __global__ void __launch_bounds__(256) wiener_apply_kernel(const WienerArgs a)
 int launch_wiener(const WienerArgs &a, cudaStream_t st)
 {
     const int tiles = ceil_div(kBins, 256);
-    wiener_reduce_kernel<<<dim3(tiles, kWienerChunks, a.n_tracks), 256, 0, st>>>(a);
-    UMX_CUDA_OK(cudaGetLastError());
-    wiener_finalize_kernel<<<dim3(tiles, a.n_tracks), 256, 0, st>>>(a);
-    UMX_CUDA_OK(cudaGetLastError());
+    const int n_win = a.win_len > 0 ? ceil_div(a.F, a.win_len) : 1;
+    UMX_CHECK(n_win <= kWienerChunks && n_win <= a.stat_windows, "wiener: at most 19 windows per segment (win_len too small for this window length)");
+    if (!a.no_em)
+    {
+        wiener_reduce_kernel<<<dim3(tiles, a.win_len > 0 ? n_win : kWienerChunks, a.n_tracks), 256, 0, st>>>(a);
+        UMX_CUDA_OK(cudaGetLastError());
+        wiener_finalize_kernel<<<dim3(tiles, a.n_tracks, n_win), 256, 0, st>>>(a);
+        UMX_CUDA_OK(cudaGetLastError());
+    }
     if (!a.out)
         return 0; // statistics only
     wiener_apply_kernel<<<dim3(tiles, ceil_div(a.F, kWienerApplyFrames), a.n_tracks), 256, 0, st>>>(a);
@@ -309,6 +326,7 @@ extern "C" int umx_cuda_wiener_noalloc(const float *d_mix, const float *d_mags, 
     w.mask_ld = 2 * kBins;
     w.mask_is_mag = 1;
     w.maxabs = maxabs;
+    w.stat_windows = 1;
     w.partials = scratch;
     w.stats = scratch + (size_t)kNoAllocMaxTracks * kNaPartials;
     w.out = reinterpret_cast<float2 *>(d_out);

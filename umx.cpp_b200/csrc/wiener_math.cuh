@@ -7,9 +7,20 @@
 namespace umx
 {
 
-__device__ __forceinline__ float wiener_max_abs(const float *maxabs, int trk)
+// max_abs of (track, window): max(1, max|X| / 10) (wiener.cpp:36-52); `slot` = track * kWienerChunks + window
+__device__ __forceinline__ float wiener_max_abs(const float *maxabs, int slot)
 {
-    return fmaxf(1.0f, maxabs[trk] / kWienerScale); // wiener.cpp:36-52
+    return fmaxf(1.0f, maxabs[slot] / kWienerScale);
+}
+__device__ __forceinline__ int wiener_window(int f, int win_len) { return win_len > 0 ? f / win_len : 0; }
+// PSD of one source from its two channels' estimates: the reference's ((re+im)_L^2 + (re+im)_R^2) / 2 (wiener.cpp:187-202, sic)
+// or upstream's mean_ch |y|^2
+__device__ __forceinline__ float wiener_psd(float2 yL, float2 yR, int psd_abs2)
+{
+    if (psd_abs2)
+        return ((yL.x * yL.x + yL.y * yL.y) + (yR.x * yR.x + yR.y * yR.y)) * 0.5f;
+    const float sL = yL.x + yL.y, sR = yR.x + yR.y;
+    return (sL * sL + sR * sR) * 0.5f;
 }
 
 // y_jc / max_abs for one channel.  inv_ma = 1 / max_abs: the reference's own build uses -freciprocal-math, and an
@@ -62,22 +73,23 @@ struct WienerCommon
     float2 u0, u1; // Cxx^-1 (x0, x1)
 };
 // R: the four sources' normalised spatial covariances of this bin, R[4j .. 4j+3] = R00, R11, Re R01, Im R01
-__device__ __forceinline__ void wiener_common(const WienerIn &in, const float (&R)[16], float inv_ma, int is_mag, WienerCommon &c)
+__device__ __forceinline__ void wiener_common(const WienerIn &in, const float (&R)[16], float inv_ma, int is_mag, WienerCommon &c,
+                                              int psd_abs2 = 0, int reg_once = 0)
 {
     const float reg = sqrtf(kWienerEps); // wiener.cpp:155-163
     c.x0 = make_float2(in.XL.x * inv_ma, in.XL.y * inv_ma);
     c.x1 = make_float2(in.XR.x * inv_ma, in.XR.y * inv_ma);
-    float c00 = 0.f, c11 = 0.f, c01r = 0.f, c01i = 0.f;
+    // Cxx = sum_j (sqrt(eps) I + v_j R_j): the reference adds the regulariser once PER SOURCE (wiener.cpp:301-325); upstream once
+    const float reg_j = reg_once ? 0.f : reg;
+    float c00 = reg_once ? reg : 0.f, c11 = c00, c01r = 0.f, c01i = 0.f;
 #pragma unroll
     for (int j = 0; j < 4; ++j)
     {
         const float2 yL = initial_estimate(in.mL[j], in.XL, inv_ma, is_mag);
         const float2 yR = initial_estimate(in.mR[j], in.XR, inv_ma, is_mag);
-        const float sL = yL.x + yL.y, sR = yR.x + yR.y;
-        c.v[j] = (sL * sL + sR * sR) * 0.5f;
-        // Cxx = sum_j (sqrt(eps) I + v_j R_j): the regulariser is added once PER SOURCE (wiener.cpp:301-325)
-        c00 += reg + c.v[j] * R[4 * j + 0];
-        c11 += reg + c.v[j] * R[4 * j + 1];
+        c.v[j] = wiener_psd(yL, yR, psd_abs2);
+        c00 += reg_j + c.v[j] * R[4 * j + 0];
+        c11 += reg_j + c.v[j] * R[4 * j + 1];
         c01r += c.v[j] * R[4 * j + 2];
         c01i += c.v[j] * R[4 * j + 3];
     }
