@@ -195,6 +195,7 @@ def main():
     ap.add_argument("--pipeline", type=int, default=-1, help="session option: 0 in order, 2 post stage under the next segment's recurrences, 3 (default) segment wavefront")
     ap.add_argument("--lane-targets", type=int, default=0, help="session option: targets per stream of the wavefront (1, 2, 4)")
     ap.add_argument("--timeline", default="", help="write the stage intervals of the last timed step to this file (JSON)")
+    ap.add_argument("--no-e2e", action="store_true", help="profiling runs only: skip the host-buffer arm (the line then carries no e2e value)")
     ap.add_argument("--no-in-order", action="store_true", help="skip the in-order pass that yields roofline_in_order")
     ap.add_argument("--no-full-window", action="store_true", help="--impl reference: skip the one real 60 s window after the timed steps")
     args = ap.parse_args()
@@ -305,23 +306,25 @@ def main():
         sess.set_option("pipeline", pipeline)
 
     # ---- e2e: host buffers through umx_cuda_demix, copies inside the timed region ----
-    host_out = [torch.empty((4, n, 2), dtype=torch.float32).pin_memory() for _ in range(T)]
-    ins_np = [h.numpy() for h in host_in]
-    outs_np = [h.numpy() for h in host_out]
-    sess.demix_into(ins_np, outs_np)
-    k_e2e = max(1, min(args.steps, 3))
-    barrier()
-    t0 = time.perf_counter()
-    for _ in range(k_e2e):
+    e2e_value, e2e_ms_max, k_e2e, checksum, copy_ms = None, None, 0, None, {}
+    if not args.no_e2e:
+        host_out = [torch.empty((4, n, 2), dtype=torch.float32).pin_memory() for _ in range(T)]
+        ins_np = [h.numpy() for h in host_in]
+        outs_np = [h.numpy() for h in host_out]
         sess.demix_into(ins_np, outs_np)
-    torch.cuda.synchronize()
-    e2e_s = (time.perf_counter() - t0) / k_e2e
-    copy_ms = read_stages()  # busy time of the two copy streams in the last e2e step
-    if args.timeline and rank == 0:
-        json.dump(sess.timeline(), open(args.timeline + ".e2e.json", "w"))
-    _, e2e_ms_max = sharding.aggregate(T * args.track_seconds, e2e_s * 1e3, dist if world > 1 else None, dev)
-    e2e_value = audio_s / (e2e_ms_max / 1e3)
-    checksum = float(np.abs(outs_np[0][:, ::4096]).sum())  # the result was read back
+        k_e2e = max(1, min(args.steps, 3))
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(k_e2e):
+            sess.demix_into(ins_np, outs_np)
+        torch.cuda.synchronize()
+        e2e_s = (time.perf_counter() - t0) / k_e2e
+        copy_ms = read_stages()  # busy time of the two copy streams in the last e2e step
+        if args.timeline and rank == 0:
+            json.dump(sess.timeline(), open(args.timeline + ".e2e.json", "w"))
+        _, e2e_ms_max = sharding.aggregate(T * args.track_seconds, e2e_s * 1e3, dist if world > 1 else None, dev)
+        e2e_value = audio_s / (e2e_ms_max / 1e3)
+        checksum = float(np.abs(outs_np[0][:, ::4096]).sum())  # the result was read back
 
     if rank == 0:
         pk = peaks()

@@ -13,6 +13,7 @@
 #include <filesystem>
 #include <iostream>
 #include <string>
+#include <thread>
 #include <vector>
 
 namespace
@@ -156,14 +157,18 @@ int main(int argc, const char **argv)
         std::cerr << "Usage: " << argv[0] << " <model dir> <wav file> <out dir> [shift offset]" << std::endl;
         return 1;
     }
+    // one track per process: the driver's default number of hardware work queues is enough, and every extra queue costs ~50 ms
+    // of start-up and teardown (the library's own default suits long-running hosts; see csrc/capi.cu).  Set before any CUDA call.
+    setenv("CUDA_DEVICE_MAX_CONNECTIONS", "8", 0);
     std::cout << "umx.cpp Main driver program (B200 / CUDA path)" << std::endl;
     const std::string model_file = argv[1], wav_file = argv[2], out_dir = argv[3];
     const int shift = argc == 5 ? std::atoi(argv[4]) : UMX_DEFAULT_SHIFT_OFFSET;
 
+    // the WAV is decoded on a second thread while the model loads (gunzip + parse + operand preparation on the GPU)
     std::vector<float> audio;
     size_t n = 0;
-    if (!load_audio(wav_file, audio, n))
-        return 1;
+    bool audio_ok = false;
+    std::thread audio_thread([&] { audio_ok = load_audio(wav_file, audio, n); });
 
     const auto t0 = std::chrono::steady_clock::now();
     umx_cuda_model *model = nullptr;
@@ -171,6 +176,7 @@ int main(int argc, const char **argv)
     std::cout << "umx_model_load returned " << (rc == 0 ? "true" : "false") << std::endl;
     if (rc != 0)
     {
+        audio_thread.join();
         std::cerr << "Error loading model: " << umx_cuda_last_error() << std::endl;
         return 1;
     }
@@ -178,12 +184,25 @@ int main(int argc, const char **argv)
     umx_cuda_session *sess = nullptr;
     if (umx_cuda_session_create(model, 1, UMX_SEGMENT_SAMPLES, &sess) != 0)
     {
+        audio_thread.join();
         std::cerr << "Error: " << umx_cuda_last_error() << std::endl;
         return 1;
     }
-    std::vector<float> out(4 * 2 * n);
-    const float *in_ptr = audio.data();
-    float *out_ptr = out.data();
+    const auto t1b = std::chrono::steady_clock::now();
+    audio_thread.join();
+    if (!audio_ok)
+        return 1;
+    // page-locked staging for both directions: the copies then run at PCIe speed and overlap the kernels
+    float *pin_in = nullptr, *pin_out = nullptr;
+    if (umx_cuda_host_alloc(sizeof(float) * 2 * std::max<size_t>(n, 1), reinterpret_cast<void **>(&pin_in)) != 0 ||
+        umx_cuda_host_alloc(sizeof(float) * 8 * std::max<size_t>(n, 1), reinterpret_cast<void **>(&pin_out)) != 0)
+    {
+        std::cerr << "Error: " << umx_cuda_last_error() << std::endl;
+        return 1;
+    }
+    std::memcpy(pin_in, audio.data(), sizeof(float) * 2 * n);
+    const float *in_ptr = pin_in;
+    float *out_ptr = pin_out;
     const int64_t n64 = (int64_t)n;
     const auto t2 = std::chrono::steady_clock::now();
     if (umx_cuda_demix(sess, &in_ptr, &n64, 1, shift, &out_ptr) != 0)
@@ -195,18 +214,32 @@ int main(int argc, const char **argv)
     auto secs = [](auto a, auto b) { return std::chrono::duration<double>(b - a).count(); };
     std::cout << "Loaded model in " << secs(t0, t1) << " s; demixed " << (double)n / UMX_SAMPLE_RATE << " s of audio in " << secs(t2, t3)
               << " s" << std::endl;
+    if (std::getenv("UMX_CLI_TIMES"))
+        std::cout << "phases: model " << secs(t0, t1) << " s, session " << secs(t1, t1b) << " s, wait for audio + pinned staging "
+                  << secs(t1b, t2) << " s, demix " << secs(t2, t3) << " s" << std::endl;
 
+    // the four stems are written by four threads (the reference: `#pragma omp parallel for` over targets, umx.cpp:75)
     std::filesystem::create_directories(out_dir);
+    bool ok[4] = {false, false, false, false};
+    std::vector<std::thread> writers;
     for (int target = 0; target < 4; ++target)
     {
         const std::string p = (std::filesystem::path(out_dir) / ("target_" + std::to_string(target) + ".wav")).string();
         std::cout << "Writing wav file " << p << " to " << out_dir << std::endl;
-        if (!write_wav(p, out.data() + (size_t)target * 2 * n, n))
+        writers.emplace_back([=, &ok] { ok[target] = write_wav(p, pin_out + (size_t)target * 2 * n, n); });
+    }
+    for (auto &w : writers)
+        w.join();
+    if (std::getenv("UMX_CLI_TIMES"))
+        std::cout << "phases: write " << secs(t3, std::chrono::steady_clock::now()) << " s" << std::endl;
+    for (int target = 0; target < 4; ++target)
+        if (!ok[target])
         {
-            std::cerr << "Error writing " << p << std::endl;
+            std::cerr << "Error writing target_" << target << ".wav" << std::endl;
             return 1;
         }
-    }
+    umx_cuda_host_free(pin_in);
+    umx_cuda_host_free(pin_out);
     umx_cuda_session_destroy(sess);
     umx_cuda_model_destroy(model);
     return 0;

@@ -84,6 +84,10 @@ int umx_cuda_demix(umx_cuda_session *s, const float *const *audio, const int64_t
 /* Same with inputs/outputs already resident in device memory (no host<->device copies). */
 int umx_cuda_demix_device(umx_cuda_session *s, const float *const *d_audio, const int64_t *n_samples,
                           int n_tracks, int shift_offset, float *const *d_out);
+/* Page-locked host buffers for umx_cuda_demix / umx_cuda_infer_segment (hosts that do not link the CUDA runtime themselves):
+ * with them the copies run at PCIe speed and overlap the kernels; pageable buffers work too, slower. */
+int umx_cuda_host_alloc(size_t bytes, void **out);
+void umx_cuda_host_free(void *p);
 /* Segment table of split_inference for a track of n samples shifted by shift_offset (umx.cpp:214-218):
  * writes up to cap (offset, chunk_length) pairs, returns the segment count. */
 int umx_cuda_segment_plan(int64_t n_samples, int shift_offset, int n_buf, int64_t *offsets, int *lengths, int cap);

@@ -16,10 +16,10 @@ from __future__ import annotations
 import ctypes as C
 import os
 
-# The segment wavefront runs on ~18 CUDA streams; with the driver's default of 8 hardware work queues several streams share a
-# queue and their kernels serialise behind each other's event waits.  Only takes effect if set before the CUDA context exists
-# (the C library sets the same default when it is loaded: csrc/capi.cu).
-os.environ.setdefault("CUDA_DEVICE_MAX_CONNECTIONS", "32")
+# The segment wavefront runs on up to 18 CUDA streams; with the driver's default of 8 hardware work queues several streams share
+# a queue and their kernels serialise behind each other's event waits.  Each queue costs ~50 ms of context creation, so 16 here
+# (as the C library does when it is loaded, csrc/capi.cu); bench.py asks for 32.  Only takes effect before the CUDA context exists.
+os.environ.setdefault("CUDA_DEVICE_MAX_CONNECTIONS", "16")
 
 import numpy as np  # noqa: E402
 
@@ -38,7 +38,7 @@ EXPORTS = [
     "umx_cuda_model_create_from_file", "umx_cuda_model_destroy", "umx_cuda_model_hidden_size",
     "umx_cuda_model_device", "umx_cuda_model_tensor", "umx_cuda_session_create", "umx_cuda_session_destroy",
     "umx_cuda_session_reset", "umx_cuda_session_get_state", "umx_cuda_infer_segment", "umx_cuda_demix",
-    "umx_cuda_demix_device", "umx_cuda_segment_plan", "umx_cuda_stft", "umx_cuda_istft", "umx_cuda_lstm_forward",
+    "umx_cuda_demix_device", "umx_cuda_host_alloc", "umx_cuda_host_free", "umx_cuda_segment_plan", "umx_cuda_stft", "umx_cuda_istft", "umx_cuda_lstm_forward",
     "umx_cuda_wiener", "umx_cuda_wiener_opts", "umx_cuda_stft_opts", "umx_cuda_target_mags", "umx_cuda_session_set_profiling", "umx_cuda_session_stage_ms",
     "umx_cuda_session_launches", "umx_cuda_session_timeline", "umx_cuda_session_set_option", "umx_cuda_session_set_stream",
     "umx_cuda_wiener_noalloc", "umx_cuda_lstm_max_active_clusters", "umx_cuda_nccl_unique_id",
@@ -79,6 +79,9 @@ def lib():
     l.umx_cuda_infer_segment.argtypes = [vp, vp, ip, vp]
     l.umx_cuda_demix.argtypes = [vp, vp, vp, ip, ip, vp]
     l.umx_cuda_demix_device.argtypes = [vp, vp, vp, ip, ip, vp]
+    l.umx_cuda_host_alloc.argtypes = [C.c_size_t, fpp]
+    l.umx_cuda_host_free.argtypes = [vp]
+    l.umx_cuda_host_free.restype = None
     l.umx_cuda_segment_plan.argtypes = [C.c_int64, ip, ip, vp, vp, ip]
     l.umx_cuda_stft.argtypes = [vp, ip, ip, vp]
     l.umx_cuda_istft.argtypes = [vp, ip, ip, vp]

@@ -10,16 +10,19 @@
 
 namespace umx
 {
-// The segment wavefront (session.cu) runs on ~18 CUDA streams.  The driver maps streams onto CUDA_DEVICE_MAX_CONNECTIONS hardware
-// work queues (default 8); streams that share a queue serialise behind each other's event waits, which undoes the wavefront.
-// Ask for 32 queues when the library is loaded, unless the host has chosen a value; it takes effect if the CUDA context of the
-// device does not exist yet (hosts that create the context first should export the variable themselves).
+// The segment wavefront (session.cu) runs on up to 18 CUDA streams.  The driver maps streams onto CUDA_DEVICE_MAX_CONNECTIONS
+// hardware work queues (default 8); streams that share a queue serialise behind each other's event waits.  Every queue costs
+// about 50 ms of context creation and teardown (measured: 2.1 s / 2.6 s / 3.7 s wall for a 3-minute CLI run at 8 / 16 / 32), so
+// the library asks for 16 at its first call that touches the device, unless the host has chosen a value (so a host's own setenv
+// before that call wins: the one-track CLI sets 8; a long-running host that batches tracks may export 32).  It takes effect if
+// the CUDA context of the device does not exist yet.
 namespace
 {
-struct ConnectionsDefault
+void connections_default()
 {
-    ConnectionsDefault() { setenv("CUDA_DEVICE_MAX_CONNECTIONS", "32", 0); }
-} g_connections_default;
+    static std::once_flag once;
+    std::call_once(once, [] { setenv("CUDA_DEVICE_MAX_CONNECTIONS", "16", 0); });
+}
 } // namespace
 
 static thread_local std::string g_err;
@@ -58,6 +61,7 @@ struct DevBuf
 
 int require_device()
 {
+    connections_default();
     int n = 0;
     if (cudaGetDeviceCount(&n) != cudaSuccess || n < 1)
     {
@@ -75,6 +79,7 @@ const char *umx_cuda_last_error(void) { return g_err.c_str(); }
 
 int umx_cuda_device_count(void)
 {
+    connections_default();
     int n = 0;
     if (cudaGetDeviceCount(&n) != cudaSuccess)
         return 0;
@@ -264,6 +269,21 @@ double umx_cuda_session_stage_ms(umx_cuda_session *s, const char *stage)
     }
     auto it = s->s->stage_ms.find(stage);
     return it == s->s->stage_ms.end() ? -1.0 : it->second;
+}
+
+int umx_cuda_host_alloc(size_t bytes, void **out)
+{
+    UMX_CHECK(out != nullptr, "umx_cuda_host_alloc: null argument");
+    if (require_device())
+        return -1;
+    UMX_CUDA_OK(cudaHostAlloc(out, std::max<size_t>(bytes, 1), cudaHostAllocDefault));
+    return 0;
+}
+
+void umx_cuda_host_free(void *p)
+{
+    if (p)
+        cudaFreeHost(p);
 }
 
 int umx_cuda_session_timeline(umx_cuda_session *s, char *stages, float *begin_ms, float *end_ms, int cap)

@@ -42,7 +42,12 @@ struct Cfg
     static constexpr int kStages = TERMS == 2 ? 6 : 4;
 };
 constexpr int kEpiWarps = 8;  // two per TMEM lane quadrant, each takes one half of the tile's columns
-constexpr int kEpiPitch = 20; // floats per row of the transpose tile: 16 columns + 4 pad
+// Transpose tile of one epilogue warp: 32 rows x 16 columns of fp32, 64-byte rows, the four 16-byte chunks of row r stored at
+// chunk position c ^ ((r >> 1) & 3).  Both sides are then free of bank conflicts: the writer (lane = row, one chunk per
+// instruction) covers all 8 16-byte bank groups with every 8 lanes, and so does the reader (4 lanes per row, 2 rows per 8 lanes).
+// (A padded pitch of 20 floats was conflict-free for the writes only: 105 M conflicts per W_ih launch in ncu.)
+constexpr int kEpiPitch = 16;
+__device__ __forceinline__ uint32_t epi_swz(int row, int chunk) { return (uint32_t)(row * 64 + ((chunk ^ ((row >> 1) & 3)) << 4)); }
 constexpr int kEpiBytesPerWarp = 32 * kEpiPitch * 4;
 constexpr int kEpiChunks = BN / 2 / 16; // 16-column chunks per epilogue warp and tile
 constexpr int kMaxStages = 6;
@@ -122,7 +127,7 @@ __device__ __forceinline__ void epi_rows(const EpiRows &e, const float (&al)[4],
         float v[4];
         asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];"
                      : "=f"(v[0]), "=f"(v[1]), "=f"(v[2]), "=f"(v[3])
-                     : "r"(e.stage_buf + (uint32_t)(row * kEpiPitch + e.c4) * 4u)
+                     : "r"(e.stage_buf + epi_swz(row, e.c4 >> 2))
                      : "memory");
 #pragma unroll
         for (int c = 0; c < 4; ++c)
@@ -451,7 +456,7 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_tc_kernel(const __grid_const
                     continue;
 #pragma unroll
                 for (int i = 0; i < 4; ++i)
-                    asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(stage_buf + (uint32_t)(lane * kEpiPitch + 4 * i) * 4u), "r"(r[4 * i]),
+                    asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(stage_buf + epi_swz(lane, i)), "r"(r[4 * i]),
                                  "r"(r[4 * i + 1]), "r"(r[4 * i + 2]), "r"(r[4 * i + 3])
                                  : "memory");
                 __syncwarp();
