@@ -160,6 +160,8 @@ int umx_cuda_lstm_max_active_clusters(void);
  * "lane_targets" = 1, 2 or 4 targets per group (0, the default: 1 up to 16 tracks, else 4); results are identical,
  * "skip_zero_frames" 1 (default) = frames of a window beyond a short chunk are computed once (first layer) or not at all
  * (after the network), 0 = every frame of every 60 s window is computed as the reference does; results are identical.
+ * "direct_final" 1 (default) = output samples that only one segment covers are written finalised, (w y)/w, by the inverse
+ * STFT kernel itself instead of going through the track accumulator and the finalize kernel; results are identical.
  * Upstream-faithful variants, all 0 by default = what the reference does (its deviations from Open-Unmix):
  * "stft_pad" 1 = true reflect padding (torch.stft) instead of the symmetric edge copy of src/dsp.cpp:109-128,
  * "wiener_psd" 1 = PSD |y|^2 instead of (re+im)^2 (src/wiener.cpp:187-202), "wiener_reg" 1 = regulariser added once instead

@@ -213,6 +213,22 @@ def test_demix_pipeline_modes_identical(umx, mode, lane_targets, hidden):
             assert np.array_equal(g, w)
 
 
+@pytest.mark.parametrize("hidden", [64, 1024])
+def test_demix_direct_final_identical(umx, hidden):
+    """Session option "direct_final": output samples that only one segment covers are written finalised by the inverse STFT
+    kernel itself, (w y)/w, instead of going through the accumulator and finalize_kernel.  Same bits, for every track length
+    (short last segments, tracks shorter than one stride, a track of one sample) and through the host and device copies."""
+    n_buf = 16384
+    gm = umx.load_umx_model(synth.make_ggml(hidden=hidden, seed=79))
+    tracks = [synth.make_audio(n, 50 + i) for i, n in enumerate((70000, 12288 - 18017 + 22050, 9000, 1, 40961))]
+    a, b = umx.Session(gm, len(tracks), n_buf), umx.Session(gm, len(tracks), n_buf)
+    a.set_option("direct_final", 0)
+    for shift in (4033, 0, 11025):
+        want, got = a.demix(tracks, shift_offset=shift), b.demix(tracks, shift_offset=shift)
+        for g, w in zip(got, want):
+            assert np.array_equal(g, w)
+
+
 def test_demix_shift_offsets_and_trim(umx, small):
     gm, om = small
     n_buf = 8192

@@ -369,6 +369,11 @@ int umx_cuda_session_set_option(umx_cuda_session *s, const char *name, int value
         UMX_CHECK(value == 1 || lstm_cluster_supported(s->s->Hh), "lstm_impl = 0: the cluster recurrence kernel does not support this model's hidden size");
         s->s->lstm_impl = value;
     }
+    else if (n == "direct_final")
+    {
+        UMX_CHECK(value == 0 || value == 1, "direct_final must be 0 or 1");
+        s->s->direct_final = value;
+    }
     else if (n == "stft_pad")
     {
         UMX_CHECK(value == 0 || value == 1, "stft_pad must be 0 (the reference's symmetric edge copy) or 1 (reflect)");

@@ -22,6 +22,13 @@ struct IstftTrack
     long out_offset;      // segment offset inside the accumulator
     int n_wave;           // samples to emit (chunk length)
     int accumulate;       // 1: out[off+k] += w[k]*y[k] (umx.cpp:234-249), 0: plain store
+    // Chunk samples [ex_lo, ex_hi) are covered by no other segment of the track: out/sum_weight there is (w y)/w with nothing
+    // else added (umx.cpp:234-273), so wiener_istft_kernel writes it straight to the track's output (sample k of the chunk is
+    // output sample final_off + k when that lies in [0, final_n)) and neither the accumulator nor finalize_kernel sees it.
+    float2 *final_out;    // [n_stems][final_n], or null
+    long final_n;
+    long final_off;
+    int ex_lo, ex_hi;
 };
 
 struct FinalizeTrack
@@ -30,6 +37,9 @@ struct FinalizeTrack
     float2 *out;       // [n_stems][n]
     long L, n;
     long i_begin, i_end; // output sample range to finalise
+    // (host side only) the range that is complete — finalised here or written by the inverse STFT itself — once this entry's
+    // kernels have run: what leaves for the host
+    long ship_begin, ship_end;
 };
 
 constexpr int kIstftFramesPerCta = 32; // + 3 halo frames recomputed per CTA

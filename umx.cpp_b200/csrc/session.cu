@@ -710,7 +710,7 @@ int session_infer_segment(Session *s, const float *audio, int n, float *out)
     StftTrack *ha = static_cast<StftTrack *>(s->h_desc);
     IstftTrack *hb = reinterpret_cast<IstftTrack *>(ha + 1);
     *ha = StftTrack{s->in_pool[0], n, 0, n, 0};
-    *hb = IstftTrack{s->out_pool[0], n, 0, n, 0};
+    *hb = IstftTrack{s->out_pool[0], n, 0, n, 0, nullptr, 0, 0, 0, 0};
     UMX_CUDA_OK(cudaMemcpyAsync(s->d_stft, ha, sizeof *ha, cudaMemcpyHostToDevice, s->st));
     UMX_CUDA_OK(cudaMemcpyAsync(s->d_istft, hb, sizeof *hb, cudaMemcpyHostToDevice, s->st));
     UMX_CUDA_OK(cudaEventRecord(s->desc_copied, s->st));
@@ -735,10 +735,10 @@ static int ship_ranges(Session *s, const FinalizeTrack *fin_host, int n_tracks, 
     for (int i = 0; i < n_tracks; ++i)
     {
         const FinalizeTrack &f = fin_host[i];
-        if (f.i_end <= f.i_begin)
+        if (f.ship_end <= f.ship_begin)
             continue;
-        const size_t o = 2 * ((size_t)s->tp_t0 * n_samples[i] + f.i_begin), pitch = sizeof(float2) * (size_t)n_samples[i];
-        UMX_CUDA_OK(cudaMemcpy2DAsync(host_out[i] + o, pitch, d_out[i] + o, pitch, sizeof(float2) * (size_t)(f.i_end - f.i_begin),
+        const size_t o = 2 * ((size_t)s->tp_t0 * n_samples[i] + f.ship_begin), pitch = sizeof(float2) * (size_t)n_samples[i];
+        UMX_CUDA_OK(cudaMemcpy2DAsync(host_out[i] + o, pitch, d_out[i] + o, pitch, sizeof(float2) * (size_t)(f.ship_end - f.ship_begin),
                                       (size_t)s->tp_nt, cudaMemcpyDeviceToHost, s->st_out));
     }
     return 0;
@@ -776,7 +776,7 @@ static int ship_inputs(Session *s, int sg, int stride, int shift_offset, int n_t
 // the result is bit-identical (tests/test_gpu_parity.py).
 static int demix_wavefront(Session *s, const float *const *d_audio, const int64_t *n_samples, int n_tracks, int shift_offset,
                            float *const *d_out, const float *const *host_in, float *const *host_out, int max_segs, int stride,
-                           const std::vector<FinalizeTrack> &hf, const std::vector<long> &max_range)
+                           const std::vector<FinalizeTrack> &hf, const std::vector<long> &max_range, const std::vector<char> &ship_any)
 {
     size_t &ev = s->ev_cursor;
     cudaStream_t main_st = s->st;
@@ -923,7 +923,7 @@ static int demix_wavefront(Session *s, const float *const *d_audio, const int64_
             }
             if (q + 1 == kPostParts && record(back_done[sg], s->st_post))
                 return -1;
-            if (host_out && max_range[(size_t)sg * kPostParts + q] > 0)
+            if (host_out && ship_any[(size_t)sg * kPostParts + q])
             {
                 cudaEvent_t e;
                 if (record(e, s->st_post) || wait(s->st_out, e))
@@ -972,6 +972,7 @@ int session_demix_device(Session *s, const float *const *d_audio, const int64_t 
         return std::max(0L, std::min((long)n_samples[i], e));
     };
     std::vector<long> max_range((size_t)max_segs * kPostParts, 0);
+    std::vector<char> ship_any((size_t)max_segs * kPostParts, 0); // some track has a finished range in this part
     for (int i = 0; i < n_tracks; ++i)
     {
         if (grow(&s->acc_pool[i], &s->acc_cap[i], 4 * L[i]))
@@ -983,18 +984,44 @@ int session_demix_device(Session *s, const float *const *d_audio, const int64_t 
             const int clen = off < L[i] ? (int)std::min<long>(s->n_buf, L[i] - off) : 0; // umx.cpp:217-218
             hs[(size_t)sg * s->T + i] = {reinterpret_cast<const float2 *>(d_audio[i]), (long)n_samples[i],
                                          off - shift_offset, clen, 0};
-            hi[(size_t)sg * s->T + i] = {s->acc_pool[i], L[i], off, clen, 1};
+            // chunk samples no other segment covers: after the overlap with the previous segment, before the next segment starts
+            const int ovl = s->n_buf - stride;
+            const int ex_lo = sg == 0 ? 0 : std::min(clen, ovl);
+            const int ex_hi = off + stride < L[i] ? std::min(clen, stride) : clen;
+            const long x_lo = off + ex_lo - shift_offset, x_hi = off + ex_hi - shift_offset; // the same range as output indices
             // part q of the segment's post stage emits the chunk samples below 1024 * (its last frame + 1) - 2048
+            long pb[kPostParts], pe[kPostParts];
             long b = sg == 0 ? 0 : final_end(i, sg - 1);
+            bool direct = s->direct_final && ex_hi > ex_lo;
             for (int q = 0; q < kPostParts; ++q)
             {
                 long e = final_end(i, sg);
                 if (q + 1 < kPostParts)
                     e = std::min(e, std::max(b, off + (long)kHop * post_part_frame(s->F, q + 1) - kPad - shift_offset));
-                const size_t d = ((size_t)sg * kPostParts + q) * s->T + i;
-                hf[d] = {s->acc_pool[i], reinterpret_cast<float2 *>(d_out[i]), L[i], (long)n_samples[i], b, e};
-                max_range[(size_t)sg * kPostParts + q] = std::max(max_range[(size_t)sg * kPostParts + q], e - b);
+                pb[q] = b;
+                pe[q] = e;
+                if (b < x_lo && e > x_hi) // finalize_kernel takes one range per part: it cannot skip a hole in the middle
+                    direct = false;
                 b = e;
+            }
+            hi[(size_t)sg * s->T + i] = {s->acc_pool[i], L[i], off, clen, 1, direct ? reinterpret_cast<float2 *>(d_out[i]) : nullptr,
+                                         (long)n_samples[i], off - shift_offset, direct ? ex_lo : 0, direct ? ex_hi : 0};
+            for (int q = 0; q < kPostParts; ++q)
+            {
+                const size_t d = ((size_t)sg * kPostParts + q) * s->T + i;
+                // finalize_kernel only has to visit what the inverse STFT did not write itself
+                long fb = pb[q], fe = pe[q];
+                if (direct)
+                {
+                    if (fb >= x_lo)
+                        fb = std::max(fb, std::min(fe, x_hi));
+                    else
+                        fe = std::min(fe, x_lo);
+                    fe = std::max(fe, fb);
+                }
+                hf[d] = {s->acc_pool[i], reinterpret_cast<float2 *>(d_out[i]), L[i], (long)n_samples[i], fb, fe, pb[q], pe[q]};
+                max_range[(size_t)sg * kPostParts + q] = std::max(max_range[(size_t)sg * kPostParts + q], fe - fb);
+                ship_any[(size_t)sg * kPostParts + q] = ship_any[(size_t)sg * kPostParts + q] || pe[q] > pb[q];
             }
         }
     }
@@ -1023,7 +1050,7 @@ int session_demix_device(Session *s, const float *const *d_audio, const int64_t 
     size_t &ev = s->ev_cursor;
     std::vector<long> copied_in(n_tracks, 0);
     if (s->pipeline == 3 && max_segs > 1)
-        return demix_wavefront(s, d_audio, n_samples, n_tracks, shift_offset, d_out, host_in, host_out, max_segs, stride, hf, max_range);
+        return demix_wavefront(s, d_audio, n_samples, n_tracks, shift_offset, d_out, host_in, host_out, max_segs, stride, hf, max_range, ship_any);
     // in order on the caller's stream: h/c stream from segment to segment
     for (int sg = 0; sg < max_segs; ++sg)
     {
@@ -1045,8 +1072,7 @@ int session_demix_device(Session *s, const float *const *d_audio, const int64_t 
             if (int rc = run_post_part(s, sg, n_tracks, v, s->st, q))
                 return rc;
             const size_t d = ((size_t)sg * kPostParts + q) * s->T;
-            if (max_range[(size_t)sg * kPostParts + q] <= 0)
-                continue;
+            if (max_range[(size_t)sg * kPostParts + q] > 0)
             {
                 StageScope sc(s, "finalize");
                 s->launches++;
@@ -1054,7 +1080,7 @@ int session_demix_device(Session *s, const float *const *d_audio, const int64_t 
                                              stride, s->tp_nt, s->st, s->tp_t0))
                     return rc;
             }
-            if (host_out)
+            if (host_out && ship_any[(size_t)sg * kPostParts + q])
             { // ship the finished range of every stem while later parts and segments compute
                 cudaEvent_t e = take_event(s, ev);
                 UMX_CUDA_OK(cudaEventRecord(e, s->st));

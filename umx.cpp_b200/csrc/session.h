@@ -99,6 +99,7 @@ struct Session
     int wiener_reg_once = 0;   // "wiener_reg" 1: sqrt(eps) I added once instead of once per source (src/wiener.cpp:301-325)
     int wiener_win_len = 0;    // "wiener_win_len" N: EM statistics per window of N frames (upstream 300) instead of per segment
     int wiener_niter = 1;      // "wiener_niter" 0: no EM iteration (y = mask X); 1: one iteration (src/wiener.hpp:14)
+    int direct_final = 1;      // "direct_final" 1 (default): samples no other segment covers are written finalised by the inverse STFT itself
     int lstm_reset = 0;        // "lstm_reset" 1: h/c zeroed before every segment (upstream) instead of streamed (src/lstm.cpp:160-161)
     // measurement
     bool profiling = false;

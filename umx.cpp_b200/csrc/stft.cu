@@ -554,6 +554,7 @@ __global__ void __launch_bounds__(kWiThreads, 1)
             const IstftTrack *tkp = tracks + trk;
             float2 *out = tkp->out + (long)(stem_begin + idx) * tkp->out_stem_stride + tkp->out_offset;
             const int accumulate = tkp->accumulate;
+            const int ex_lo = tkp->ex_lo, ex_hi = tkp->final_out ? tkp->ex_hi : 0;
             auto emit = [&](int hop, int j, float2 v) {
                 const int i = kHop * hop + t + 256 * j - kPad;
                 if (i >= 0 && i < n_wave)
@@ -561,7 +562,15 @@ __global__ void __launch_bounds__(kWiThreads, 1)
                     if (accumulate)
                     { // out[off + k] += w[k] * y[k] (umx.cpp:234-249)
                         const float wgt = tri_weight(i, n_buf);
-                        wi::red_add2(out + i, make_float2(wgt * v.x, wgt * v.y));
+                        const float2 c = make_float2(wgt * v.x, wgt * v.y);
+                        if (i >= ex_lo && i < ex_hi)
+                        { // no other segment reaches this sample: (0 + w y) / (0 + w), the accumulator is never touched
+                            const long io = tkp->final_off + i;
+                            if (io >= 0 && io < tkp->final_n)
+                                tkp->final_out[(long)(stem_begin + idx) * tkp->final_n + io] = make_float2(__fdiv_rn(c.x, wgt), __fdiv_rn(c.y, wgt));
+                        }
+                        else
+                            wi::red_add2(out + i, c);
                     }
                     else
                         out[i] = v;
