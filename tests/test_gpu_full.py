@@ -1,6 +1,6 @@
-"""GPU parity at the real UMX-L size (hidden 1024, 60 s windows, 2584 frames) against the compiled,
-unmodified reference (oracle/_ref/libumxref.so, which travels to the GPU box).  Two streamed
-umx_inference calls: ~2 minutes of single-core reference time."""
+"""GPU parity at the real UMX-L size (hidden 1024, 60 s windows, 2584 frames) and at UMX-HQ's (hidden 512) against the
+compiled, unmodified reference (oracle/_ref/libumxref.so, which travels to the GPU box).  Two streamed
+umx_inference calls each: ~2 + 1 minutes of single-core reference time."""
 import gzip
 import os
 
@@ -20,9 +20,11 @@ def sdr(got, want):
 
 @pytest.mark.skipif(not ref.available(), reason="oracle/_ref/libumxref.so not built")
 @pytest.mark.parametrize("terms", [int(os.environ.get("UMX_TEST_TERMS", "0"))])
-def test_umxl_two_streamed_segments_vs_reference(umx, tmp_path, terms):
-    raw = synth.make_ggml(hidden=1024, seed=1234)
-    assert len(raw) == 138340380  # 172 tensors, 131.93 MB
+@pytest.mark.parametrize("hidden", [1024, 512], ids=["umxl", "umxhq"])
+def test_umxl_two_streamed_segments_vs_reference(umx, tmp_path, terms, hidden):
+    raw = synth.make_ggml(hidden=hidden, seed=1234)
+    if hidden == 1024:
+        assert len(raw) == 138340380  # 172 tensors, 131.93 MB
     p = tmp_path / "umxl-synth.gz"
     p.write_bytes(gzip.compress(raw, 1))
     rm = ref.Model(str(p))
@@ -35,14 +37,14 @@ def test_umxl_two_streamed_segments_vs_reference(umx, tmp_path, terms):
     sess = umx.Session(gm, 1, N_BUF)
     if terms:
         sess.set_option("gemm_terms", terms)
-    rs = ref.LstmState(512, ref.nb_frames(N_BUF))
+    rs = ref.LstmState(hidden // 2, ref.nb_frames(N_BUF))
     audio = synth.make_audio(10 * 44100 + 18017, 7)
     for chunk in (audio[:, :441000], audio[:, 441000 - 300000:]):  # 10 s, then a different 7 s chunk (state streams)
         want = ref.umx_inference(rm, rs, chunk, N_BUF)
         got = sess.umx_inference(chunk)
         err = float(np.abs(got - want).max())
         sdrs = [sdr(got[j], want[j]) for j in range(4)]
-        print(f"UMX-L chunk {chunk.shape[1]}: max-abs {err:.3e}, SDR {['%.1f' % s for s in sdrs]}, "
+        print(f"{'UMX-L' if hidden == 1024 else 'UMX-HQ size'} chunk {chunk.shape[1]}: max-abs {err:.3e}, SDR {['%.1f' % s for s in sdrs]}, "
               f"stems rms {np.sqrt((want ** 2).mean()):.4f}")
         assert err < 1e-3 and min(sdrs) > 60.0
     for l in range(3):

@@ -1,5 +1,5 @@
-"""GPU: the tensor-core cluster recurrence (lstm_cluster.cu, UMX-L size only: 512 units per direction)
-against the simple recurrence kernel and the oracle, single and multi-track, streaming across calls."""
+"""GPU: the tensor-core cluster recurrence (lstm_cluster.cu: UMX-L's 512 units per direction on clusters of 8 CTAs, UMX-HQ's 256
+on clusters of 4) against the simple recurrence kernel and the oracle, single and multi-track, streaming across calls."""
 import numpy as np
 import pytest
 
@@ -11,19 +11,20 @@ N_BUF = 16384
 F = N_BUF // 1024 + 1
 
 
-@pytest.fixture(scope="module")
-def umxl(umx):
-    raw = synth.make_ggml(hidden=1024, seed=1234)
+@pytest.fixture(scope="module", params=[1024, 512], ids=["umxl-hidden1024", "umxhq-hidden512"])
+def umxl(umx, request):
+    raw = synth.make_ggml(hidden=request.param, seed=1234)
     return umx.load_umx_model(raw), O.load_model(raw)
 
 
 def test_lstm_forward_cluster_vs_oracle_streaming(umx, umxl):
     gm, om = umxl
-    x = np.random.default_rng(0).uniform(-1, 1, (F, 1024)).astype(np.float32)
+    H = gm.hidden_size
+    x = np.random.default_rng(0).uniform(-1, 1, (F, H)).astype(np.float32)
     fast, slow = umx.Session(gm, 1, N_BUF), umx.Session(gm, 1, N_BUF)
     fast.set_option("lstm_impl", 0)
     slow.set_option("lstm_impl", 1)
-    st = O.LstmState(512)
+    st = O.LstmState(H // 2)
     for call in range(3):  # state streams from call to call (lstm.cpp:160-161)
         want = O.lstm_forward(om.t[2], x, st)
         a, b = fast.umx_lstm_forward(2, x), slow.umx_lstm_forward(2, x)

@@ -146,11 +146,11 @@ struct LstmLayerArgs
     const IstftTrack *chunks;
 };
 int launch_lstm_simple(const LstmLayerArgs &a, cudaStream_t st);
-// lstm_cluster.cu: W_hh resident in SMEM across a cluster of 8 CTAs, tcgen05 kind::i8 (Hh == 512 only)
+// lstm_cluster.cu: W_hh resident in tensor memory across a cluster of Hh / 64 CTAs, tcgen05 kind::i8 (Hh == 512 or 256)
 bool lstm_cluster_supported(int Hh);
 int lstm_cluster_max_active();
-size_t whh_image_bytes();
-int launch_whh_image(const uint8_t *q, uint8_t *img, cudaStream_t st);
+size_t whh_image_bytes(int Hh);
+int launch_whh_image(const uint8_t *q, uint8_t *img, int Hh, cudaStream_t st);
 int launch_lstm_cluster(const LstmLayerArgs &a, const uint8_t *const (*img)[2], cudaStream_t st);
 
 // ---- wiener --------------------------------------------------------------------------------------

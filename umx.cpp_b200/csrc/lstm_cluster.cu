@@ -40,23 +40,29 @@ using namespace tc;
 
 namespace
 {
-constexpr int kC = 8;            // CTAs per cluster
-constexpr int kHhC = 512;        // hidden units per direction this kernel is built for
 constexpr int kUnits = 64;       // units per CTA
 constexpr int kMaxNG = 4;        // at most four ping-pong groups of tracks per cluster
-constexpr int kABytes = 256 * kHhC;               // this CTA's 256 gate rows x 512 k of W_hh, uint8: 128 KB, held in TMEM
-constexpr int kBTile = 48 * 64;                   // one source CTA's tile: up to 48 (track, digit) rows x 64 units
-constexpr int kBBuf = kC * kBTile;                // one (half, parity) h buffer: 24 KB
-constexpr int kBOff = 0;                          // [half 2][parity 2][8 source CTAs][48 rows][64 B], 64-byte swizzle
-constexpr int kSOff = kBOff + 2 * kMaxNG * kBBuf;   // offset * sum_k h_k: [group][16 tracks] f32
-constexpr int kPOff = kSOff + kMaxNG * 64;          // its per-CTA partial sums: [group][parity 2][8 source CTAs][16 tracks] f32
-constexpr int kPBuf = kC * 64;
-constexpr int kBarOff = kPOff + 2 * kMaxNG * kPBuf;
-constexpr int kSmemBytes = kBarOff + 256;
-static_assert(kSmemBytes <= 232448, "dynamic shared memory budget of one CTA exceeded");
+constexpr int kBTile = 48 * 64;  // one source CTA's tile: up to 48 (track, digit) rows x 64 units
+// Everything that depends on the hidden size per direction HH: 512 (UMX-L) = clusters of 8 CTAs, 256 (UMX-HQ) = clusters of 4.
+template <int HH>
+struct Cfg
+{
+    static_assert(HH == 512 || HH == 256, "hidden units per direction this kernel is built for");
+    static constexpr int kC = HH / kUnits;              // CTAs per cluster
+    static constexpr int kABytes = 256 * HH;            // this CTA's 256 gate rows x HH k of W_hh, uint8 (128 / 64 KB), held in TMEM
+    static constexpr int kACols = HH / 4;               // TMEM columns of one 128-row half of it (four k bytes per 32-bit column)
+    static constexpr int kBBuf = kC * kBTile;           // one (half, parity) h buffer
+    static constexpr int kBOff = 0;                     // [half][parity 2][source CTAs][48 rows][64 B], 64-byte swizzle
+    static constexpr int kSOff = kBOff + 2 * kMaxNG * kBBuf;  // offset * sum_k h_k: [group][16 tracks] f32
+    static constexpr int kPOff = kSOff + kMaxNG * 64;         // its per-CTA partial sums: [group][parity 2][source CTAs][16 tracks] f32
+    static constexpr int kPBuf = kC * 64;
+    static constexpr int kBarOff = kPOff + 2 * kMaxNG * kPBuf;
+    static constexpr int kSmemBytes = kBarOff + 256;
+    static_assert(kSmemBytes <= 232448, "dynamic shared memory budget of one CTA exceeded");
+};
 // 8 epilogue warps (one per TMEM lane quadrant and row half), 1 MMA warp, 1 shipper warp and 2 helper warps
 constexpr int kThreads = 32 * 12; // 8 epilogue warps, MMA warp, shipper warp, 2 helper warps
-constexpr uint32_t kTmemCols = 512; // [0,256): accumulators (half*128 + row half*64), [256,512): W_hh (row half*128 + k/4)
+constexpr uint32_t kTmemCols = 512; // [0,256): accumulators (half*128 + row half*64), [256, 256 + HH/2): W_hh (row half * HH/4 + k/4)
 constexpr uint32_t kTmemA = 256;
 
 __device__ __forceinline__ uint32_t mapa(uint32_t local_addr, uint32_t cta)
@@ -229,9 +235,14 @@ __device__ __forceinline__ void publish_digits(float h, uint32_t trk, uint32_t t
     }
 }
 
-template <int TP, int NG> // tracks per ping-pong group (8 or 16), groups per cluster (2 or 4)
-__global__ void __cluster_dims__(kC, 1, 1) __launch_bounds__(kThreads, 1) lstm_cluster_kernel(const ClusterArgs P)
+// tracks per ping-pong group (8 or 16), groups per cluster (2 or 4), hidden units per direction; launched with a cluster of
+// Cfg<HH>::kC CTAs along x (launch attribute)
+template <int TP, int NG, int HH>
+__global__ void __launch_bounds__(kThreads, 1) lstm_cluster_kernel(const ClusterArgs P)
 {
+    using C = Cfg<HH>;
+    constexpr int kC = C::kC, kHhC = HH, kABytes = C::kABytes, kBBuf = C::kBBuf, kBOff = C::kBOff, kSOff = C::kSOff, kPOff = C::kPOff,
+                  kPBuf = C::kPBuf, kBarOff = C::kBarOff;
     extern __shared__ __align__(1024) uint8_t smem[];
     const LstmLayerArgs &a = P.a;
     const int r = blockIdx.x; // rank in cluster (cluster spans x)
@@ -290,9 +301,9 @@ __global__ void __cluster_dims__(kC, 1, 1) __launch_bounds__(kThreads, 1) lstm_c
         // 512-byte row of the image per lane, four k bytes per 32-bit column
         const int qd = warp & 3, hh = warp >> 2;
         const uint4 *src = reinterpret_cast<const uint4 *>(P.img[target][dir] + (size_t)r * kABytes + (size_t)(hh * 128 + 32 * qd + lane) * kHhC);
-        const uint32_t dst = tmem_base + ((uint32_t)(32 * qd) << 16) + kTmemA + (uint32_t)hh * 128u;
+        const uint32_t dst = tmem_base + ((uint32_t)(32 * qd) << 16) + kTmemA + (uint32_t)hh * (uint32_t)C::kACols;
 #pragma unroll 2
-        for (int c16 = 0; c16 < 8; ++c16)
+        for (int c16 = 0; c16 < C::kACols / 16; ++c16)
             tmem_st16(dst + 16u * c16, __ldg(&src[4 * c16]), __ldg(&src[4 * c16 + 1]), __ldg(&src[4 * c16 + 2]), __ldg(&src[4 * c16 + 3]));
         asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
     }
@@ -633,8 +644,8 @@ __global__ void __cluster_dims__(kC, 1, 1) __launch_bounds__(kThreads, 1) lstm_c
 #pragma unroll
                     for (int h2 = 0; h2 < 2; ++h2)
 #pragma unroll
-                        for (int ks = 0; ks < 16; ++ks) // 32 bytes (K = 32) per MMA; B = the tile of source CTA ks / 2
-                            mma_i8_ts(tmem_base + half * kDCols + h2 * (kDCols / 2), tmem_base + kTmemA + h2 * 128 + 8 * ks,
+                        for (int ks = 0; ks < HH / 32; ++ks) // 32 bytes (K = 32) per MMA; B = the tile of source CTA ks / 2
+                            mma_i8_ts(tmem_base + half * kDCols + h2 * (kDCols / 2), tmem_base + kTmemA + h2 * C::kACols + 8 * ks,
                                       b_lo + (((ks >> 1) * kBTile) >> 4) + 2 * (ks & 1), b_hi, idesc, ks != 0);
                     tc_commit(mma_done0 + 8u * half);
                 }
@@ -673,10 +684,11 @@ __global__ void __cluster_dims__(kC, 1, 1) __launch_bounds__(kThreads, 1) lstm_c
                     if (dbg)
                         g_lstm_dbg[28 + (step - 200) * 2 + half] = clock64();
 #endif
-                    // lane l: track l % 16, source CTAs 4 (l / 16) .. + 3
-                    const float *ps = reinterpret_cast<const float *>(smem + kPOff + slot * kPBuf) + (lane & 15) + (lane >> 4) * 64;
+                    // lane l: track l % 16, source CTAs 4 (l / 16) .. + 3 (a cluster of 4 has only the first four)
+                    const float *ps = reinterpret_cast<const float *>(smem + kPOff + slot * kPBuf) + (lane & 15) + (kC == 8 ? (lane >> 4) * 64 : 0);
                     float tot = (ps[0] + ps[16]) + (ps[32] + ps[48]);
-                    tot += __shfl_xor_sync(0xffffffffu, tot, 16);
+                    if (kC == 8)
+                        tot += __shfl_xor_sync(0xffffffffu, tot, 16);
                     if (lane < 16)
                         st_shared_f32(sS + (uint32_t)(half * 64 + lane * 4), tot);
                     __syncwarp();
@@ -710,32 +722,45 @@ __global__ void __cluster_dims__(kC, 1, 1) __launch_bounds__(kThreads, 1) lstm_c
     }
 }
 
-// byte o of the image: CTA r, row half h, TMEM lane m, k: plain rows of 512 bytes (one per TMEM lane)
-__global__ void whh_image_kernel(const uint8_t *__restrict__ q, uint8_t *__restrict__ img)
+// byte o of the image: CTA r, row half h, TMEM lane m, k: plain rows of HH bytes (one per TMEM lane)
+__global__ void whh_image_kernel(const uint8_t *__restrict__ q, uint8_t *__restrict__ img, int HH)
 {
     const long o = (long)blockIdx.x * blockDim.x + threadIdx.x;
-    if (o >= (long)kC * kABytes)
+    const int a_bytes = 256 * HH;
+    if (o >= (long)(HH / kUnits) * a_bytes)
         return;
-    const int r = (int)(o / kABytes);
-    const int rem = (int)(o % kABytes);
-    const int h = rem / (128 * kHhC), m = (rem / kHhC) & 127, k = rem % kHhC;
+    const int r = (int)(o / a_bytes);
+    const int rem = (int)(o % a_bytes);
+    const int h = rem / (128 * HH), m = (rem / HH) & 127, k = rem % HH;
     const int qd = m >> 5, g = (m >> 3) & 3, up = 8 * qd + (m & 7); // lane 8*gate + unit' inside each 32-lane quadrant
-    const int row = g * kHhC + kUnits * r + 32 * h + up;
-    img[o] = q[(long)row * kHhC + k];
+    const int row = g * HH + kUnits * r + 32 * h + up;
+    img[o] = q[(long)row * HH + k];
 }
 
-template <int TP, int NG>
+template <int TP, int NG, int HH>
 int launch_tp(const ClusterArgs &P, cudaStream_t st)
 {
+    using C = Cfg<HH>;
     const int groups = ceil_div(P.a.n_tracks, TP * NG); // clusters per (target, direction)
     static PerDeviceOnce once; // one per template instantiation
     if (int rc = once.run([&](int) {
-            UMX_CUDA_OK(cudaFuncSetAttribute(lstm_cluster_kernel<TP, NG>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
+            UMX_CUDA_OK(cudaFuncSetAttribute(lstm_cluster_kernel<TP, NG, HH>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmemBytes));
             return 0;
         }))
         return rc;
-    dim3 grid(kC, 2 * P.a.target_count, groups);
-    lstm_cluster_kernel<TP, NG><<<grid, kThreads, kSmemBytes, st>>>(P);
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3(C::kC, 2 * P.a.target_count, groups);
+    cfg.blockDim = dim3(kThreads);
+    cfg.dynamicSmemBytes = C::kSmemBytes;
+    cfg.stream = st;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeClusterDimension;
+    at[0].val.clusterDim.x = C::kC;
+    at[0].val.clusterDim.y = 1;
+    at[0].val.clusterDim.z = 1;
+    cfg.attrs = at;
+    cfg.numAttrs = 1;
+    UMX_CUDA_OK(cudaLaunchKernelEx(&cfg, lstm_cluster_kernel<TP, NG, HH>, P));
     UMX_CUDA_OK(cudaGetLastError());
 #ifdef UMX_LSTM_TIMING
     if (getenv("UMX_LSTM_DEBUG"))
@@ -761,42 +786,44 @@ int launch_tp(const ClusterArgs &P, cudaStream_t st)
 }
 } // namespace
 
-size_t whh_image_bytes() { return (size_t)kC * kABytes; }
+size_t whh_image_bytes(int Hh) { return (size_t)(Hh / kUnits) * 256 * Hh; }
 
-int launch_whh_image(const uint8_t *q, uint8_t *img, cudaStream_t st)
+int launch_whh_image(const uint8_t *q, uint8_t *img, int Hh, cudaStream_t st)
 {
-    whh_image_kernel<<<ceil_div((long)kC * kABytes, 256), 256, 0, st>>>(q, img);
+    UMX_CHECK(lstm_cluster_supported(Hh), "whh_image: unsupported hidden size");
+    whh_image_kernel<<<ceil_div((long)whh_image_bytes(Hh), 256), 256, 0, st>>>(q, img, Hh);
     UMX_CUDA_OK(cudaGetLastError());
     return 0;
 }
 
-bool lstm_cluster_supported(int Hh) { return Hh == kHhC; }
+// UMX-L (512 units per direction: clusters of 8 CTAs) and UMX-HQ (256: clusters of 4)
+bool lstm_cluster_supported(int Hh) { return Hh == 512 || Hh == 256; }
 
 // how many 8-CTA clusters of the recurrence kernel the current device can run at once (0 on error)
 int lstm_cluster_max_active()
 {
     int n = 0;
     cudaLaunchConfig_t cfg{};
-    cfg.gridDim = dim3(kC, 64, 1);
+    cfg.gridDim = dim3(8, 64, 1);
     cfg.blockDim = dim3(kThreads);
-    cfg.dynamicSmemBytes = kSmemBytes;
+    cfg.dynamicSmemBytes = Cfg<512>::kSmemBytes;
     cudaLaunchAttribute at[1];
     at[0].id = cudaLaunchAttributeClusterDimension;
-    at[0].val.clusterDim.x = kC;
+    at[0].val.clusterDim.x = 8;
     at[0].val.clusterDim.y = 1;
     at[0].val.clusterDim.z = 1;
     cfg.attrs = at;
     cfg.numAttrs = 1;
-    if (cudaFuncSetAttribute(lstm_cluster_kernel<16, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes) != cudaSuccess)
+    if (cudaFuncSetAttribute(lstm_cluster_kernel<16, 2, 512>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg<512>::kSmemBytes) != cudaSuccess)
         return 0;
-    if (cudaOccupancyMaxActiveClusters(&n, lstm_cluster_kernel<16, 2>, &cfg) != cudaSuccess)
+    if (cudaOccupancyMaxActiveClusters(&n, lstm_cluster_kernel<16, 2, 512>, &cfg) != cudaSuccess)
         return 0;
     return n;
 }
 
 int launch_lstm_cluster(const LstmLayerArgs &a, const uint8_t *const (*img)[2], cudaStream_t st)
 {
-    UMX_CHECK(a.Hh == kHhC, "lstm_cluster: built for 512 hidden units per direction (UMX-L)");
+    UMX_CHECK(lstm_cluster_supported(a.Hh), "lstm_cluster: built for 512 (UMX-L) or 256 (UMX-HQ) hidden units per direction");
     ClusterArgs P;
     P.a = a;
     for (int t = 0; t < kTargets; ++t)
@@ -805,9 +832,9 @@ int launch_lstm_cluster(const LstmLayerArgs &a, const uint8_t *const (*img)[2], 
     // a cluster takes up to 32 tracks as two ping-pong groups: one group's MMAs and exchange run while the other's gates
     // are computed.  (Four groups of 8 — lstm_cluster_kernel<16, 2> — shorten the chain of a group but double the MMAs,
     // bulk copies and barrier traffic per step: measured 116 ms against 92 ms per bench step.)
-    if (a.n_tracks <= 16)
-        return launch_tp<8, 2>(P, st); // one or two groups of 8
-    return launch_tp<16, 2>(P, st);
+    if (a.Hh == 512)
+        return a.n_tracks <= 16 ? launch_tp<8, 2, 512>(P, st) : launch_tp<16, 2, 512>(P, st);
+    return a.n_tracks <= 16 ? launch_tp<8, 2, 256>(P, st) : launch_tp<16, 2, 256>(P, st);
 }
 
 } // namespace umx

@@ -449,9 +449,9 @@ static int build_operands(Model *m, std::map<std::string, uint8_t *> (&whh_raw)[
                 if (lstm_cluster_supported(Hh))
                 {
                     uint8_t *img = nullptr;
-                    if (dev_alloc(m, &img, whh_image_bytes()))
+                    if (dev_alloc(m, &img, whh_image_bytes(Hh)))
                         return -1;
-                    rc = launch_whh_image(whh_raw[t]["lstm.weight_hh" + sfx], img, 0);
+                    rc = launch_whh_image(whh_raw[t]["lstm.weight_hh" + sfx], img, Hh, 0);
                     if (rc)
                         return rc;
                     tw.whh_img[l][d] = img;

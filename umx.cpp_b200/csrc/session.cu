@@ -165,7 +165,7 @@ int session_create(Model *m, int max_tracks, int n_buf, Session **out)
         s->lstm_impl = 1;
         static bool warned = false;
         if (!warned)
-            fprintf(stderr, "umx_cuda: hidden_size %d has no tcgen05 cluster recurrence kernel (built for LSTM hidden 512 = UMX-L); "
+            fprintf(stderr, "umx_cuda: hidden_size %d has no tcgen05 cluster recurrence kernel (built for hidden_size 1024 = UMX-L and 512 = UMX-HQ); "
                             "this session runs the slow validation recurrence kernel (option lstm_impl = 1)\n", s->H);
         warned = true;
     }
