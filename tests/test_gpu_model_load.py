@@ -1,5 +1,6 @@
 """GPU: load_umx_model (src/model.cpp:42-665) on damaged model files.  The reference compares whole tensor names and answers
 anything else with "failed to load" (src/model.cpp:240-546); the C ABI promises a clean negative status, never a crash."""
+import numpy as np
 import pytest
 
 from oracle import synth
@@ -34,3 +35,24 @@ def test_truncated_and_garbage_files(umx, raw):
     with pytest.raises(umx.UmxCudaError, match="magic"):
         umx.load_umx_model(b"\x00" * 64)
     umx.load_umx_model(raw).close()  # the intact file still loads
+
+
+def test_model_written_by_the_cpp_writer_loads_bit_exact(umx, tmp_path):
+    """A model file made by the C++ ggml writer (cli/umx_make_ggml.cpp) loads, and its dequantised tensors equal the oracle's."""
+    import os
+    import subprocess
+
+    from oracle import umx_oracle as O
+
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    exe = os.path.join(root, "umx.cpp_b200", "umx.make-ggml")
+    if not os.path.exists(exe):
+        pytest.skip("umx.make-ggml not built")
+    out = tmp_path / "m.bin.gz"
+    assert subprocess.run([exe, str(out), "32", "9"], capture_output=True).returncode == 0
+    gm, om = umx.load_umx_model(str(out)), O.load_model(str(out))
+    assert gm.hidden_size == 32
+    for t in (0, 3):
+        assert np.array_equal(gm.tensor("fc1_w", t), om.t[t]["fc1.weight"].T)
+        assert np.array_equal(gm.tensor("fc3_w", t), om.t[t]["fc3.weight"].T)
+        assert np.array_equal(gm.tensor("lstm_hh_w", t, 1, 1), om.t[t]["lstm.weight_hh_l1_reverse"].T)

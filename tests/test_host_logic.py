@@ -93,3 +93,33 @@ def test_frames_beyond_a_chunk_are_exactly_zero_in_the_oracle(n_buf, n_wave):
     # tight up to the window's zero first tap: at most one frame more than strictly necessary is computed
     last_nonzero = max(f for f in range(F) if np.any(spec[:, f, :] != 0))
     assert fz - 1 - last_nonzero in (0, 1)
+
+
+def test_cpp_ggml_writer_round_trip(tmp_path):
+    """cli/umx_ggml_writer.hpp (the C++ counterpart of scripts/convert-umx-pth-to-ggml.py:96-160): the file it writes parses
+    with the oracle's reader (= src/model.cpp:93-553 restated), has the 4 x 43 tensors in state_dict order with the reference's
+    shapes and payload widths, and dequantises to within half a quantisation step of the fp32 values it was given."""
+    from oracle import ref, synth
+
+    exe = tmp_path / "umx.make-ggml"
+    subprocess.run(["/usr/bin/g++", "-O2", "-std=c++17", "-o", str(exe), os.path.join(ROOT, "cli", "umx_make_ggml.cpp"), "-lz"], check=True)
+    out, dump = tmp_path / "m.bin.gz", tmp_path / "m.f32"
+    r = subprocess.run([str(exe), str(out), "16", "5", "--dump-f32", str(dump)], capture_output=True, text=True)
+    assert r.returncode == 0 and "172 tensors" in r.stdout, r.stdout + r.stderr
+    hidden, targets = O.parse_ggml(O.gzip.decompress(out.read_bytes()))
+    assert hidden == 16 and len(targets) == 4 and all(len(t) == 43 for t in targets)
+    f32 = np.fromfile(dump, dtype=np.float32)
+    pos = 0
+    for tensors in targets:
+        for qt, (name, shape, _) in zip(tensors, synth.tensor_specs(16)):
+            assert qt.name == name and tuple(qt.dims) == tuple(reversed(shape))
+            assert qt.q.dtype == (np.uint16 if any(k in name for k in ("bn2", "bn3", "fc2", "fc3")) else np.uint8)
+            n = int(np.prod(shape))
+            want = f32[pos:pos + n].reshape(shape)
+            pos += n
+            assert np.abs(qt.dequant().reshape(shape) - want).max() <= 0.5001 * float(qt.scale) + 1e-7
+    assert pos == f32.size
+    if ref.available():  # the compiled reference's own loader accepts it too
+        rm = ref.Model(str(out))
+        assert rm.hidden == 16
+        assert np.array_equal(rm.tensor("fc1_w", 1), targets[1][4].dequant().reshape(16, 2974).T)
