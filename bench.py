@@ -192,7 +192,8 @@ def main():
     ap.add_argument("--track-seconds", type=float, default=180.0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--gemm-terms", type=int, default=0)
-    ap.add_argument("--pipeline", type=int, default=-1, help="session option: 0 in order, 2 post stage under the next segment's recurrences, 3 (default) segment wavefront")
+    ap.add_argument("--gemm-impl", type=int, default=-1, help="session option: 0 = tcgen05 CTA pairs (default), 3 = single-CTA tiles")
+    ap.add_argument("--pipeline", type=int, default=-1, help="session option: 0 = every kernel in order on one stream, 3 (default) = segment wavefront")
     ap.add_argument("--lane-targets", type=int, default=0, help="session option: targets per stream of the wavefront (1, 2, 4)")
     ap.add_argument("--timeline", default="", help="write the stage intervals of the last timed step to this file (JSON)")
     ap.add_argument("--no-e2e", action="store_true", help="profiling runs only: skip the host-buffer arm (the line then carries no e2e value)")
@@ -227,6 +228,8 @@ def main():
     sess = umx.Session(model, max_tracks=T, n_buf=SEG)
     if args.gemm_terms:
         sess.set_option("gemm_terms", args.gemm_terms)
+    if args.gemm_impl >= 0:
+        sess.set_option("gemm_impl", args.gemm_impl)
     if args.pipeline >= 0:
         sess.set_option("pipeline", args.pipeline)
     if args.lane_targets:
@@ -390,8 +393,6 @@ def main():
                 in_order["note"] = ("one extra step with option pipeline = 0 (every kernel in order on one stream) after the timed "
                                     "region: stage times do not overlap and match an ncu launch list of the step")
         schedules = {0: "every kernel in order on one stream",
-                     1: "Wiener/iSTFT/finalize of segment s on a second stream",
-                     2: "Wiener/iSTFT/finalize of segment s in slots under the recurrence kernels of segment s+1",
                      3: "segment wavefront: LSTM layer l of segment s+1 beside layer l+1 of segment s, one stream per (layer, target "
                         "group), post stage on a low-priority stream; stage times overlap"}
         GB = 1e9
@@ -405,7 +406,7 @@ def main():
                                    f"60 s segments, streaming LSTM, Wiener-EM",
                        "tracks_per_gpu": T, "segments_per_track": segs, "weights": "synthetic UMX-L u8/u16 ggml (seed 1234)",
                        "l2": "inputs and intermediates per step are far larger than L2 (>1 GB per track-segment)",
-                       "schedule": schedules[pipeline], "gemm_terms": terms},
+                       "schedule": schedules[0 if pipeline == 0 else 3], "gemm_terms": terms},
             "e2e": {"value": e2e_value, "unit": "audio-s/s", "h2d_bytes_per_step": T * n * 8, "d2h_bytes_per_step": T * n * 32,
                     "steps": k_e2e, "ms_per_step": e2e_ms_max, "h2d_ms": copy_ms.get("h2d"), "d2h_ms": copy_ms.get("d2h"),
                     "h2d_gbs": (T * n * 8 / GB) / (copy_ms["h2d"] / 1e3) if copy_ms.get("h2d") else None,

@@ -3,6 +3,8 @@ restatement pinned to the compiled reference) and the golden vectors of the comp
 
 Tolerances are BASELINE.json's: dequantised weights and segment indexing bit-exact; spectrograms
 <= 1e-4 relative; stem waveforms <= 1e-3 max-abs and SDR >= 60 dB against the reference."""
+import os
+
 import numpy as np
 import pytest
 
@@ -142,7 +144,10 @@ def test_wiener_zero_mix_and_loud_mix(umx):
 
 
 # ---- network / inference ------------------------------------------------------------------------------
-@pytest.mark.parametrize("gemm_impl", [1, 0])
+PAIRS = [3]  # gemm_impl: 0 = tcgen05 CTA pairs (default), 3 = single-CTA tiles
+
+
+@pytest.mark.parametrize("gemm_impl", [1, 0] + PAIRS)
 def test_umx_inference_golden(umx, small, G, gemm_impl):
     gm, _ = small
     sess = umx.Session(gm, 1, gi.N_BUF)
@@ -154,7 +159,7 @@ def test_umx_inference_golden(umx, small, G, gemm_impl):
         assert min(sdr(got[j], G[call][j]) for j in range(4)) > SDR_MIN
 
 
-@pytest.mark.parametrize("gemm_impl", [1, 0])
+@pytest.mark.parametrize("gemm_impl", [1, 0] + PAIRS)
 def test_target_mags_vs_oracle(umx, small, G, gemm_impl):
     gm, om = small
     sess = umx.Session(gm, 1, gi.N_BUF)
@@ -166,7 +171,7 @@ def test_target_mags_vs_oracle(umx, small, G, gemm_impl):
         assert rel(got[j], want) < 1e-3
 
 
-@pytest.mark.parametrize("gemm_impl,terms", [(1, 3), (0, 3), (0, 2), (0, 1)])
+@pytest.mark.parametrize("gemm_impl,terms", [(1, 3), (0, 3), (0, 2), (0, 1)] + [(3, 3), (3, 2), (3, 1)])
 def test_demix_multi_segment_multi_track(umx, gemm_impl, terms):
     """shift + split + recombine (umx.cpp:99-295) on three tracks of different lengths in lockstep."""
     hidden, n_buf = 64, 16384
@@ -227,6 +232,21 @@ def test_demix_direct_final_identical(umx, hidden):
         want, got = a.demix(tracks, shift_offset=shift), b.demix(tracks, shift_offset=shift)
         for g, w in zip(got, want):
             assert np.array_equal(g, w)
+
+
+@pytest.mark.parametrize("terms", [3, 2, 1])
+def test_gemm_cta_pairs_identical_to_single_cta(umx, terms):
+    """gemm_impl 0 (tcgen05.mma.cta_group::2 on 256 x 256 tiles, B split across the pair; the default) accumulates every output element over
+    the same k-blocks in the same order as the single-CTA kernel (gemm_impl 3): identical bits, at the UMX-L hidden size, ragged row counts."""
+    n_buf = 16384
+    gm = umx.load_umx_model(synth.make_ggml(hidden=1024, seed=80))
+    tracks = [synth.make_audio(n, 60 + i) for i, n in enumerate((40000, 9000, 23000, 30000, 12000))]
+    a, b = umx.Session(gm, len(tracks), n_buf), umx.Session(gm, len(tracks), n_buf)
+    for sess, impl in ((a, 3), (b, 0)):
+        sess.set_option("gemm_impl", impl)
+        sess.set_option("gemm_terms", terms)
+    for g, w in zip(b.demix(tracks), a.demix(tracks)):
+        assert np.array_equal(g, w)
 
 
 def test_demix_shift_offsets_and_trim(umx, small):

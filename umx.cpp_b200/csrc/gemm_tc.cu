@@ -32,14 +32,19 @@ constexpr int BM = 128, BN = 256;
 //   TERMS 1: A_hi, B_hi              k-block 64 (128-byte rows, SWIZZLE_128B)   48 KB/stage, 4 stages
 //   TERMS 2: A_hi, A_lo, B_hi        k-block 32 ( 64-byte rows, SWIZZLE_64B)    32 KB/stage, 6 stages
 //   TERMS 3: A_hi, A_lo, B_hi, B_lo  k-block 32 ( 64-byte rows, SWIZZLE_64B)    48 KB/stage, 4 stages
-template <int TERMS>
+// PAIR: two CTAs of a cluster (one TPC) work on one 256 x 256 tile with tcgen05.mma.cta_group::2: each CTA stages its own 128
+// rows of A and HALF of the B tile (128 of the 256 weight rows); the tensor cores of both SMs read both halves.  Per CTA and
+// k-block the B traffic — TMA writes and MMA operand reads — halves, which is what bounds the K = 1024 launches.
+template <int TERMS, bool PAIR = false>
 struct Cfg
 {
     static constexpr int BK = TERMS == 1 ? 64 : 32;
     static constexpr int nA = TERMS >= 2 ? 2 : 1, nB = TERMS == 3 ? 2 : 1;
-    static constexpr int kAPlane = BM * BK * 2, kBPlane = BN * BK * 2;
+    static constexpr int kBRows = PAIR ? BN / 2 : BN; // B rows this CTA stages
+    static constexpr int kAPlane = BM * BK * 2, kBPlane = kBRows * BK * 2;
     static constexpr int kStageBytes = nA * kAPlane + nB * kBPlane;
-    static constexpr int kStages = TERMS == 2 ? 6 : 4;
+    static constexpr int kStages = PAIR ? 6 : (TERMS == 2 ? 6 : 4);
+    static constexpr int kTileM = PAIR ? 2 * BM : BM; // rows of one scheduled tile
 };
 constexpr int kEpiWarps = 8;  // two per TMEM lane quadrant, each takes one half of the tile's columns
 // Transpose tile of one epilogue warp: 32 rows x 16 columns of fp32, 64-byte rows, the four 16-byte chunks of row r stored at
@@ -80,7 +85,7 @@ struct alignas(64) TcParams
 {
     CUtensorMap a_hi[kMaxGemmProblems], a_lo[kMaxGemmProblems], b_hi[kMaxGemmProblems], b_lo[kMaxGemmProblems];
     TcProblem p[kMaxGemmProblems];
-    int count, total_tiles, terms, pad_;
+    int count, total_tiles, terms, tile_m; // tile_m: rows of one scheduled tile (128, or 256 for CTA pairs)
     // null: tiles blockIdx.x, + gridDim.x, ...; else int[2] {next tile, CTAs finished}, both zero at launch: tiles are drawn from
     // the first, and the last CTA to finish puts both back to zero for the next launch (no memset between launches: a memset
     // node may be served by a copy engine and then queues behind whatever host<->device copies that engine has pending)
@@ -177,10 +182,85 @@ __device__ __forceinline__ void epi_rows(const EpiRows &e, const float (&al)[4],
     }
 }
 
-template <int TERMS>
+// ---- CTA-pair (cta_group::2) forms ---------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t cluster_ctarank()
+{
+    uint32_t r;
+    asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+    return r;
+}
+__device__ __forceinline__ uint32_t mapa_cluster(uint32_t local_addr, uint32_t cta)
+{
+    uint32_t r;
+    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(local_addr), "r"(cta));
+    return r;
+}
+__device__ __forceinline__ void cluster_sync()
+{
+    asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+// TMA tile load whose bytes are counted on a barrier that may live in the peer CTA of the pair (the leader's)
+__device__ __forceinline__ void tma_load_2d_pair(uint32_t dst, const CUtensorMap *map, int c0, int c1, uint32_t bar_cluster_addr)
+{
+    asm volatile("cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
+                 ::"r"(dst), "l"(map), "r"(c0), "r"(c1), "r"(bar_cluster_addr)
+                 : "memory");
+}
+__device__ __forceinline__ void mma_f16_pair(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc, uint32_t accumulate)
+{
+    asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+                 "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(d_tmem),
+                 "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate)
+                 : "memory");
+}
+// arrive on the barrier at this shared-memory offset in BOTH CTAs of the pair once the MMAs issued so far have retired
+__device__ __forceinline__ void tc_commit_pair(uint32_t bar)
+{
+    asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(bar),
+                 "h"((uint16_t)3)
+                 : "memory");
+}
+__device__ __forceinline__ void mbar_arrive_cluster(uint32_t bar_cluster_addr)
+{
+    asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(bar_cluster_addr) : "memory");
+}
+__device__ __forceinline__ void st_cluster_u32(uint32_t cluster_addr, uint32_t v)
+{
+    asm volatile("st.shared::cluster.u32 [%0], %1;" ::"r"(cluster_addr), "r"(v) : "memory");
+}
+// wait on a LOCAL barrier whose arrivals (and the data they publish) come from the peer CTA: cluster-scope acquire
+__device__ __forceinline__ void mbar_wait_cluster(uint32_t bar, uint32_t parity)
+{
+    const long long t0 = clock64();
+    for (;;)
+    {
+        uint32_t ok;
+        asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 p, [%1], %2;\n\t"
+                     "selp.u32 %0, 1, 0, p;\n\t}"
+                     : "=r"(ok)
+                     : "r"(bar), "r"(parity)
+                     : "memory");
+        if (ok)
+            return;
+        if (clock64() - t0 > 4000000000LL) // a protocol bug must abort the kernel, never hang the GPU
+            __trap();
+    }
+}
+__device__ __forceinline__ void tmem_alloc_pair(uint32_t smem_dst, uint32_t cols) // one warp of EACH CTA of the pair
+{
+    asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_dst), "r"(cols) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc_pair(uint32_t taddr, uint32_t cols)
+{
+    asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(cols) : "memory");
+}
+
+template <int TERMS, bool PAIR>
 __global__ void __launch_bounds__(kThreads, 1) gemm_tc_kernel(const __grid_constant__ TcParams P)
 {
-    using C = Cfg<TERMS>;
+    using C = Cfg<TERMS, PAIR>;
+    const uint32_t rank = PAIR ? cluster_ctarank() : 0u; // CTA of the pair: 0 = leader (issues the MMAs)
     constexpr int BK = C::BK, kStages = C::kStages, kStageBytes = C::kStageBytes, kAPlane = C::kAPlane, kBPlane = C::kBPlane;
     static_assert(kStages * kStageBytes <= 4 * 49152 && kStages <= kMaxStages, "stage ring does not fit");
     extern __shared__ uint8_t smem_raw[];
@@ -196,6 +276,10 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_tc_kernel(const __grid_const
     // the tiles may come from a global counter (CTAs that get their SM late, or share the GPU with other kernels, take fewer)
     const uint32_t sfull0 = smem_u32(bars + 2 * kMaxStages + 5), sempty0 = sfull0 + 8 * kSched;
     volatile int *sched_tile = reinterpret_cast<volatile int *>(bars + 2 * kMaxStages + 5 + 2 * kSched);
+    // CTA pairs drawing from the global counter: the LEADER draws and hands every tile index to both rings; the peer's ten
+    // readers (its producer, its MMA thread, its 8 epilogue warps) release a slot on the leader's psempty barrier
+    const uint32_t psempty0 = smem_u32(bars + 2 * kMaxStages + 5 + 2 * kSched + 2);
+    const bool pair_dyn = PAIR && P.tile_counter != nullptr;
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
@@ -209,20 +293,28 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_tc_kernel(const __grid_const
         for (int i = 0; i < 2; ++i)
         {
             mbar_init(tfull0 + 8 * i, 1);
-            mbar_init(tempty0 + 8 * i, kEpiWarps);
+            mbar_init(tempty0 + 8 * i, PAIR ? 2 * kEpiWarps : kEpiWarps); // pair: the leader's barrier collects both CTAs' epilogues
         }
         for (int i = 0; i < kSched; ++i)
         {
             mbar_init(sfull0 + 8 * i, 1);
             mbar_init(sempty0 + 8 * i, 1 + kEpiWarps); // the MMA thread and one lane per epilogue warp
+            mbar_init(psempty0 + 8 * i, 2 + kEpiWarps);
         }
         fence_barrier_init();
     }
     if (warp == 1)
-        tmem_alloc(smem_u32(tmem_slot), kTmemCols);
+    {
+        if (PAIR)
+            tmem_alloc_pair(smem_u32(tmem_slot), kTmemCols);
+        else
+            tmem_alloc(smem_u32(tmem_slot), kTmemCols);
+    }
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
+    if (PAIR)
+        cluster_sync(); // both CTAs' barriers exist before a TMA load or an arrive of the peer can reach them
     const uint32_t tmem_base = *tmem_slot;
 
     auto locate = [&](int tile, int &pi, int &m0, int &n0) {
@@ -233,7 +325,7 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_tc_kernel(const __grid_const
         // n fastest: the CTAs running together cover a band of ~grid / n_tiles row tiles x all column tiles, so the
         // activations (the big operand) stream from HBM once while the weights (a few MB) stay in L2
         n0 = (local % P.p[pi].n_tiles) * BN;
-        m0 = (local / P.p[pi].n_tiles) * BM;
+        m0 = (local / P.p[pi].n_tiles) * C::kTileM;
     };
     // A row tile none of whose rows is a frame that reaches its track's chunk is not computed (all three warp roles skip
     // the same tiles, so their pipeline counters stay in step).
@@ -245,13 +337,27 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_tc_kernel(const __grid_const
         const int t0 = m0 / F, f0 = m0 - t0 * F;
         if (f0 < frames_reaching(ch[t0].n_wave, F) + P.p[pi].extra_rows)
             return true;
-        const int t1 = (min(m0 + BM, P.p[pi].M) - 1) / F;
+        const int t1 = (min(m0 + C::kTileM, P.p[pi].M) - 1) / F;
         for (int t = t0 + 1; t <= t1; ++t) // later tracks start inside this tile at frame 0
             if (ch[t].n_wave > 0 || P.p[pi].extra_rows)
                 return true;
         return false;
     };
 
+
+    // a reader of the tile ring is done with slot `sslot`
+    auto release_slot = [&](int sslot) {
+        if (pair_dyn && rank != 0)
+            mbar_arrive_cluster(mapa_cluster(psempty0 + 8 * sslot, 0));
+        else
+            mbar_arrive(sempty0 + 8 * sslot);
+    };
+    auto wait_slot = [&](int sslot, uint32_t sphase) {
+        if (pair_dyn && rank != 0)
+            mbar_wait_cluster(sfull0 + 8 * sslot, sphase);
+        else
+            mbar_wait(sfull0 + 8 * sslot, sphase);
+    };
 
     if (warp == 0)
     {
@@ -262,26 +368,46 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_tc_kernel(const __grid_const
             uint32_t phase = 0;
             int sslot = 0;
             uint32_t sphase = 0;
-            int *const counter = P.tile_counter;
-            int cand = counter ? atomicAdd(counter, 1) : (int)blockIdx.x;
+            // static stride: every CTA (both CTAs of a pair alike) derives its tiles itself.  Global counter: the CTA — of a pair,
+            // the leader — draws them
+            int *const counter = (PAIR && rank != 0) ? nullptr : P.tile_counter;
+            const int stride = PAIR ? (int)gridDim.x / 2 : (int)gridDim.x;
+            int cand = counter ? atomicAdd(counter, 1) : (PAIR ? (int)blockIdx.x / 2 : (int)blockIdx.x);
             for (;;)
             {
-                // next tile that has to be computed (row tiles beyond every chunk are skipped here, once, for all warp roles)
                 int tile = -1, pi = 0, m0 = 0, n0 = 0;
-                while (cand < P.total_tiles)
-                {
-                    locate(cand, pi, m0, n0);
-                    const int c = cand;
-                    cand = counter ? atomicAdd(counter, 1) : cand + (int)gridDim.x; // the next draw is in flight during this tile's loads
-                    if (needed(pi, m0))
-                    {
-                        tile = c;
-                        break;
-                    }
+                if (pair_dyn && rank != 0)
+                { // the peer's producer reads what the leader drew
+                    mbar_wait_cluster(sfull0 + 8 * sslot, sphase);
+                    tile = sched_tile[sslot];
+                    release_slot(sslot);
+                    if (tile >= 0)
+                        locate(tile, pi, m0, n0);
                 }
-                mbar_wait(sempty0 + 8 * sslot, sphase ^ 1);
-                sched_tile[sslot] = tile;
-                mbar_arrive(sfull0 + 8 * sslot);
+                else
+                {
+                    // next tile that has to be computed (row tiles beyond every chunk are skipped here, once, for all warp roles)
+                    while (cand < P.total_tiles)
+                    {
+                        locate(cand, pi, m0, n0);
+                        const int c = cand;
+                        cand = counter ? atomicAdd(counter, 1) : cand + stride; // the next draw is in flight during this tile's loads
+                        if (needed(pi, m0))
+                        {
+                            tile = c;
+                            break;
+                        }
+                    }
+                    mbar_wait(sempty0 + 8 * sslot, sphase ^ 1);
+                    sched_tile[sslot] = tile;
+                    if (pair_dyn)
+                    { // ... and the peer's ring: its readers are done with the slot, the index goes over, its full barrier follows
+                        mbar_wait_cluster(psempty0 + 8 * sslot, sphase ^ 1);
+                        st_cluster_u32(mapa_cluster(smem_u32(const_cast<int *>(sched_tile) + sslot), 1), (uint32_t)tile);
+                        mbar_arrive_cluster(mapa_cluster(sfull0 + 8 * sslot, 1));
+                    }
+                    mbar_arrive(sfull0 + 8 * sslot);
+                }
                 if (++sslot == kSched)
                 {
                     sslot = 0;
@@ -293,15 +419,31 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_tc_kernel(const __grid_const
                 for (int kb = 0; kb < kblocks; ++kb)
                 {
                     mbar_wait(empty0 + 8 * stage, phase ^ 1);
-                    const uint32_t bar = full0 + 8 * stage;
-                    mbar_arrive_expect_tx(bar, kStageBytes);
                     const uint32_t sa = smem_u32(smem + stage * kStageBytes);
-                    tma_load_2d(sa, &P.a_hi[pi], kb * BK, m0, bar);
-                    if (C::nA == 2)
-                        tma_load_2d(sa + kAPlane, &P.a_lo[pi], kb * BK, m0, bar);
-                    tma_load_2d(sa + C::nA * kAPlane, &P.b_hi[pi], kb * BK, n0, bar);
-                    if (C::nB == 2)
-                        tma_load_2d(sa + C::nA * kAPlane + kBPlane, &P.b_lo[pi], kb * BK, n0, bar);
+                    if (PAIR)
+                    { // this CTA's 128 rows of A and its half of the B tile; every byte is counted on the LEADER's full barrier
+                        const uint32_t bar = mapa_cluster(full0 + 8 * stage, 0);
+                        if (rank == 0)
+                            mbar_arrive_expect_tx(full0 + 8 * stage, 2 * kStageBytes);
+                        const int ma = m0 + (int)rank * BM, nb = n0 + (int)rank * C::kBRows;
+                        tma_load_2d_pair(sa, &P.a_hi[pi], kb * BK, ma, bar);
+                        if (C::nA == 2)
+                            tma_load_2d_pair(sa + kAPlane, &P.a_lo[pi], kb * BK, ma, bar);
+                        tma_load_2d_pair(sa + C::nA * kAPlane, &P.b_hi[pi], kb * BK, nb, bar);
+                        if (C::nB == 2)
+                            tma_load_2d_pair(sa + C::nA * kAPlane + kBPlane, &P.b_lo[pi], kb * BK, nb, bar);
+                    }
+                    else
+                    {
+                        const uint32_t bar = full0 + 8 * stage;
+                        mbar_arrive_expect_tx(bar, kStageBytes);
+                        tma_load_2d(sa, &P.a_hi[pi], kb * BK, m0, bar);
+                        if (C::nA == 2)
+                            tma_load_2d(sa + kAPlane, &P.a_lo[pi], kb * BK, m0, bar);
+                        tma_load_2d(sa + C::nA * kAPlane, &P.b_hi[pi], kb * BK, n0, bar);
+                        if (C::nB == 2)
+                            tma_load_2d(sa + C::nA * kAPlane + kBPlane, &P.b_lo[pi], kb * BK, n0, bar);
+                    }
                     if (++stage == kStages)
                     {
                         stage = 0;
@@ -324,9 +466,9 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_tc_kernel(const __grid_const
             uint32_t sphase = 0;
             for (;;)
             {
-                mbar_wait(sfull0 + 8 * sslot, sphase);
+                wait_slot(sslot, sphase);
                 const int tile = sched_tile[sslot];
-                mbar_arrive(sempty0 + 8 * sslot);
+                release_slot(sslot);
                 if (++sslot == kSched)
                 {
                     sslot = 0;
@@ -334,11 +476,14 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_tc_kernel(const __grid_const
                 }
                 if (tile < 0)
                     break;
+                if (PAIR && rank != 0)
+                    continue; // the leader issues for both CTAs; this thread only keeps the tile ring moving
                 int pi, m0, n0;
                 locate(tile, pi, m0, n0);
                 const int kiters = (P.p[pi].K + BK - 1) / BK;
-                // a ragged last column tile only pays for the columns it has (N of the MMA in steps of 16)
-                const uint32_t idesc = idesc_f16_f32acc(BM, min(BN, (P.p[pi].N - n0 + 15) & ~15));
+                // a ragged last column tile only pays for the columns it has (N of the MMA in steps of 16); a pair always issues
+                // the full width: its B rows are split between the two CTAs at N / 2
+                const uint32_t idesc = PAIR ? idesc_f16_f32acc(2 * BM, BN) : idesc_f16_f32acc(BM, min(BN, (P.p[pi].N - n0 + 15) & ~15));
                 mbar_wait(tempty0 + 8 * acc, acc_phase ^ 1); // epilogue has drained this accumulator
                 tc_fence_after();
                 const uint32_t d_tmem = tmem_base + acc * BN;
@@ -353,20 +498,33 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_tc_kernel(const __grid_const
 #pragma unroll
                     for (int k = 0; k < BK / 16; ++k) // +32 bytes per K=16 step inside the swizzle row
                     {
-                        mma_f16(d_tmem, a_hi + 2 * k, b_hi + 2 * k, idesc, (it > 0 || k > 0) ? 1u : 0u); // hi * hi
+                        auto mma = [&](uint64_t da, uint64_t db, uint32_t accum) {
+                            if (PAIR)
+                                mma_f16_pair(d_tmem, da, db, idesc, accum);
+                            else
+                                mma_f16(d_tmem, da, db, idesc, accum);
+                        };
+                        mma(a_hi + 2 * k, b_hi + 2 * k, (it > 0 || k > 0) ? 1u : 0u); // hi * hi
                         if (C::nA == 2)
-                            mma_f16(d_tmem, desc(sa + kAPlane) + 2 * k, b_hi + 2 * k, idesc, 1u);          // lo * hi
+                            mma(desc(sa + kAPlane) + 2 * k, b_hi + 2 * k, 1u);          // lo * hi
                         if (C::nB == 2)
-                            mma_f16(d_tmem, a_hi + 2 * k, desc(sb + kBPlane) + 2 * k, idesc, 1u);          // hi * lo
+                            mma(a_hi + 2 * k, desc(sb + kBPlane) + 2 * k, 1u);          // hi * lo
                     }
-                    tc_commit(empty0 + 8 * stage); // frees the smem slot when these MMAs retire
+                    // frees the smem slot (in both CTAs of a pair) when these MMAs retire
+                    if (PAIR)
+                        tc_commit_pair(empty0 + 8 * stage);
+                    else
+                        tc_commit(empty0 + 8 * stage);
                     if (++stage == kStages)
                     {
                         stage = 0;
                         phase ^= 1;
                     }
                 }
-                tc_commit(tfull0 + 8 * acc); // accumulator complete
+                if (PAIR)
+                    tc_commit_pair(tfull0 + 8 * acc); // accumulator complete, in both CTAs
+                else
+                    tc_commit(tfull0 + 8 * acc);
                 if (++acc == 2)
                 {
                     acc = 0;
@@ -392,11 +550,11 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_tc_kernel(const __grid_const
         uint32_t sphase = 0;
         for (;;)
         {
-            mbar_wait(sfull0 + 8 * sslot, sphase);
+            wait_slot(sslot, sphase);
             const int tile = sched_tile[sslot];
             __syncwarp();
             if (lane == 0)
-                mbar_arrive(sempty0 + 8 * sslot);
+                release_slot(sslot);
             if (++sslot == kSched)
             {
                 sslot = 0;
@@ -416,7 +574,7 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_tc_kernel(const __grid_const
             float *__restrict__ of32 = P.p[pi].out_f32;
             __half *__restrict__ ohi = P.p[pi].out_hi;
             __half *__restrict__ olo = P.p[pi].out_lo;
-            const int row0 = m0 + 32 * q;
+            const int row0 = m0 + (int)rank * BM + 32 * q; // a pair's second CTA holds rows 128..255 of the tile
             // the rank-1 term's row factors of this thread's 8 rows: loaded once per tile, before waiting for the MMAs
             float rvv[4];
 #pragma unroll
@@ -450,7 +608,12 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_tc_kernel(const __grid_const
                     tc_fence_before();
                     __syncwarp();
                     if (lane == 0)
-                        mbar_arrive(tempty0 + 8 * acc);
+                    {
+                        if (PAIR && rank != 0)
+                            mbar_arrive_cluster(mapa_cluster(tempty0 + 8 * acc, 0));
+                        else
+                            mbar_arrive(tempty0 + 8 * acc);
+                    }
                 }
                 if (nc0 >= N)
                     continue;
@@ -486,10 +649,15 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_tc_kernel(const __grid_const
 
     tc_fence_before();
     __syncthreads();
+    if (PAIR)
+        cluster_sync(); // no CTA of a pair leaves (or frees tensor memory) while its peer may still signal or read it
     if (warp == 1)
     {
         tc_fence_after();
-        tmem_dealloc(tmem_base, kTmemCols);
+        if (PAIR)
+            tmem_dealloc_pair(tmem_base, kTmemCols);
+        else
+            tmem_dealloc(tmem_base, kTmemCols);
     }
     if (P.tile_counter && threadIdx.x == 0)
     { // this CTA's last draw is long done (the producer left its loop): the last CTA out re-arms the queue
@@ -544,7 +712,7 @@ int make_map(CUtensorMap *map, const __half *ptr, int K, int rows, int ld, int b
 }
 } // namespace
 
-int launch_gemm_tc(const GemmBatch &batch, int terms, cudaStream_t st, int *tile_counter)
+int launch_gemm_tc(const GemmBatch &batch, int terms, cudaStream_t st, int *tile_counter, bool pair)
 {
     UMX_CHECK(batch.count >= 1 && batch.count <= kMaxGemmProblems, "gemm_tc: bad problem count");
     UMX_CHECK(terms >= 1 && terms <= 3, "gemm_tc: terms must be 1..3");
@@ -562,9 +730,10 @@ int launch_gemm_tc(const GemmBatch &batch, int terms, cudaStream_t st, int *tile
         UMX_CHECK((terms < 2 || g.A.lo != nullptr) && (terms < 3 || g.B.lo != nullptr), "gemm_tc: the chosen terms need lo planes");
         UMX_CHECK(g.rowvec == nullptr || g.gamma != nullptr, "gemm_tc: rowvec needs gamma");
         const int bk = terms == 1 ? 64 : 32;
-        if (make_map(&P.a_hi[i], g.A.hi, g.K, g.M, g.A.ld, BM, bk) || make_map(&P.b_hi[i], g.B.hi, g.K, g.N, g.B.ld, BN, bk) ||
+        const int b_rows = pair ? BN / 2 : BN; // a CTA of a pair stages half of the B tile
+        if (make_map(&P.a_hi[i], g.A.hi, g.K, g.M, g.A.ld, BM, bk) || make_map(&P.b_hi[i], g.B.hi, g.K, g.N, g.B.ld, b_rows, bk) ||
             (terms >= 2 && make_map(&P.a_lo[i], g.A.lo, g.K, g.M, g.A.ld, BM, bk)) ||
-            (terms >= 3 && make_map(&P.b_lo[i], g.B.lo, g.K, g.N, g.B.ld, BN, bk)))
+            (terms >= 3 && make_map(&P.b_lo[i], g.B.lo, g.K, g.N, g.B.ld, b_rows, bk)))
             return -1;
         TcProblem &p = P.p[i];
         p.M = g.M;
@@ -585,33 +754,60 @@ int launch_gemm_tc(const GemmBatch &batch, int terms, cudaStream_t st, int *tile
         p.rows_per_track = g.rows_per_track;
         p.extra_rows = g.extra_rows;
         UMX_CHECK(!g.chunks || g.rows_per_track > 0, "gemm_tc: rows_per_track missing");
-        p.m_tiles = ceil_div(g.M, BM);
+        p.m_tiles = ceil_div(g.M, pair ? 2 * BM : BM);
         p.n_tiles = ceil_div(g.N, BN);
         p.tile_begin = tiles;
         tiles += p.m_tiles * p.n_tiles;
     }
     P.total_tiles = tiles;
     P.tile_counter = tile_counter;
+    P.tile_m = pair ? 2 * BM : BM;
 
     static PerDeviceOnce once;
     static int sm_count[64] = {};
     if (int rc = once.run([&](int dev) {
-            UMX_CUDA_OK(cudaFuncSetAttribute(gemm_tc_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
-            UMX_CUDA_OK(cudaFuncSetAttribute(gemm_tc_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
-            UMX_CUDA_OK(cudaFuncSetAttribute(gemm_tc_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
+            UMX_CUDA_OK(cudaFuncSetAttribute(gemm_tc_kernel<1, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
+            UMX_CUDA_OK(cudaFuncSetAttribute(gemm_tc_kernel<2, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
+            UMX_CUDA_OK(cudaFuncSetAttribute(gemm_tc_kernel<3, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
+            UMX_CUDA_OK(cudaFuncSetAttribute(gemm_tc_kernel<1, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
+            UMX_CUDA_OK(cudaFuncSetAttribute(gemm_tc_kernel<2, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
+            UMX_CUDA_OK(cudaFuncSetAttribute(gemm_tc_kernel<3, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
             UMX_CUDA_OK(cudaDeviceGetAttribute(&sm_count[dev], cudaDevAttrMultiProcessorCount, dev));
             return 0;
         }))
         return rc;
     int dev = 0;
     UMX_CUDA_OK(cudaGetDevice(&dev));
+    if (pair)
+    { // clusters of two CTAs (one TPC); one pair per tile at a time
+        cudaLaunchConfig_t cfg{};
+        cfg.gridDim = dim3(2 * std::min(tiles, sm_count[dev] / 2));
+        cfg.blockDim = dim3(kThreads);
+        cfg.dynamicSmemBytes = kSmemBytes;
+        cfg.stream = st;
+        cudaLaunchAttribute at[1];
+        at[0].id = cudaLaunchAttributeClusterDimension;
+        at[0].val.clusterDim.x = 2;
+        at[0].val.clusterDim.y = 1;
+        at[0].val.clusterDim.z = 1;
+        cfg.attrs = at;
+        cfg.numAttrs = 1;
+        if (terms == 1)
+            UMX_CUDA_OK(cudaLaunchKernelEx(&cfg, gemm_tc_kernel<1, true>, P));
+        else if (terms == 2)
+            UMX_CUDA_OK(cudaLaunchKernelEx(&cfg, gemm_tc_kernel<2, true>, P));
+        else
+            UMX_CUDA_OK(cudaLaunchKernelEx(&cfg, gemm_tc_kernel<3, true>, P));
+        UMX_CUDA_OK(cudaGetLastError());
+        return 0;
+    }
     const int grid = std::min(tiles, sm_count[dev]);
     if (terms == 1)
-        gemm_tc_kernel<1><<<grid, kThreads, kSmemBytes, st>>>(P);
+        gemm_tc_kernel<1, false><<<grid, kThreads, kSmemBytes, st>>>(P);
     else if (terms == 2)
-        gemm_tc_kernel<2><<<grid, kThreads, kSmemBytes, st>>>(P);
+        gemm_tc_kernel<2, false><<<grid, kThreads, kSmemBytes, st>>>(P);
     else
-        gemm_tc_kernel<3><<<grid, kThreads, kSmemBytes, st>>>(P);
+        gemm_tc_kernel<3, false><<<grid, kThreads, kSmemBytes, st>>>(P);
     UMX_CUDA_OK(cudaGetLastError());
     return 0;
 }

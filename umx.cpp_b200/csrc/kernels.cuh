@@ -116,7 +116,8 @@ int launch_gemm_simt(const GemmBatch &batch, cudaStream_t st);
 // tile_counter (optional, device int[2], zero before the first launch; every launch leaves it zero): tiles are drawn from it at
 // run time instead of the static blockIdx stride, so a launch that shares the GPU with other kernels finishes as soon as the
 // CTAs that did get an SM have worked through all tiles.  Launches that may overlap need counters of their own.
-int launch_gemm_tc(const GemmBatch &batch, int terms, cudaStream_t st, int *tile_counter = nullptr);
+// pair: CTA pairs (tcgen05.mma.cta_group::2) on 256 x 256 tiles, static tile stride
+int launch_gemm_tc(const GemmBatch &batch, int terms, cudaStream_t st, int *tile_counter = nullptr, bool pair = false);
 
 // ---- lstm ----------------------------------------------------------------------------------------
 struct LstmLayerArgs

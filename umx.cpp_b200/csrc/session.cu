@@ -341,7 +341,11 @@ static int run_gemm(Session *s, const GemmBatch &b, cudaStream_t st, int terms =
     s->launches++;
     if (s->gemm_impl == 1)
         return launch_gemm_simt(b, st);
-    return launch_gemm_tc(b, terms ? terms : s->gemm_terms, st, tile_counter);
+    // CTA pairs (256 x 256 tiles, B split across the pair) for every launch: measured faster than single-CTA tiles even for fc3,
+    // whose 17th column tile holds 2 of 256 columns (in-order GEMM time per bench step 105.4 ms with pairs everywhere, 107.1 ms
+    // with single-CTA tiles for fc3 only, 111.4 ms without pairs)
+    const bool pair = s->gemm_impl != 3;
+    return launch_gemm_tc(b, terms ? terms : s->gemm_terms, st, tile_counter, pair);
 }
 
 static cudaEvent_t take_event(Session *s, size_t &cursor)
