@@ -14,6 +14,7 @@
 #include "wiener_math.cuh"
 
 #include <cmath>
+#include <cstdlib>
 #include <mutex>
 #include <vector>
 
@@ -409,7 +410,7 @@ __global__ void __launch_bounds__(kWiThreads, 1)
     wiener_istft_kernel(const float2 *__restrict__ spec, const float *__restrict__ mask, long mask_target_stride, int mask_ld,
                         const float *__restrict__ maxabs, const float *__restrict__ stats, int F,
                         const IstftTrack *__restrict__ tracks, int n_buf, int stem_begin, int stem_count, int frame_begin,
-                        int frame_end, int stat_windows, int win_len, int flags)
+                        int frame_end, int stat_windows, int win_len, int flags, int frames_per_cta)
 {
     const int psd_abs2 = flags & 1, reg_once = (flags >> 1) & 1, no_em = (flags >> 2) & 1; // WienerArgs: upstream-faithful variants
     extern __shared__ __align__(128) uint8_t smem_raw[];
@@ -421,11 +422,11 @@ __global__ void __launch_bounds__(kWiThreads, 1)
     const int tid = threadIdx.x, half = tid >> 8, t = tid & 255;
     const int trk = blockIdx.z;
     const int n_wave = tracks[trk].n_wave;
-    const int f0 = frame_begin + blockIdx.x * kWiFrames; // this launch emits the hops of frames [frame_begin, frame_end)
+    const int f0 = frame_begin + blockIdx.x * frames_per_cta; // this launch emits the hops of frames [frame_begin, frame_end)
     const int f_need = min(frame_end, frames_reaching(n_wave, F)); // frames that reach an emitted sample (see istft_kernel)
     if (f0 >= f_need)
         return;
-    const int f1 = min(f_need, f0 + kWiFrames);
+    const int f1 = min(f_need, f0 + frames_per_cta);
     const bool last_cta = (f1 == F);
     const int f_first = max(f0 - 3, 0);
 
@@ -756,11 +757,16 @@ int launch_wiener_istft(const WienerArgs &w, const IstftTrack *d_tracks, int n_b
             return 0;
         }))
         return rc;
-    dim3 grid(ceil_div(frame_end - frame_begin, kWiFrames), 1, w.n_tracks);
+    static const int frames_per_cta = [] {
+        const char *e = getenv("UMX_WI_FRAMES"); // frames per CTA (+ 3 halo frames): tuning knob, default 32
+        const int v = e ? atoi(e) : kWiFrames;
+        return v >= 4 && v <= 1024 ? v : kWiFrames;
+    }();
+    dim3 grid(ceil_div(frame_end - frame_begin, frames_per_cta), 1, w.n_tracks);
     wiener_istft_kernel<<<grid, kWiThreads, smem, st>>>(w.spec, w.mask, w.mask_target_stride, w.mask_ld, w.maxabs, w.stats, w.F,
                                                         d_tracks, n_buf, w.stem_begin, w.stem_count, frame_begin, frame_end,
                                                         w.stat_windows, w.win_len,
-                                                        (w.psd_abs2 ? 1 : 0) | (w.reg_once ? 2 : 0) | (w.no_em ? 4 : 0));
+                                                        (w.psd_abs2 ? 1 : 0) | (w.reg_once ? 2 : 0) | (w.no_em ? 4 : 0), frames_per_cta);
     UMX_CUDA_OK(cudaGetLastError());
     return 0;
 }
