@@ -167,7 +167,7 @@ int umx_cuda_lstm_max_active_clusters(void);
  * "stft_pad" 1 = true reflect padding (torch.stft) instead of the symmetric edge copy of src/dsp.cpp:109-128,
  * "wiener_psd" 1 = PSD |y|^2 instead of (re+im)^2 (src/wiener.cpp:187-202), "wiener_reg" 1 = regulariser added once instead
  * of once per source (src/wiener.cpp:301-325), "wiener_win_len" N = EM statistics and max|X| per window of N frames
- * (upstream 300; at most 19 windows per segment) instead of per segment, "wiener_niter" 0 = no EM iteration (default 1 =
+ * (upstream 300; at most 19 windows per segment) instead of per segment, "wiener_niter" 0 = no EM iteration, 2..8 = more of them, unfused (default 1 =
  * src/wiener.hpp:14), "lstm_reset" 1 = LSTM state zeroed before every segment instead of streamed (src/lstm.cpp:160-161). */
 int umx_cuda_session_set_option(umx_cuda_session *s, const char *name, int value);
 

@@ -2,7 +2,7 @@
 imported here; PyTorch, float64): the behaviours the reference deviates from and that the session options
 "stft_pad", "wiener_psd", "wiener_reg", "wiener_win_len", "wiener_niter" switch back on.
     python tests/golden/make_golden_upstream.py
-Stored: torch.stft with reflect padding of golden_inputs.audio(); openunmix.filtering.wiener (1 iteration, and 0 iterations)
+Stored: torch.stft with reflect padding of golden_inputs.audio(); openunmix.filtering.wiener (0, 1 and 2 iterations)
 applied per window of UP_WIN frames exactly as openunmix.model.Separator.forward does (model.py:297-311)."""
 import os
 import sys
@@ -32,7 +32,7 @@ def main():
     mix, mags = gi.upstream_wiener_inputs()
     mix_t = torch.view_as_real(torch.from_numpy(mix.astype(np.complex128)).permute(1, 2, 0).contiguous())  # (F, B, C, 2)
     mags_t = torch.from_numpy(mags.astype(np.float64)).permute(2, 3, 1, 0).contiguous()                   # (F, B, C, sources)
-    for it in (0, 1):
+    for it in (0, 1, 2):
         y = torch.zeros(mix_t.shape + (4,), dtype=torch.float64)
         pos = 0
         while pos < gi.UP_F:  # model.py:301-311

@@ -27,9 +27,9 @@ def test_stft_reflect_padding_matches_torch_stft(umx):
     assert rel(umx.stft(gi.audio(), gi.N_BUF), g["stft_reflect"]) > 1e-3  # the default (reference) padding differs
 
 
-@pytest.mark.parametrize("niter", [0, 1])
+@pytest.mark.parametrize("niter", [0, 1, 2])
 def test_wiener_upstream_variant_matches_open_unmix(umx, niter):
-    """PSD |y|^2, regulariser once, per-window statistics and max|X| (three windows, the last one short), 0 or 1 EM iterations."""
+    """PSD |y|^2, regulariser once, per-window statistics and max|X| (three windows, the last one short), 0, 1 or 2 EM iterations."""
     g = np.load(gi.UP_GOLDEN)
     mix, mags = gi.upstream_wiener_inputs()
     got, _ = umx.wiener_filter(mix, mags, psd_abs2=True, reg_once=True, win_len=gi.UP_WIN, niter=niter)
@@ -42,6 +42,8 @@ OPTION_SETS = [
     {"wiener_reg": 1},
     {"wiener_win_len": 5},
     {"wiener_niter": 0},
+    {"wiener_niter": 2},
+    {"wiener_niter": 3, "wiener_win_len": 5, "wiener_psd": 1},
     {"lstm_reset": 1},
     {"stft_pad": 1, "wiener_psd": 1, "wiener_reg": 1, "wiener_win_len": 6, "lstm_reset": 1},  # "as upstream"
 ]
@@ -78,6 +80,6 @@ def test_option_errors(umx):
     with pytest.raises(umx.UmxCudaError, match="19 windows"):
         sess.set_option("wiener_win_len", -3)
     with pytest.raises(umx.UmxCudaError):
-        sess.set_option("wiener_niter", 2)
+        sess.set_option("wiener_niter", 9)
     with pytest.raises(umx.UmxCudaError):
         sess.set_option("no_such_option", 1)

@@ -87,3 +87,37 @@ def test_skipping_frames_beyond_the_chunk_changes_nothing(umx, hidden, n_buf):
     for x, y in zip(*outs):
         assert np.isfinite(x).all()
         assert np.array_equal(x, y)
+
+
+def test_stage_timeline_and_pinned_host_buffers(umx):
+    """umx_cuda_session_timeline (the raw stage intervals behind stage_ms) and umx_cuda_host_alloc (page-locked buffers for hosts
+    without the CUDA runtime): a demix through pinned buffers gives the bits of the pageable path, and the timeline of the call
+    holds every stage, ordered and inside the call."""
+    import ctypes as C
+
+    gm = umx.load_umx_model(synth.make_ggml(hidden=64, seed=81))
+    sess = umx.Session(gm, 2, 16384)
+    tracks = [synth.make_audio(n, 90 + i) for i, n in enumerate((40000, 9000))]
+    want = [w.transpose(0, 2, 1) for w in sess.demix(tracks)]  # (4, n, 2) like the interleaved output buffers
+    L = umx.lib()
+    ins, outs, raw = [], [], []
+    for t in tracks:
+        n = t.shape[1]
+        for nbytes, shape, dst in ((8 * n, (n, 2), ins), (32 * n, (4, n, 2), outs)):
+            p = C.c_void_p()
+            assert L.umx_cuda_host_alloc(nbytes, C.byref(p)) == 0 and p.value
+            raw.append(p)
+            dst.append(np.ctypeslib.as_array(C.cast(p, C.POINTER(C.c_float)), shape=(nbytes // 4,)).reshape(shape))
+        ins[-1][:] = t.T
+    sess.set_profiling(True)
+    sess.demix_into(ins, outs)
+    for o, w in zip(outs, want):
+        assert np.array_equal(o, w)
+    tl = sess.timeline()
+    names = {s for s, _, _ in tl}
+    assert {"stft", "gemm", "lstm", "wiener", "istft", "h2d", "d2h"} <= names
+    assert all(0.0 <= b <= e for _, b, e in tl)
+    assert abs(sess.stage_ms("gemm") - sum(e - b for s, b, e in tl if s == "gemm")) >= -1e-3  # union <= sum of intervals
+    assert sess.stage_ms("gemm") <= sum(e - b for s, b, e in tl if s == "gemm") + 1e-3
+    for p in raw:
+        L.umx_cuda_host_free(p)

@@ -139,7 +139,7 @@ def test_upstream_variants_match_open_unmix():
     assert rel(O.stft(gi.audio(), gi.N_BUF, reflect=True), g["stft_reflect"]) < 1e-5
     assert rel(O.stft(gi.audio(), gi.N_BUF, reflect=False), g["stft_reflect"]) > 1e-3  # the reference's padding IS different
     mix, mags = gi.upstream_wiener_inputs()
-    for it in (0, 1):
+    for it in (0, 1, 2):
         y = O.wiener_windows(mix, mags, gi.UP_WIN, psd_abs2=True, reg_once=True, niter=it)
         assert rel(y[..., :: gi.UP_BIN_STEP], g[f"wiener_win_niter{it}"]) < 2e-4, it
     # and each switch matters: the reference's own arithmetic does not reproduce upstream

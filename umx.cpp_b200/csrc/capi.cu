@@ -397,7 +397,10 @@ int umx_cuda_session_set_option(umx_cuda_session *s, const char *name, int value
     }
     else if (n == "wiener_niter")
     {
-        UMX_CHECK(value == 0 || value == 1, "wiener_niter must be 0 (no EM iteration) or 1 (one, as the reference)");
+        UMX_CHECK(value >= 0 && value <= 8, "wiener_niter must be in [0, 8] (1 = the reference)");
+        if (value > 1)
+            if (int rc = ensure_iter_buffers(s->s))
+                return rc;
         s->s->wiener_niter = value;
     }
     else if (n == "lstm_reset")
@@ -482,7 +485,7 @@ int umx_cuda_wiener_opts(float *mix, const float *mags, int F, float *out, int p
     if (require_device())
         return -1;
     UMX_CHECK(mix && mags && out && F >= 1, "umx_cuda_wiener: bad argument");
-    UMX_CHECK(niter == 0 || niter == 1, "umx_cuda_wiener_opts: niter must be 0 or 1");
+    UMX_CHECK(niter >= 0 && niter <= 8, "umx_cuda_wiener_opts: niter must be in [0, 8]");
     const int n_win = win_len > 0 ? (F + win_len - 1) / win_len : 1;
     UMX_CHECK(win_len >= 0 && n_win <= kWienerChunks, "umx_cuda_wiener_opts: at most 19 windows");
     const size_t e = (size_t)F * 2 * kBins;
@@ -532,11 +535,30 @@ int umx_cuda_wiener_opts(float *mix, const float *mags, int F, float *out, int p
     w.n_tracks = 1;
     w.stem_begin = 0;
     w.stem_count = 4;
-    if (int rc = launch_wiener(w, 0))
-        return rc;
+    // more than one EM iteration: every iteration but the last leaves its outputs divided by max_abs for the next one
+    DevBuf d_out2;
+    if (niter > 1 && d_out2.alloc(sizeof(float2) * e * 4))
+        return -1;
+    float2 *bufs[2] = {d_out.as<float2>(), niter > 1 ? d_out2.as<float2>() : nullptr};
+    const float2 *final_out = bufs[0];
+    for (int it = 0; it < std::max(niter, 1); ++it)
+    {
+        if (it > 0)
+        {
+            w.mask = nullptr;
+            w.y_in = bufs[(it - 1) & 1];
+            w.y_in_stem_stride = (long)e;
+            w.mix_out = nullptr; // the mixture was left divided by max_abs by the first iteration
+        }
+        w.out = bufs[it & 1];
+        w.out_normalized = it + 1 < niter;
+        final_out = w.out;
+        if (int rc = launch_wiener(w, 0))
+            return rc;
+    }
     for (int j = 0; j < 4; ++j)
     {
-        if (int rc = launch_to_ref_layout_c64(d_out.as<float2>() + j * e, d_ref.as<float2>() + j * e, F, 0))
+        if (int rc = launch_to_ref_layout_c64(final_out + j * e, d_ref.as<float2>() + j * e, F, 0))
             return rc;
     }
     UMX_CUDA_OK(cudaMemcpy(out, d_ref.p, sizeof(float2) * e * 4, cudaMemcpyDeviceToHost));

@@ -179,6 +179,11 @@ struct WienerArgs
     int win_len;   // > 0: statistics and max|X| per window of win_len frames (upstream wiener_win_len = 300), <= kWienerChunks
                    //      windows; 0: one window = the whole segment (the reference)
     int no_em;     // 1: no EM iteration (upstream niter = 0): y_j = mask_j X
+    // second and later EM iterations (upstream niter > 1; the reference's loop at src/wiener.cpp:175 with WIENER_ITERATIONS > 1):
+    // the source estimates are the previous iteration's outputs, still divided by max_abs, instead of mask / magnitude times mix
+    const float2 *y_in;   // [4][M][2][2049] or null
+    long y_in_stem_stride;
+    int out_normalized;   // 1: leave the outputs divided by max_abs (they feed another iteration)
 };
 constexpr int kWienerChunks = 19;
 int launch_wiener(const WienerArgs &a, cudaStream_t st);

@@ -253,10 +253,21 @@ int session_create(Model *m, int max_tracks, int n_buf, Session **out)
 // The post stage of a segment (filter + inverse STFT + overlap-add, finalize, copy-out) is cut into kPostParts runs of frames, so
 // the first finished output ranges of a segment are on their way to the host while the rest of it is still computed: the tail
 // of a host-buffer call after the last kernel is one part's copy, not a whole segment's.
-static int post_part_frame(int F, int q)
+static int post_part_frame(const Session *s, int q)
 {
-    const int per = ((F + kPostParts - 1) / kPostParts + 31) / 32 * 32; // whole CTAs of the fused kernel
-    return std::min(F, q * per);
+    if (s->wiener_niter > 1) // more than one EM iteration runs unfused, whole segments at a time: everything in the last part
+        return q < kPostParts ? 0 : s->F;
+    const int per = ((s->F + kPostParts - 1) / kPostParts + 31) / 32 * 32; // whole CTAs of the fused kernel
+    return std::min(s->F, q * per);
+}
+
+int ensure_iter_buffers(Session *s)
+{
+    UMX_CUDA_OK(cudaSetDevice(s->device));
+    for (auto &p : s->stems_iter)
+        if (!p && salloc(s, &p, (size_t)4 * s->Mcap * 2 * kBins))
+            return -1;
+    return 0;
 }
 
 int ensure_desc_capacity(Session *s, int segs)
@@ -652,13 +663,52 @@ static WienerArgs post_args(Session *s, int seg, int n_tracks, const NetView &v)
 }
 static int run_post_stats(Session *s, int seg, int n_tracks, const NetView &v, cudaStream_t st)
 {
+    if (s->wiener_niter > 1)
+        return 0; // run_post_iterated does everything, in the last part
     StageScope sc(s, "wiener", st);
     s->launches += 2;
     return launch_wiener(post_args(s, seg, n_tracks, v), st);
 }
+// More than one EM iteration (option "wiener_niter" > 1; the reference's loop at src/wiener.cpp:175 with WIENER_ITERATIONS > 1):
+// every iteration needs all sources' estimates of the one before, so the filtered spectrograms are materialised
+// (Session::stems_iter) and the last iteration feeds the stand-alone inverse STFT kernel.
+static int run_post_iterated(Session *s, int seg, int n_tracks, const NetView &v, cudaStream_t st)
+{
+    UMX_CHECK(s->stems_iter[0] && s->stems_iter[1], "wiener_niter > 1: iteration buffers are not allocated");
+    const long stride = s->Mcap * 2 * kBins;
+    for (int it = 0; it < s->wiener_niter; ++it)
+    {
+        StageScope sc(s, "wiener", st);
+        WienerArgs w = post_args(s, seg, n_tracks, v);
+        if (it > 0)
+        {
+            w.mask = nullptr;
+            w.y_in = s->stems_iter[(it - 1) & 1];
+            w.y_in_stem_stride = stride;
+        }
+        w.out = s->stems_iter[it & 1];
+        w.out_stem_stride = stride;
+        const bool last = it + 1 == s->wiener_niter;
+        w.out_normalized = !last;
+        if (!last)
+        { // every iteration but the last needs all four sources' outputs
+            w.stem_begin = 0;
+            w.stem_count = kTargets;
+        }
+        s->launches += 3;
+        if (int rc = launch_wiener(w, st))
+            return rc;
+    }
+    StageScope sc(s, "istft", st);
+    s->launches++;
+    return launch_istft(s->stems_iter[(s->wiener_niter - 1) & 1], stride, s->tp_nt, s->d_istft + (size_t)seg * s->T, n_tracks, s->n_buf, st,
+                        s->tp_t0);
+}
 static int run_post_part(Session *s, int seg, int n_tracks, const NetView &v, cudaStream_t st, int part)
 {
-    const int fa = post_part_frame(s->F, part), fb = part + 1 == kPostParts ? s->F : post_part_frame(s->F, part + 1);
+    if (s->wiener_niter > 1)
+        return part + 1 == kPostParts ? run_post_iterated(s, seg, n_tracks, v, st) : 0;
+    const int fa = post_part_frame(s, part), fb = part + 1 == kPostParts ? s->F : post_part_frame(s, part + 1);
     if (fa >= fb)
         return 0;
     StageScope sc(s, "istft", st);
@@ -996,12 +1046,12 @@ int session_demix_device(Session *s, const float *const *d_audio, const int64_t 
             // part q of the segment's post stage emits the chunk samples below 1024 * (its last frame + 1) - 2048
             long pb[kPostParts], pe[kPostParts];
             long b = sg == 0 ? 0 : final_end(i, sg - 1);
-            bool direct = s->direct_final && ex_hi > ex_lo;
+            bool direct = s->direct_final && ex_hi > ex_lo && s->wiener_niter <= 1; // (the stand-alone inverse STFT only accumulates)
             for (int q = 0; q < kPostParts; ++q)
             {
                 long e = final_end(i, sg);
                 if (q + 1 < kPostParts)
-                    e = std::min(e, std::max(b, off + (long)kHop * post_part_frame(s->F, q + 1) - kPad - shift_offset));
+                    e = std::min(e, std::max(b, off + (long)kHop * post_part_frame(s, q + 1) - kPad - shift_offset));
                 pb[q] = b;
                 pe[q] = e;
                 if (b < x_lo && e > x_hi) // finalize_kernel takes one range per part: it cannot skip a hole in the middle

@@ -98,7 +98,8 @@ struct Session
     int wiener_psd_abs2 = 0;   // "wiener_psd" 1: v = mean_ch |y|^2 instead of ((re+im)_L^2 + (re+im)_R^2)/2 (src/wiener.cpp:187-202)
     int wiener_reg_once = 0;   // "wiener_reg" 1: sqrt(eps) I added once instead of once per source (src/wiener.cpp:301-325)
     int wiener_win_len = 0;    // "wiener_win_len" N: EM statistics per window of N frames (upstream 300) instead of per segment
-    int wiener_niter = 1;      // "wiener_niter" 0: no EM iteration (y = mask X); 1: one iteration (src/wiener.hpp:14)
+    int wiener_niter = 1;      // "wiener_niter" 0: no EM iteration (y = mask X); 1: one iteration (src/wiener.hpp:14); 2..8: more (unfused path)
+    float2 *stems_iter[2] = {}; // [4][Mcap][2][2049] each, allocated when wiener_niter > 1: estimates between EM iterations
     int direct_final = 1;      // "direct_final" 1 (default): samples no other segment covers are written finalised by the inverse STFT itself
     int lstm_reset = 0;        // "lstm_reset" 1: h/c zeroed before every segment (upstream) instead of streamed (src/lstm.cpp:160-161)
     // measurement
@@ -142,6 +143,7 @@ void session_begin_profile(Session *s);
 int session_end_profile(Session *s);
 int session_resolve_profile(Session *s); // waits for the most recent call and fills stage_ms
 int ensure_desc_capacity(Session *s, int segs);
+int ensure_iter_buffers(Session *s); // the two stem-spectrogram buffers EM iterations beyond the first need
 // tp.cu: NCCL is loaded with dlopen on first use, so the library has no link-time dependency on it
 int tp_unique_id(void *id128);
 int tp_init(Session *s, const void *id128, int rank, int world);

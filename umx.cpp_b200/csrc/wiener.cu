@@ -54,8 +54,8 @@ __global__ void __launch_bounds__(256) wiener_reduce_kernel(const WienerArgs a)
 #pragma unroll
             for (int j = 0; j < 4; ++j)
             {
-                const float2 yL = initial_estimate(in[u].mL[j], in[u].XL, ma, a.mask_is_mag);
-                const float2 yR = initial_estimate(in[u].mR[j], in[u].XR, ma, a.mask_is_mag);
+                float2 yL, yR;
+                wiener_estimate(a, in[u], (long)trk * a.F + f0 + u, b, j, ma, yL, yR);
                 acc[5 * j + 0] += yL.x * yL.x + yL.y * yL.y;
                 acc[5 * j + 1] += yR.x * yR.x + yR.y * yR.y;
                 acc[5 * j + 2] += yL.x * yR.x + yL.y * yR.y; // yL * conj(yR)
@@ -131,7 +131,9 @@ __global__ void __launch_bounds__(256) wiener_apply_kernel(const WienerArgs a)
             }
             const long row = (long)trk * a.F + f;
             WienerCommon c;
-            wiener_common(in[u], R, inv_ma, a.mask_is_mag, c, a.psd_abs2, a.reg_once);
+            wiener_common_est(in[u].XL, in[u].XR, R, inv_ma, c, a.psd_abs2, a.reg_once,
+                              [&](int j, float2 &yL, float2 &yR) { wiener_estimate(a, in[u], row, b, j, inv_ma, yL, yR); });
+            const float ma_out = a.out_normalized ? 1.0f : ma; // an iteration that feeds another leaves its outputs divided by max_abs
 #pragma unroll
             for (int j = 0; j < 4; ++j)
                 if (j >= a.stem_begin && j < a.stem_begin + a.stem_count) // target-parallel ranks only write their own stems
@@ -143,7 +145,7 @@ __global__ void __launch_bounds__(256) wiener_apply_kernel(const WienerArgs a)
                         y1 = initial_estimate(in[u].mR[j], in[u].XR, 1.f, a.mask_is_mag);
                     }
                     else
-                        wiener_source(c, R, j, ma, y0, y1);
+                        wiener_source(c, R, j, ma_out, y0, y1);
                     float2 *o = a.out + (long)j * a.out_stem_stride + (row * 2) * kBins + b;
                     o[0] = y0;
                     o[kBins] = y1;

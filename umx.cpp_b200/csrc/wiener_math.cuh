@@ -56,8 +56,8 @@ __device__ __forceinline__ void wiener_load(const float2 *__restrict__ spec, con
     for (int j = 0; j < 4; ++j)
     {
         const float *mk = mask + (long)j * mask_target_stride + row * mask_ld;
-        w.mL[j] = __ldg(mk + b);
-        w.mR[j] = __ldg(mk + kBins + b);
+        w.mL[j] = mask ? __ldg(mk + b) : 0.f; // (no masks in the second and later EM iterations: WienerArgs::y_in)
+        w.mR[j] = mask ? __ldg(mk + kBins + b) : 0.f;
     }
 }
 __device__ __forceinline__ void wiener_load(const WienerArgs &a, long row, int b, WienerIn &w)
@@ -72,21 +72,23 @@ struct WienerCommon
     float v[4];    // v_j = ((re+im)_L^2 + (re+im)_R^2) / 2 of the initial estimate (wiener.cpp:187-202, sic)
     float2 u0, u1; // Cxx^-1 (x0, x1)
 };
-// R: the four sources' normalised spatial covariances of this bin, R[4j .. 4j+3] = R00, R11, Re R01, Im R01
-__device__ __forceinline__ void wiener_common(const WienerIn &in, const float (&R)[16], float inv_ma, int is_mag, WienerCommon &c,
-                                              int psd_abs2 = 0, int reg_once = 0)
+// R: the four sources' normalised spatial covariances of this bin, R[4j .. 4j+3] = R00, R11, Re R01, Im R01.
+// est(j, yL, yR): the current estimate of source j (both channels), divided by max_abs.
+template <class Est>
+__device__ __forceinline__ void wiener_common_est(float2 XL, float2 XR, const float (&R)[16], float inv_ma, WienerCommon &c,
+                                                  int psd_abs2, int reg_once, Est est)
 {
     const float reg = sqrtf(kWienerEps); // wiener.cpp:155-163
-    c.x0 = make_float2(in.XL.x * inv_ma, in.XL.y * inv_ma);
-    c.x1 = make_float2(in.XR.x * inv_ma, in.XR.y * inv_ma);
+    c.x0 = make_float2(XL.x * inv_ma, XL.y * inv_ma);
+    c.x1 = make_float2(XR.x * inv_ma, XR.y * inv_ma);
     // Cxx = sum_j (sqrt(eps) I + v_j R_j): the reference adds the regulariser once PER SOURCE (wiener.cpp:301-325); upstream once
     const float reg_j = reg_once ? 0.f : reg;
     float c00 = reg_once ? reg : 0.f, c11 = c00, c01r = 0.f, c01i = 0.f;
 #pragma unroll
     for (int j = 0; j < 4; ++j)
     {
-        const float2 yL = initial_estimate(in.mL[j], in.XL, inv_ma, is_mag);
-        const float2 yR = initial_estimate(in.mR[j], in.XR, inv_ma, is_mag);
+        float2 yL, yR;
+        est(j, yL, yR);
         c.v[j] = wiener_psd(yL, yR, psd_abs2);
         c00 += reg_j + c.v[j] * R[4 * j + 0];
         c11 += reg_j + c.v[j] * R[4 * j + 1];
@@ -101,6 +103,15 @@ __device__ __forceinline__ void wiener_common(const WienerIn &in, const float (&
     c.u0 = make_float2(inv_det * (c11 * c.x0.x - (c01r * c.x1.x - c01i * c.x1.y)), inv_det * (c11 * c.x0.y - (c01r * c.x1.y + c01i * c.x1.x)));
     c.u1 = make_float2(inv_det * (c00 * c.x1.x - (c01r * c.x0.x + c01i * c.x0.y)), inv_det * (c00 * c.x1.y - (c01r * c.x0.y - c01i * c.x0.x)));
 }
+// first iteration: the estimates are mask (or magnitude with the mixture's phase) times the mixture
+__device__ __forceinline__ void wiener_common(const WienerIn &in, const float (&R)[16], float inv_ma, int is_mag, WienerCommon &c,
+                                              int psd_abs2 = 0, int reg_once = 0)
+{
+    wiener_common_est(in.XL, in.XR, R, inv_ma, c, psd_abs2, reg_once, [&](int j, float2 &yL, float2 &yR) {
+        yL = initial_estimate(in.mL[j], in.XL, inv_ma, is_mag);
+        yR = initial_estimate(in.mR[j], in.XR, inv_ma, is_mag);
+    });
+}
 // y_j = v_j R_j u, times max_abs (wiener.cpp:335-422) for source j; R10 = conj(R01)
 __device__ __forceinline__ void wiener_source(const WienerCommon &c, const float (&R)[16], int j, float ma, float2 &y0, float2 &y1)
 {
@@ -110,6 +121,23 @@ __device__ __forceinline__ void wiener_source(const WienerCommon &c, const float
     y0.y = g * (r00 * c.u0.y + (r01r * c.u1.y + r01i * c.u1.x));
     y1.x = g * ((r01r * c.u0.x + r01i * c.u0.y) + r11 * c.u1.x);
     y1.y = g * ((r01r * c.u0.y - r01i * c.u0.x) + r11 * c.u1.y);
+}
+
+// the current estimate of source j at (row, bin b), divided by max_abs: the previous iteration's output, or the initial estimate
+__device__ __forceinline__ void wiener_estimate(const WienerArgs &a, const WienerIn &in, long row, int b, int j, float inv_ma, float2 &yL,
+                                                float2 &yR)
+{
+    if (a.y_in)
+    {
+        const float2 *p = a.y_in + (long)j * a.y_in_stem_stride + (row * 2) * kBins + b;
+        yL = __ldg(p);
+        yR = __ldg(p + kBins);
+    }
+    else
+    {
+        yL = initial_estimate(in.mL[j], in.XL, inv_ma, a.mask_is_mag);
+        yR = initial_estimate(in.mR[j], in.XR, inv_ma, a.mask_is_mag);
+    }
 }
 
 } // namespace umx
