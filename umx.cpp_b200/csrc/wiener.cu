@@ -23,6 +23,9 @@ constexpr int kWienerApplyFrames = 16;
 
 constexpr int kWienerUnroll = 4; // frames whose loads are in flight together (the kernels are latency-bound otherwise)
 
+// YIN: the estimates come from WienerArgs::y_in (second and later EM iterations); compile-time so the first-iteration path, the
+// one every segment takes, keeps its prefetched loads
+template <bool YIN>
 __global__ void __launch_bounds__(256) wiener_reduce_kernel(const WienerArgs a)
 {
     const int b = blockIdx.x * 256 + threadIdx.x;
@@ -55,7 +58,13 @@ __global__ void __launch_bounds__(256) wiener_reduce_kernel(const WienerArgs a)
             for (int j = 0; j < 4; ++j)
             {
                 float2 yL, yR;
-                wiener_estimate(a, in[u], (long)trk * a.F + f0 + u, b, j, ma, yL, yR);
+                if (YIN)
+                    wiener_estimate(a, in[u], (long)trk * a.F + f0 + u, b, j, ma, yL, yR);
+                else
+                {
+                    yL = initial_estimate(in[u].mL[j], in[u].XL, ma, a.mask_is_mag);
+                    yR = initial_estimate(in[u].mR[j], in[u].XR, ma, a.mask_is_mag);
+                }
                 acc[5 * j + 0] += yL.x * yL.x + yL.y * yL.y;
                 acc[5 * j + 1] += yR.x * yR.x + yR.y * yR.y;
                 acc[5 * j + 2] += yL.x * yR.x + yL.y * yR.y; // yL * conj(yR)
@@ -166,7 +175,11 @@ int launch_wiener(const WienerArgs &a, cudaStream_t st)
     UMX_CHECK(n_win <= kWienerChunks && n_win <= a.stat_windows, "wiener: at most 19 windows per segment (win_len too small for this window length)");
     if (!a.no_em)
     {
-        wiener_reduce_kernel<<<dim3(tiles, a.win_len > 0 ? n_win : kWienerChunks, a.n_tracks), 256, 0, st>>>(a);
+        const dim3 grid(tiles, a.win_len > 0 ? n_win : kWienerChunks, a.n_tracks);
+        if (a.y_in)
+            wiener_reduce_kernel<true><<<grid, 256, 0, st>>>(a);
+        else
+            wiener_reduce_kernel<false><<<grid, 256, 0, st>>>(a);
         UMX_CUDA_OK(cudaGetLastError());
         wiener_finalize_kernel<<<dim3(tiles, a.n_tracks, n_win), 256, 0, st>>>(a);
         UMX_CUDA_OK(cudaGetLastError());
