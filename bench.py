@@ -183,6 +183,10 @@ def run_reference(args, rank):
 
 
 def main():
+    # a run that stops making progress prints where it stands and exits instead of hanging its caller
+    import faulthandler
+
+    faulthandler.dump_traceback_later(int(os.environ.get("UMX_BENCH_WATCHDOG_S", "1500")), exit=True)
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=3)
@@ -192,7 +196,7 @@ def main():
     ap.add_argument("--track-seconds", type=float, default=180.0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--gemm-terms", type=int, default=0)
-    ap.add_argument("--gemm-impl", type=int, default=-1, help="session option: 0 = tcgen05 CTA pairs (default), 3 = single-CTA tiles")
+    ap.add_argument("--gemm-impl", type=int, default=-1, help="session option: 0 = CTA pairs in order, single-CTA tiles in the wavefront (default), 2 = pairs always, 3 = single-CTA always")
     ap.add_argument("--pipeline", type=int, default=-1, help="session option: 0 = every kernel in order on one stream, 3 (default) = segment wavefront")
     ap.add_argument("--lane-targets", type=int, default=0, help="session option: targets per stream of the wavefront (1, 2, 4)")
     ap.add_argument("--timeline", default="", help="write the stage intervals of the last timed step to this file (JSON)")

@@ -154,8 +154,9 @@ int umx_cuda_session_set_stream(umx_cuda_session *s, void *stream);
 /* How many 8-CTA clusters of the recurrence kernel the current device can hold at once (diagnostic). */
 int umx_cuda_lstm_max_active_clusters(void);
 /* Tuning knobs (documented in DESIGN.md): "gemm_terms" 1..3 fp16 split terms per tensor-core GEMM,
- * "gemm_impl" 0 = tcgen05 with CTA pairs (cta_group::2, 256 x 256 tiles), 1 = SIMT fp32 validation kernel, 3 = tcgen05 with
- * single-CTA 128 x 256 tiles (identical results to 0), "lstm_impl" 0 = cluster kernel, 1 = simple,
+ * "gemm_impl" 0 = tcgen05 (CTA pairs, cta_group::2 on 256 x 256 tiles, in the in-order schedule; single-CTA 128 x 256 tiles in
+ * the segment wavefront), 1 = SIMT fp32 validation kernel, 2 = CTA pairs always, 3 = single-CTA tiles always (0, 2 and 3 give
+ * identical results), "lstm_impl" 0 = cluster kernel, 1 = simple,
  * "pipeline" 0 = every kernel in order on one stream, 3 (default) = segment wavefront: LSTM layer l of segment s+1 runs beside
  * layer l+1 of segment s (the h/c carry of src/lstm.cpp:160-161 is per layer), one stream per (layer, target group) with
  * "lane_targets" = 1, 2 or 4 targets per group (0, the default: 1 up to 16 tracks, else 4); results are identical,

@@ -144,7 +144,7 @@ def test_wiener_zero_mix_and_loud_mix(umx):
 
 
 # ---- network / inference ------------------------------------------------------------------------------
-PAIRS = [3]  # gemm_impl: 0 = tcgen05 CTA pairs (default), 3 = single-CTA tiles
+PAIRS = [3]  # gemm_impl: 0 = tcgen05 (CTA pairs in order, single-CTA tiles in the wavefront), 2 = pairs always, 3 = single-CTA always
 
 
 @pytest.mark.parametrize("gemm_impl", [1, 0] + PAIRS)
@@ -236,8 +236,9 @@ def test_demix_direct_final_identical(umx, hidden):
 
 @pytest.mark.parametrize("terms", [3, 2, 1])
 def test_gemm_cta_pairs_identical_to_single_cta(umx, terms):
-    """gemm_impl 0 (tcgen05.mma.cta_group::2 on 256 x 256 tiles, B split across the pair; the default) accumulates every output element over
-    the same k-blocks in the same order as the single-CTA kernel (gemm_impl 3): identical bits, at the UMX-L hidden size, ragged row counts."""
+    """CTA pairs (tcgen05.mma.cta_group::2 on 256 x 256 tiles, B split across the pair; what gemm_impl 0 uses in the in-order schedule)
+    accumulate every output element over the same k-blocks in the same order as the single-CTA kernel (gemm_impl 3): identical bits,
+    at the UMX-L hidden size, ragged row counts."""
     n_buf = 16384
     gm = umx.load_umx_model(synth.make_ggml(hidden=1024, seed=80))
     tracks = [synth.make_audio(n, 60 + i) for i, n in enumerate((40000, 9000, 23000, 30000, 12000))]
@@ -245,8 +246,15 @@ def test_gemm_cta_pairs_identical_to_single_cta(umx, terms):
     for sess, impl in ((a, 3), (b, 0)):
         sess.set_option("gemm_impl", impl)
         sess.set_option("gemm_terms", terms)
-    for g, w in zip(b.demix(tracks), a.demix(tracks)):
+        sess.set_option("pipeline", 0)
+    want = a.demix(tracks)
+    for g, w in zip(b.demix(tracks), want):
         assert np.array_equal(g, w)
+    if os.environ.get("UMX_TEST_PAIRS_WAVEFRONT") == "1":  # pairs drawing from the wavefront's tile queues (opt-in: gemm_impl 2)
+        b.set_option("gemm_impl", 2)
+        b.set_option("pipeline", 3)
+        for g, w in zip(b.demix(tracks), want):
+            assert np.array_equal(g, w)
 
 
 def test_demix_shift_offsets_and_trim(umx, small):

@@ -345,7 +345,7 @@ int umx_cuda_session_set_option(umx_cuda_session *s, const char *name, int value
     }
     else if (n == "gemm_impl")
     {
-        UMX_CHECK(value >= 0 && value <= 3, "gemm_impl must be 0 (tcgen05 CTA pairs), 1 (SIMT validation), 2 (same as 0) or 3 (tcgen05 single-CTA tiles)");
+        UMX_CHECK(value >= 0 && value <= 3, "gemm_impl must be 0 (tcgen05: CTA pairs in order, single-CTA tiles in the wavefront), 1 (SIMT validation), 2 (CTA pairs always) or 3 (single-CTA tiles always)");
         s->s->gemm_impl = value;
     }
     else if (n == "pipeline")

@@ -352,10 +352,12 @@ static int run_gemm(Session *s, const GemmBatch &b, cudaStream_t st, int terms =
     s->launches++;
     if (s->gemm_impl == 1)
         return launch_gemm_simt(b, st);
-    // CTA pairs (256 x 256 tiles, B split across the pair) for every launch: measured faster than single-CTA tiles even for fc3,
-    // whose 17th column tile holds 2 of 256 columns (in-order GEMM time per bench step 105.4 ms with pairs everywhere, 107.1 ms
-    // with single-CTA tiles for fc3 only, 111.4 ms without pairs)
-    const bool pair = s->gemm_impl != 3;
+    // CTA pairs (256 x 256 tiles, B split across the pair) when the GEMM has the GPU to itself — the in-order schedule, where
+    // they are measured faster even for fc3 (in-order GEMM time per bench step 105.4 ms with pairs, 111.4 ms without).  In the
+    // segment wavefront (GEMMs of several lanes and the recurrence clusters of 8 share the SMs; the launch passes a tile queue)
+    // single-CTA tiles pack better: 226.5 ms per bench step against 229 ms with pairs, which need both SMs of a TPC at once.
+    // "gemm_impl" 2 forces pairs everywhere, 3 single-CTA tiles everywhere.
+    const bool pair = s->gemm_impl == 2 || (s->gemm_impl == 0 && tile_counter == nullptr);
     return launch_gemm_tc(b, terms ? terms : s->gemm_terms, st, tile_counter, pair);
 }
 
