@@ -81,6 +81,15 @@ int umx_cuda_infer_segment(umx_cuda_session *s, const float *audio, int n, float
  * audio[i]: float[n_samples[i]][2]; out[i]: 4 x float[n_samples[i]][2]. Host memory (pinned is faster). */
 int umx_cuda_demix(umx_cuda_session *s, const float *const *audio, const int64_t *n_samples, int n_tracks,
                    int shift_offset, float *const *out);
+/* The same call, enqueued only: it returns once the work is queued and hands back a ticket; out[] holds the stems after
+ * umx_cuda_session_wait(s, ticket) (ticket 0: every call enqueued so far), and audio[] / out[] must stay valid (and should be
+ * page-locked) until then.  Up to two calls are in flight per session — a third call first waits for the oldest — so the
+ * inputs of call k+1 go up, and the last output ranges of call k come down, while the other call's kernels run: a host feeding
+ * a queue of batches (one shift_inference after another, umx.cpp:99-147) is not idle between them.  Give consecutive calls
+ * different out[] buffers.  Every other entry point of the session first waits for the calls in flight. */
+int umx_cuda_demix_async(umx_cuda_session *s, const float *const *audio, const int64_t *n_samples, int n_tracks,
+                         int shift_offset, float *const *out, int64_t *ticket);
+int umx_cuda_session_wait(umx_cuda_session *s, int64_t ticket);
 /* Same with inputs/outputs already resident in device memory (no host<->device copies). */
 int umx_cuda_demix_device(umx_cuda_session *s, const float *const *d_audio, const int64_t *n_samples,
                           int n_tracks, int shift_offset, float *const *d_out);

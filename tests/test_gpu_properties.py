@@ -121,3 +121,34 @@ def test_stage_timeline_and_pinned_host_buffers(umx):
     assert sess.stage_ms("gemm") <= sum(e - b for s, b, e in tl if s == "gemm") + 1e-3
     for p in raw:
         L.umx_cuda_host_free(p)
+
+
+def test_demix_async_two_calls_in_flight(umx):
+    """umx_cuda_demix_async / umx_cuda_session_wait: three different batches enqueued back to back (two in flight at a time, the
+    third call waits for the first) give, each in its own output buffers, the bits of umx_cuda_demix one call at a time; the
+    synchronous entry points in between wait for what is in flight."""
+    gm = umx.load_umx_model(synth.make_ggml(hidden=64, seed=82))
+    sess = umx.Session(gm, 3, 16384)
+    batches = [[synth.make_audio(n, 100 + 10 * b + i) for i, n in enumerate(lens)]
+               for b, lens in enumerate(((40000, 9000, 23000), (12000, 52000), (30000, 30000, 1)))]
+    want = [[w.transpose(0, 2, 1) for w in sess.demix(tr)] for tr in batches]
+    for pipeline in (3, 0):
+        sess.set_option("pipeline", pipeline)
+        ins = [[np.ascontiguousarray(t.T) for t in tr] for tr in batches]
+        outs = [[np.full((4, t.shape[1], 2), np.nan, np.float32) for t in tr] for tr in batches]
+        tickets = [sess.demix_async(i, o) for i, o in zip(ins, outs)]
+        assert tickets == sorted(tickets) and len(set(tickets)) == 3
+        sess.wait(tickets[1])
+        for o, w in zip(outs[0] + outs[1], want[0] + want[1]):
+            assert np.array_equal(o, w)
+        sess.wait()
+        for o, w in zip(outs[2], want[2]):
+            assert np.array_equal(o, w)
+        # a synchronous call right behind an enqueued one
+        outs0 = [np.full_like(o, np.nan) for o in outs[0]]
+        sess.demix_async(ins[0], outs0)
+        again = [w.transpose(0, 2, 1) for w in sess.demix(batches[1])]
+        for o, w in zip(again, want[1]):
+            assert np.array_equal(o, w)
+        for o, w in zip(outs0, want[0]):
+            assert np.array_equal(o, w)

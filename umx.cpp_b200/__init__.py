@@ -38,6 +38,7 @@ EXPORTS = [
     "umx_cuda_model_create_from_file", "umx_cuda_model_destroy", "umx_cuda_model_hidden_size",
     "umx_cuda_model_device", "umx_cuda_model_tensor", "umx_cuda_session_create", "umx_cuda_session_destroy",
     "umx_cuda_session_reset", "umx_cuda_session_get_state", "umx_cuda_infer_segment", "umx_cuda_demix",
+    "umx_cuda_demix_async", "umx_cuda_session_wait",
     "umx_cuda_demix_device", "umx_cuda_host_alloc", "umx_cuda_host_free", "umx_cuda_segment_plan", "umx_cuda_stft", "umx_cuda_istft", "umx_cuda_lstm_forward",
     "umx_cuda_wiener", "umx_cuda_wiener_opts", "umx_cuda_stft_opts", "umx_cuda_target_mags", "umx_cuda_session_set_profiling", "umx_cuda_session_stage_ms",
     "umx_cuda_session_launches", "umx_cuda_session_timeline", "umx_cuda_session_set_option", "umx_cuda_session_set_stream",
@@ -79,6 +80,8 @@ def lib():
     l.umx_cuda_infer_segment.argtypes = [vp, vp, ip, vp]
     l.umx_cuda_demix.argtypes = [vp, vp, vp, ip, ip, vp]
     l.umx_cuda_demix_device.argtypes = [vp, vp, vp, ip, ip, vp]
+    l.umx_cuda_demix_async.argtypes = [vp, vp, vp, ip, ip, vp, vp]
+    l.umx_cuda_session_wait.argtypes = [vp, C.c_int64]
     l.umx_cuda_host_alloc.argtypes = [C.c_size_t, fpp]
     l.umx_cuda_host_free.argtypes = [vp]
     l.umx_cuda_host_free.restype = None
@@ -265,6 +268,21 @@ class Session:
         pout = (C.c_void_p * k)(*[o.ctypes.data for o in outs])
         ns = (C.c_int64 * k)(*[a.shape[0] for a in ins])
         _check(self._lib.umx_cuda_demix(self._h, pin, ns, k, shift_offset, pout), "umx_cuda_demix")
+
+    def demix_async(self, ins, outs, shift_offset: int = DEFAULT_SHIFT_OFFSET) -> int:
+        """demix_into that only enqueues the work: returns a ticket for wait().  ins / outs must stay alive (and should be
+        pinned) until then; up to two calls are in flight, so give consecutive calls different outs."""
+        k = len(ins)
+        pin = (C.c_void_p * k)(*[a.ctypes.data for a in ins])
+        pout = (C.c_void_p * k)(*[o.ctypes.data for o in outs])
+        ns = (C.c_int64 * k)(*[a.shape[0] for a in ins])
+        ticket = C.c_int64(0)
+        _check(self._lib.umx_cuda_demix_async(self._h, pin, ns, k, shift_offset, pout, C.byref(ticket)), "umx_cuda_demix_async")
+        return ticket.value
+
+    def wait(self, ticket: int = 0):
+        """Blocks until the call with this ticket (0: every call enqueued so far) has delivered its outputs."""
+        _check(self._lib.umx_cuda_session_wait(self._h, ticket), "umx_cuda_session_wait")
 
     def demix_device(self, in_ptrs, n_samples, out_ptrs, shift_offset: int = DEFAULT_SHIFT_OFFSET):
         """Device pointers (ints) of interleaved tracks / (4, n, 2) outputs."""

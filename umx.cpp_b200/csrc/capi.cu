@@ -217,10 +217,29 @@ int umx_cuda_demix(umx_cuda_session *s, const float *const *audio, const int64_t
     return session_demix_host(s->s, audio, n_samples, n_tracks, shift_offset, out);
 }
 
+int umx_cuda_demix_async(umx_cuda_session *s, const float *const *audio, const int64_t *n_samples, int n_tracks,
+                         int shift_offset, float *const *out, int64_t *ticket)
+{
+    UMX_CHECK(s && audio && n_samples && out && ticket, "umx_cuda_demix_async: null argument");
+    long t = 0;
+    if (int rc = session_demix_host(s->s, audio, n_samples, n_tracks, shift_offset, out, &t))
+        return rc;
+    *ticket = t;
+    return 0;
+}
+
+int umx_cuda_session_wait(umx_cuda_session *s, int64_t ticket)
+{
+    UMX_CHECK(s, "umx_cuda_session_wait: null argument");
+    return session_wait(s->s, (long)ticket);
+}
+
 int umx_cuda_demix_device(umx_cuda_session *s, const float *const *d_audio, const int64_t *n_samples, int n_tracks,
                           int shift_offset, float *const *d_out)
 {
     UMX_CHECK(s && d_audio && n_samples && d_out, "umx_cuda_demix_device: null argument");
+    if (int rc = session_wait(s->s, 0))
+        return rc;
     session_begin_profile(s->s);
     if (int rc = session_demix_device(s->s, d_audio, n_samples, n_tracks, shift_offset, d_out))
         return rc;
@@ -337,6 +356,8 @@ long umx_cuda_session_launches(umx_cuda_session *s) { return s ? s->s->launches 
 int umx_cuda_session_set_option(umx_cuda_session *s, const char *name, int value)
 {
     UMX_CHECK(s && name, "umx_cuda_session_set_option: null argument");
+    if (int rc = session_wait(s->s, 0)) // options change between calls, not under one
+        return rc;
     const std::string n(name);
     if (n == "gemm_terms")
     {

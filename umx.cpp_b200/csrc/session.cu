@@ -188,7 +188,10 @@ int session_create(Model *m, int max_tracks, int n_buf, Session **out)
               cudaStreamCreateWithPriority(&s->st_comm, cudaStreamNonBlocking, prio_hi) == cudaSuccess &&
               cudaStreamCreateWithFlags(&s->st_probe[0], cudaStreamNonBlocking) == cudaSuccess &&
               cudaStreamCreateWithFlags(&s->st_probe[1], cudaStreamNonBlocking) == cudaSuccess &&
-              cudaEventCreateWithFlags(&s->desc_copied, cudaEventDisableTiming) == cudaSuccess;
+              cudaEventCreateWithFlags(&s->desc_copied, cudaEventDisableTiming) == cudaSuccess &&
+              cudaEventCreateWithFlags(&s->spare.desc_copied, cudaEventDisableTiming) == cudaSuccess &&
+              cudaEventCreateWithFlags(&s->call_done[0], cudaEventDisableTiming) == cudaSuccess &&
+              cudaEventCreateWithFlags(&s->call_done[1], cudaEventDisableTiming) == cudaSuccess;
     for (int l = 0; ok && l < 3; ++l)
         for (int g = 0; ok && g < kTargets; ++g)
             ok = cudaStreamCreateWithPriority(&s->st_lane[l][g], cudaStreamNonBlocking, prio(4 - l)) == cudaSuccess;
@@ -244,6 +247,8 @@ int session_create(Model *m, int max_tracks, int n_buf, Session **out)
     s->acc_cap.assign(s->T, 0);
     s->in_cap.assign(s->T, 0);
     s->out_cap.assign(s->T, 0);
+    s->spare.in_pool.assign(s->T, nullptr);
+    s->spare.in_cap.assign(s->T, 0);
     if (ensure_desc_capacity(s, 16))
         return fail(-1);
     *out = s;
@@ -275,25 +280,28 @@ int ensure_desc_capacity(Session *s, int segs)
     if (segs <= s->seg_cap)
         return 0;
     UMX_CUDA_OK(cudaDeviceSynchronize()); // nothing may still be reading the old tables
-    if (s->d_stft)
-        cudaFree(s->d_stft);
-    if (s->d_istft)
-        cudaFree(s->d_istft);
-    if (s->d_final)
-        cudaFree(s->d_final);
-    if (s->h_desc)
-        cudaFreeHost(s->h_desc);
-    s->d_stft = nullptr;
-    s->d_istft = nullptr;
-    s->d_final = nullptr;
-    s->h_desc = nullptr;
     s->seg_cap = 0;
     const size_t n = (size_t)segs * s->T;
-    UMX_CUDA_OK(cudaMalloc(&s->d_stft, sizeof(StftTrack) * n));
-    UMX_CUDA_OK(cudaMalloc(&s->d_istft, sizeof(IstftTrack) * n));
-    UMX_CUDA_OK(cudaMalloc(&s->d_final, sizeof(FinalizeTrack) * n * kPostParts));
     s->h_desc_bytes = (sizeof(StftTrack) + sizeof(IstftTrack) + sizeof(FinalizeTrack) * kPostParts) * n;
-    UMX_CUDA_OK(cudaMallocHost(&s->h_desc, s->h_desc_bytes));
+    auto renew = [&](StftTrack *&a, IstftTrack *&b, FinalizeTrack *&c, void *&h) -> int {
+        cudaFree(a);
+        cudaFree(b);
+        cudaFree(c);
+        if (h)
+            cudaFreeHost(h);
+        a = nullptr;
+        b = nullptr;
+        c = nullptr;
+        h = nullptr;
+        UMX_CUDA_OK(cudaMalloc(&a, sizeof(StftTrack) * n));
+        UMX_CUDA_OK(cudaMalloc(&b, sizeof(IstftTrack) * n));
+        UMX_CUDA_OK(cudaMalloc(&c, sizeof(FinalizeTrack) * n * kPostParts));
+        UMX_CUDA_OK(cudaMallocHost(&h, s->h_desc_bytes));
+        return 0;
+    };
+    if (renew(s->d_stft, s->d_istft, s->d_final, s->h_desc) ||
+        renew(s->spare.d_stft, s->spare.d_istft, s->spare.d_final, s->spare.h_desc))
+        return -1;
     s->seg_cap = segs;
     return 0;
 }
@@ -314,11 +322,21 @@ void session_destroy(Session *s)
         cudaFree(p);
     for (auto *p : s->out_pool)
         cudaFree(p);
+    for (auto *p : s->spare.in_pool)
+        cudaFree(p);
     cudaFree(s->d_stft);
     cudaFree(s->d_istft);
     cudaFree(s->d_final);
+    cudaFree(s->spare.d_stft);
+    cudaFree(s->spare.d_istft);
+    cudaFree(s->spare.d_final);
     if (s->h_desc)
         cudaFreeHost(s->h_desc);
+    if (s->spare.h_desc)
+        cudaFreeHost(s->spare.h_desc);
+    for (cudaEvent_t e : {s->spare.desc_copied, s->call_done[0], s->call_done[1]})
+        if (e)
+            cudaEventDestroy(e);
     for (auto e : s->ev_pool)
         cudaEventDestroy(e);
     for (auto e : s->timer_pool)
@@ -754,6 +772,8 @@ int session_infer_segment(Session *s, const float *audio, int n, float *out)
 {
     UMX_CHECK(n >= 0 && n <= s->n_buf, "umx_cuda_infer_segment: n must be in [0, n_buf]");
     UMX_CUDA_OK(cudaSetDevice(s->device));
+    if (int rc = session_wait(s, 0)) // calls enqueued with umx_cuda_demix_async use the same buffers
+        return rc;
     session_begin_profile(s);
     if (grow(&s->in_pool[0], &s->in_cap[0], std::max(n, 1)) || grow(&s->out_pool[0], &s->out_cap[0], 4L * std::max(n, 1)))
         return -1;
@@ -875,6 +895,9 @@ static int demix_wavefront(Session *s, const float *const *d_audio, const int64_
             if (wait(s->st_lane[l][g], fork))
                 return -1;
     std::vector<long> copied_in(n_tracks, 0);
+    // the previous call's finished ranges may still be on their way out of the output buffers this call's post stage writes
+    if (host_out && s->calls_enqueued > 0 && wait(s->st_post, s->call_done[s->calls_enqueued & 1]))
+        return -1;
 
     for (int sg = 0; sg < max_segs; ++sg)
     {
@@ -992,9 +1015,7 @@ static int demix_wavefront(Session *s, const float *const *d_audio, const int64_
     // join: the post stage of the last segment is the last thing to finish; the lanes and the front stream finished before it
     if (wait(main_st, back_done[max_segs - 1]))
         return -1;
-    if (host_out)
-        UMX_CUDA_OK(cudaStreamSynchronize(s->st_out));
-    return 0;
+    return 0; // (the caller, session_demix_host, marks the end of the output copies)
 }
 
 int session_demix_device(Session *s, const float *const *d_audio, const int64_t *n_samples, int n_tracks,
@@ -1093,9 +1114,14 @@ int session_demix_device(Session *s, const float *const *d_audio, const int64_t 
         // The tables travel at the HEAD of the input copy stream, not on the compute stream: a copy engine serves one stream's
         // queued copies to the end before it turns to another stream's, so three small uploads issued elsewhere would sit behind
         // every input copy of the call (measured: the first kernel then starts when the last input byte has arrived).
-        cudaEvent_t prev = take_event(s, s->ev_cursor);
-        UMX_CUDA_OK(cudaEventRecord(prev, s->st)); // the previous call's kernels (stream order) are done with the old tables
-        UMX_CUDA_OK(cudaStreamWaitEvent(s->st_in, prev, 0));
+        // Host-buffer calls alternate between two sets of tables and input buffers (session_demix_host): the set in hand was
+        // last used two calls ago, so nothing is waited for and the uploads run under the previous call's kernels.
+        if (!host_in)
+        {
+            cudaEvent_t prev = take_event(s, s->ev_cursor);
+            UMX_CUDA_OK(cudaEventRecord(prev, s->st)); // the previous call's kernels (stream order) are done with the old tables
+            UMX_CUDA_OK(cudaStreamWaitEvent(s->st_in, prev, 0));
+        }
         UMX_CUDA_OK(cudaMemcpyAsync(s->d_stft, hp, b0, cudaMemcpyHostToDevice, s->st_in));
         UMX_CUDA_OK(cudaMemcpyAsync(s->d_istft, hp + b0, b1, cudaMemcpyHostToDevice, s->st_in));
         UMX_CUDA_OK(cudaMemcpyAsync(s->d_final, hp + b0 + b1, b2, cudaMemcpyHostToDevice, s->st_in));
@@ -1108,6 +1134,8 @@ int session_demix_device(Session *s, const float *const *d_audio, const int64_t 
     if (s->pipeline == 3 && max_segs > 1)
         return demix_wavefront(s, d_audio, n_samples, n_tracks, shift_offset, d_out, host_in, host_out, max_segs, stride, hf, max_range, ship_any);
     // in order on the caller's stream: h/c stream from segment to segment
+    if (host_out && s->calls_enqueued > 0) // the previous call's output copies have left the output buffers
+        UMX_CUDA_OK(cudaStreamWaitEvent(s->st, s->call_done[s->calls_enqueued & 1], 0));
     for (int sg = 0; sg < max_segs; ++sg)
     {
         if (host_in)
@@ -1146,32 +1174,77 @@ int session_demix_device(Session *s, const float *const *d_audio, const int64_t 
             }
         }
     }
-    if (host_out)
-        UMX_CUDA_OK(cudaStreamSynchronize(s->st_out));
+    return 0;
+}
+
+int session_wait(Session *s, long ticket)
+{
+    if (ticket <= 0 || ticket > s->calls_enqueued)
+        ticket = s->calls_enqueued;
+    if (ticket <= s->calls_completed)
+        return 0;
+    UMX_CUDA_OK(cudaSetDevice(s->device));
+    for (long t = std::max(s->calls_completed + 1, ticket - 1); t <= ticket; ++t) // at most two calls are in flight
+        UMX_CUDA_OK(cudaEventSynchronize(s->call_done[t & 1]));
+    s->calls_completed = ticket;
     return 0;
 }
 
 int session_demix_host(Session *s, const float *const *audio, const int64_t *n_samples, int n_tracks, int shift_offset,
-                       float *const *out)
+                       float *const *out, long *ticket)
 {
     UMX_CHECK(n_tracks >= 1 && n_tracks <= s->T, "umx_cuda_demix: n_tracks must be in [1, max_tracks]");
     UMX_CUDA_OK(cudaSetDevice(s->device));
+    const long me = s->calls_enqueued + 1;
+    if (me > 2)
+        if (int rc = session_wait(s, me - 2)) // the tables and input buffers this call takes over belong to the call before the last
+        return rc;
+    std::swap(s->d_stft, s->spare.d_stft);
+    std::swap(s->d_istft, s->spare.d_istft);
+    std::swap(s->d_final, s->spare.d_final);
+    std::swap(s->h_desc, s->spare.h_desc);
+    std::swap(s->desc_copied, s->spare.desc_copied);
+    s->in_pool.swap(s->spare.in_pool);
+    s->in_cap.swap(s->spare.in_cap);
+    // stage timers belong to one call at a time: a call enqueued behind a running one is not profiled
+    const bool was_profiling = s->profiling;
+    if (ticket && s->calls_completed < s->calls_enqueued)
+        s->profiling = false;
     session_begin_profile(s);
     std::vector<const float *> din(n_tracks);
     std::vector<float *> dout(n_tracks);
-    for (int i = 0; i < n_tracks; ++i)
+    int rc = 0;
+    for (int i = 0; i < n_tracks && !rc; ++i)
     {
         const long n = std::max<long>((long)n_samples[i], 1);
-        if (grow(&s->in_pool[i], &s->in_cap[i], n) || grow(&s->out_pool[i], &s->out_cap[i], 4 * n))
-            return -1;
+        rc = grow(&s->in_pool[i], &s->in_cap[i], n) || grow(&s->out_pool[i], &s->out_cap[i], 4 * n);
         din[i] = reinterpret_cast<const float *>(s->in_pool[i]);
         dout[i] = reinterpret_cast<float *>(s->out_pool[i]);
     }
     // inputs stream in and finished output ranges stream out on their own copy streams, segment by segment
-    if (int rc = session_demix_device(s, din.data(), n_samples, n_tracks, shift_offset, dout.data(), audio, out))
-        return rc;
-    UMX_CUDA_OK(cudaStreamSynchronize(s->st));
-    return session_end_profile(s);
+    if (!rc)
+        rc = session_demix_device(s, din.data(), n_samples, n_tracks, shift_offset, dout.data(), audio, out);
+    if (!rc)
+        rc = session_end_profile(s);
+    s->profiling = was_profiling;
+    // the end of the call: its kernels (joined into s->st) and every copy queued on the output stream.  Recorded even after a
+    // failure, so that whatever was enqueued is waited for before its buffers are touched again.
+    cudaEvent_t joined = take_event(s, s->ev_cursor);
+    if (cudaEventRecord(joined, s->st) != cudaSuccess || cudaStreamWaitEvent(s->st_out, joined, 0) != cudaSuccess ||
+        cudaEventRecord(s->call_done[me & 1], s->st_out) != cudaSuccess)
+    {
+        cudaDeviceSynchronize();
+        set_error("umx_cuda_demix: could not mark the end of the call");
+        return -1;
+    }
+    s->calls_enqueued = me;
+    if (rc || !ticket)
+    {
+        const int wrc = session_wait(s, me);
+        return rc ? rc : wrc;
+    }
+    *ticket = me;
+    return 0;
 }
 
 } // namespace umx

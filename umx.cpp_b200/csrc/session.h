@@ -82,6 +82,21 @@ struct Session
     cudaEvent_t desc_copied = nullptr;              // the previous call's descriptor upload has left the staging buffer
     std::vector<cudaEvent_t> ev_pool;
     size_t ev_cursor = 0;
+    // Calls on host buffers alternate between two sets of descriptor tables, staging and input buffers, so that a call can be
+    // enqueued (umx_cuda_demix_async) while the previous one is still running: its inputs and tables go up meanwhile, and the
+    // previous call's last output ranges travel to the host under its first kernels.  At most two calls are in flight.
+    struct CallSet
+    {
+        StftTrack *d_stft = nullptr;
+        IstftTrack *d_istft = nullptr;
+        FinalizeTrack *d_final = nullptr;
+        void *h_desc = nullptr;
+        cudaEvent_t desc_copied = nullptr;
+        std::vector<float2 *> in_pool;
+        std::vector<long> in_cap;
+    } spare; // the set the previous host-buffer call used
+    cudaEvent_t call_done[2] = {};             // [ticket & 1]: everything of that call, copies included, has finished
+    long calls_enqueued = 0, calls_completed = 0; // tickets count from 1
     // grow-only pools for whole-track demixing
     std::vector<float2 *> acc_pool, in_pool, out_pool;
     std::vector<long> acc_cap, in_cap, out_cap;
@@ -136,8 +151,10 @@ int session_lstm(Session *s, int n_tracks, int target_begin, int target_count, b
 int session_demix_device(Session *s, const float *const *d_audio, const int64_t *n_samples, int n_tracks,
                          int shift_offset, float *const *d_out, const float *const *host_in = nullptr,
                          float *const *host_out = nullptr);
+// ticket (optional): the call only enqueues the work and returns its ticket for session_wait; null: returns when the outputs are there
 int session_demix_host(Session *s, const float *const *audio, const int64_t *n_samples, int n_tracks,
-                       int shift_offset, float *const *out);
+                       int shift_offset, float *const *out, long *ticket = nullptr);
+int session_wait(Session *s, long ticket); // 0: every call enqueued so far
 int session_infer_segment(Session *s, const float *audio, int n, float *out);
 void session_begin_profile(Session *s);
 int session_end_profile(Session *s);
