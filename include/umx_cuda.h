@@ -13,6 +13,9 @@
  *   mags      Eigen::Tensor3dXf(2, F, 2049)      -> float[2049][F][2]
  *   matrices  Eigen::MatrixXf(r, c)              -> float[c][r]
  * Host pointers unless a parameter is named d_* (device pointer).
+ *
+ * Threading: like the reference's lstm_data / stft_buffers, a session belongs to one host thread at a time; different sessions
+ * (and models) may be used from different threads.  umx_cuda_last_error() is per thread.
  */
 #ifndef UMX_CUDA_H
 #define UMX_CUDA_H
