@@ -123,3 +123,20 @@ def test_cpp_ggml_writer_round_trip(tmp_path):
         rm = ref.Model(str(out))
         assert rm.hidden == 16
         assert np.array_equal(rm.tensor("fc1_w", 1), targets[1][4].dequant().reshape(16, 2974).T)
+
+
+def test_header_is_plain_c_and_links_from_c(umx, tmp_path):
+    """include/umx_cuda.h compiles as C99 with strict warnings, and a C program linked against libumx_cuda.so gets the reference's
+    segment table (umx.cpp:214-218: 5 segments for 3 minutes, the last one 18,017 samples) through the ABI."""
+    inc = os.path.join(ROOT, "include")
+    subprocess.run(["/usr/bin/gcc", "-std=c99", "-pedantic", "-Wall", "-Wextra", "-Wstrict-prototypes", "-Werror", "-fsyntax-only",
+                    "-x", "c", os.path.join(inc, "umx_cuda.h")], check=True)
+    exe = tmp_path / "abi_from_c"
+    libdir = os.path.dirname(umx.LIB_PATH)
+    subprocess.run(["/usr/bin/gcc", "-std=c99", "-Wall", "-Werror", "-I", inc, "-o", str(exe), os.path.join(ROOT, "tests", "host", "abi_from_c.c"),
+                    "-L", libdir, "-l:libumx_cuda.so", f"-Wl,-rpath,{libdir}"], check=True)
+    out = subprocess.run([str(exe)], check=True, capture_output=True, text=True).stdout.split("\n")
+    assert out[0] == "frames 2584 segments 5"
+    rows = [tuple(int(x) for x in l.split()) for l in out[1:] if l]
+    total = 7938000 + 22050 - 4033  # umx.cpp:120-121
+    assert rows == [(k * 1984500, min(2646000, total - k * 1984500)) for k in range(5)] and rows[-1][1] == 18017
